@@ -1,0 +1,180 @@
+"""dsp_b200 -- host-side Python mirror of libscrubjay_cuda's C ABI (include/scrubjay_cuda.h).
+
+The product is the C shared library `dsp_b200/libscrubjay_cuda.so` (hand-written sm_100a CUDA behind
+plain-C entry points, see dsp_b200/csrc).  This module is only a thin ctypes binding so that tests
+and bench.py can call the library the way a C host would; it holds no arithmetic and no fallback:
+if the library is missing or no B200 is present the calls raise.
+
+Reference interface mirrored (cornell-c2s2/dsp):
+  mfcc_stats   cepstrum/scrubjay_infer.c:19-77   -> ScrubJay.mfcc_stats / mfcc_stats_batch_dev
+  ort_init     cepstrum/scrubjay_infer.c:93-102  -> ScrubJay(...)
+  ort_predict  cepstrum/scrubjay_infer.c:105-141 -> ScrubJay.predict / predict_batch_dev
+  main loop    cepstrum/scrubjay_infer.c:156-177 -> ScrubJay.infer_batch / infer_batch_dev
+"""
+import ctypes
+import os
+
+import numpy as np
+
+N_MFCC = 20
+FEAT_DIM = 40
+WIN_SIZE = 2048
+HOP_SIZE = 1024
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libscrubjay_cuda.so")
+DEFAULT_MODEL = os.path.join(_HERE, "data", "scrubjay_svm.bin")
+
+_lib = None
+
+
+class ScrubJayError(RuntimeError):
+    pass
+
+
+def load_library():
+    """dlopen the in-tree library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ScrubJayError("%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                            "or `make -C dsp_b200/csrc`" % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, c_long, c_int, c_uint = ctypes.c_void_p, ctypes.c_long, ctypes.c_int, ctypes.c_uint
+    L.scrubjay_create.argtypes = [ctypes.POINTER(vp), c_int, vp, ctypes.c_size_t, c_uint]
+    L.scrubjay_destroy.argtypes = [vp]
+    L.scrubjay_destroy.restype = None
+    L.scrubjay_last_error.argtypes = [vp]
+    L.scrubjay_last_error.restype = ctypes.c_char_p
+    L.scrubjay_set_stream.argtypes = [vp, vp]
+    L.scrubjay_launch_count.argtypes = [vp]
+    L.scrubjay_launch_count.restype = c_long
+    L.scrubjay_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.scrubjay_mfcc_stats_batch_dev.argtypes = [vp, vp, c_long, c_int, vp]
+    L.scrubjay_predict_batch_dev.argtypes = [vp, vp, c_long, vp, vp, vp]
+    L.scrubjay_infer_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_mfcc_stats.argtypes = [vp, vp, c_long, vp]
+    L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
+    L.scrubjay_infer_batch.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_synth_clips_dev.argtypes = [vp, vp, c_long, c_long, c_int, c_uint]
+    L.scrubjay_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
+    L.scrubjay_host_free.argtypes = [vp]
+    L.scrubjay_host_free.restype = None
+    _lib = L
+    return L
+
+
+def _ptr(x):
+    """Raw address of a device tensor (anything with data_ptr()), a numpy array, an int or None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    raise TypeError("cannot take the address of %r" % type(x))
+
+
+class ScrubJay:
+    """One context per GPU (scrubjay_create / scrubjay_destroy)."""
+
+    def __init__(self, device=0, samplerate=16000, model_blob=None):
+        self._L = load_library()
+        self._h = ctypes.c_void_p()
+        if model_blob is None:
+            blob, n = None, 0
+        else:
+            blob = bytes(model_blob)
+            n = len(blob)
+        rc = self._L.scrubjay_create(ctypes.byref(self._h), device, blob, n, samplerate)
+        if rc != 0:
+            msg = self._L.scrubjay_last_error(None).decode()
+            self._h = ctypes.c_void_p()
+            raise ScrubJayError("scrubjay_create failed (%d): %s" % (rc, msg))
+        self.device = device
+        self.samplerate = samplerate
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.scrubjay_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc < 0:
+            raise ScrubJayError("libscrubjay_cuda error %d: %s" % (rc, self._L.scrubjay_last_error(self._h).decode()))
+        return rc
+
+    # ---- plumbing
+    def set_stream(self, cuda_stream):
+        """cuda_stream: integer cudaStream_t handle (e.g. torch.cuda.current_stream().cuda_stream)."""
+        self._check(self._L.scrubjay_set_stream(self._h, cuda_stream))
+
+    @property
+    def launch_count(self):
+        return self._L.scrubjay_launch_count(self._h)
+
+    def last_kernel_ms(self):
+        ms = ctypes.c_float()
+        self._check(self._L.scrubjay_last_kernel_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    # ---- device-pointer entry points
+    def mfcc_stats_batch_dev(self, d_clips, n_clips, n_samples, d_feats):
+        self._check(self._L.scrubjay_mfcc_stats_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_feats)))
+
+    def predict_batch_dev(self, d_feats, n, d_labels, d_conf=None, d_score=None):
+        self._check(self._L.scrubjay_predict_batch_dev(self._h, _ptr(d_feats), n, _ptr(d_labels), _ptr(d_conf),
+                                                       _ptr(d_score)))
+
+    def infer_batch_dev(self, d_clips, n_clips, n_samples, d_labels, d_conf=None, d_score=None, d_feats=None):
+        self._check(self._L.scrubjay_infer_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_labels),
+                                                     _ptr(d_conf), _ptr(d_score), _ptr(d_feats)))
+
+    def synth_clips_dev(self, d_out, first_clip, n_clips, n_samples, seed=0x5C2B):
+        self._check(self._L.scrubjay_synth_clips_dev(self._h, _ptr(d_out), first_clip, n_clips, n_samples, seed))
+
+    # ---- host-pointer entry points (numpy in, numpy out)
+    def mfcc_stats(self, samples):
+        x = np.ascontiguousarray(samples, dtype=np.float32)
+        out = np.empty(FEAT_DIM, np.float32)
+        self._check(self._L.scrubjay_mfcc_stats(self._h, x.ctypes.data, x.size, out.ctypes.data))
+        return out
+
+    def predict(self, feat):
+        f = np.ascontiguousarray(feat, dtype=np.float32)
+        assert f.size == FEAT_DIM
+        conf = ctypes.c_float()
+        label = self._check(self._L.scrubjay_predict(self._h, f.ctypes.data, ctypes.byref(conf)))
+        return label, conf.value
+
+    def infer_batch(self, clips, want_feats=False, n_clips=None, n_samples=None):
+        """clips: numpy [n_clips][n_samples] float32, or a raw host address with n_clips/n_samples."""
+        if isinstance(clips, np.ndarray):
+            clips = np.ascontiguousarray(clips, dtype=np.float32)
+            n_clips, n_samples = clips.shape
+        labels = np.empty(n_clips, np.int32)
+        conf = np.empty(n_clips, np.float32)
+        score = np.empty(n_clips, np.float32)
+        feats = np.empty((n_clips, FEAT_DIM), np.float32) if want_feats else None
+        self._check(self._L.scrubjay_infer_batch(self._h, _ptr(clips), n_clips, n_samples, labels.ctypes.data,
+                                                 conf.ctypes.data, score.ctypes.data, _ptr(feats)))
+        return (labels, conf, score, feats) if want_feats else (labels, conf, score)
+
+
+def shard_range(n_items, rank, world_size):
+    """Contiguous clip range [lo, hi) owned by `rank`: clips are independent,
+    so multi-GPU is pure sharding with no data-path collective."""
+    lo = (n_items * rank) // world_size
+    hi = (n_items * (rank + 1)) // world_size
+    return lo, hi

@@ -1,0 +1,396 @@
+// scrubjay_api.cu -- the C ABI of libscrubjay_cuda (include/scrubjay_cuda.h): context management,
+// device-pointer batch entry points and the host-pointer pipeline (H2D -> kernel -> D2H).
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/scrubjay_cuda.h"
+#include "cepstrum_kernel.h"
+#include "sj_tables.h"
+
+cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
+                            cudaStream_t stream);
+
+namespace {
+
+constexpr int kStages = 3;          // host pipeline depth
+constexpr long kChunkBytes = 256l << 20; // clips per chunk = kChunkBytes / clip bytes
+
+struct Stage {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    float *d_clips = nullptr;
+    int32_t *d_labels = nullptr, *h_labels = nullptr;
+    float *d_conf = nullptr, *d_score = nullptr, *d_feats = nullptr;
+    float *h_conf = nullptr, *h_score = nullptr, *h_feats = nullptr;
+    long pending_first = -1, pending_count = 0; // chunk whose outputs still sit in the h_* buffers
+};
+
+thread_local char g_create_err[512];
+
+} // namespace
+
+struct scrubjay_ctx {
+    int device = 0, num_sms = 0;
+    unsigned samplerate = 0;
+    cudaStream_t stream = nullptr;
+    SjTables *h_tables = nullptr, *d_tables = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool have_timing = false;
+    long launches = 0;
+    char err[512] = {0};
+    // host pipeline (allocated on first use)
+    Stage st[kStages];
+    long chunk_clips = 0;
+    int chunk_n_samples = 0;
+    // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
+    float *d_small = nullptr;
+};
+
+namespace {
+
+int set_err(scrubjay_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (c) {
+        if (e != cudaSuccess) snprintf(c->err, sizeof c->err, "%s: %s", what, cudaGetErrorString(e));
+        else snprintf(c->err, sizeof c->err, "%s", what);
+    }
+    return code;
+}
+
+#define SJ_CUDA(c, call)                                                \
+    do {                                                                \
+        cudaError_t e_ = (call);                                        \
+        if (e_ != cudaSuccess) return set_err((c), SJ_ECUDA, #call, e_); \
+    } while (0)
+
+void free_stages(scrubjay_ctx *c)
+{
+    for (Stage &s : c->st) {
+        if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.done) cudaEventDestroy(s.done);
+        cudaFree(s.d_clips); cudaFree(s.d_labels); cudaFree(s.d_conf); cudaFree(s.d_score); cudaFree(s.d_feats);
+        cudaFreeHost(s.h_labels); cudaFreeHost(s.h_conf); cudaFreeHost(s.h_score); cudaFreeHost(s.h_feats);
+        s = Stage();
+    }
+    c->chunk_clips = 0;
+    c->chunk_n_samples = 0;
+}
+
+int ensure_stages(scrubjay_ctx *c, int n_samples)
+{
+    if (c->chunk_clips && c->chunk_n_samples == n_samples) return SJ_OK;
+    free_stages(c);
+    long clips = kChunkBytes / ((long)n_samples * 4);
+    if (clips < 1) clips = 1;
+    for (Stage &s : c->st) {
+        SJ_CUDA(c, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        SJ_CUDA(c, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        SJ_CUDA(c, cudaMalloc(&s.d_clips, (size_t)clips * n_samples * 4));
+        SJ_CUDA(c, cudaMalloc(&s.d_labels, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMalloc(&s.d_conf, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMalloc(&s.d_score, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMalloc(&s.d_feats, (size_t)clips * SJ_FEAT * 4));
+        SJ_CUDA(c, cudaMallocHost(&s.h_labels, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMallocHost(&s.h_conf, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMallocHost(&s.h_score, (size_t)clips * 4));
+        SJ_CUDA(c, cudaMallocHost(&s.h_feats, (size_t)clips * SJ_FEAT * 4));
+    }
+    c->chunk_clips = clips;
+    c->chunk_n_samples = n_samples;
+    return SJ_OK;
+}
+
+int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, long n_clips, int n_samples,
+                    int32_t *labels, float *conf, float *score, float *feats, int do_svm, bool timed)
+{
+    SjCepstrumArgs a;
+    a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
+    a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
+    if (timed) SJ_CUDA(c, cudaEventRecord(c->ev0, stream));
+    SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables->mel_maxseg, c->num_sms, stream));
+    if (timed) { SJ_CUDA(c, cudaEventRecord(c->ev1, stream)); c->have_timing = true; }
+    c->launches += 1;
+    return SJ_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int scrubjay_create(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes, unsigned samplerate)
+{
+    g_create_err[0] = 0;
+    if (!out) { snprintf(g_create_err, sizeof g_create_err, "out is NULL"); return SJ_EINVAL; }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) {
+        snprintf(g_create_err, sizeof g_create_err, "no usable CUDA device %d (%s); libscrubjay_cuda has no CPU fallback",
+                 device, e == cudaSuccess ? "index out of range" : cudaGetErrorString(e));
+        return SJ_ENODEVICE;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10) {
+        snprintf(g_create_err, sizeof g_create_err, "device %d is not sm_100 (libscrubjay_cuda is built for sm_100a only)", device);
+        return SJ_ENODEVICE;
+    }
+    scrubjay_ctx *c = new (std::nothrow) scrubjay_ctx();
+    if (!c) return SJ_ENOMEM;
+    c->device = device;
+    c->samplerate = samplerate;
+    c->num_sms = prop.multiProcessorCount;
+    c->h_tables = new (std::nothrow) SjTables;
+    char terr[256] = {0};
+    int rc = SJ_OK;
+    if (!c->h_tables) rc = SJ_ENOMEM;
+    else if (sj_build_tables(c->h_tables, model_blob, blob_bytes, samplerate, terr)) {
+        snprintf(g_create_err, sizeof g_create_err, "%s", terr);
+        rc = strstr(terr, "model") || strstr(terr, "support-vector") ? SJ_EMODEL : SJ_EINVAL;
+    }
+    if (rc == SJ_OK) {
+        cudaError_t ce = cudaSetDevice(device);
+        if (ce == cudaSuccess) ce = cudaMalloc(&c->d_tables, sizeof(SjTables));
+        if (ce == cudaSuccess) ce = cudaMemcpy(c->d_tables, c->h_tables, sizeof(SjTables), cudaMemcpyHostToDevice);
+        if (ce == cudaSuccess) ce = cudaMalloc(&c->d_small, 4096);
+        if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
+        if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
+        if (ce == cudaSuccess) ce = sj_cepstrum_setup(c->h_tables->mel_maxseg);
+        if (ce != cudaSuccess) {
+            snprintf(g_create_err, sizeof g_create_err, "CUDA set-up failed: %s", cudaGetErrorString(ce));
+            rc = SJ_ECUDA;
+        }
+    }
+    if (rc != SJ_OK) { scrubjay_destroy(c); return rc; }
+    *out = c;
+    return SJ_OK;
+}
+
+void scrubjay_destroy(scrubjay_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    free_stages(c);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    cudaFree(c->d_tables);
+    cudaFree(c->d_small);
+    delete c->h_tables;
+    delete c;
+}
+
+const char *scrubjay_last_error(const scrubjay_ctx *c) { return c ? c->err : g_create_err; }
+
+int scrubjay_set_stream(scrubjay_ctx *c, void *s)
+{
+    if (!c) return SJ_EINVAL;
+    c->stream = (cudaStream_t)s;
+    return SJ_OK;
+}
+
+long scrubjay_launch_count(const scrubjay_ctx *c) { return c ? c->launches : 0; }
+
+int scrubjay_last_kernel_ms(scrubjay_ctx *c, float *ms)
+{
+    if (!c || !ms) return SJ_EINVAL;
+    if (!c->have_timing) return set_err(c, SJ_EINVAL, "no timed launch yet");
+    SJ_CUDA(c, cudaEventSynchronize(c->ev1));
+    SJ_CUDA(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return SJ_OK;
+}
+
+int scrubjay_mfcc_stats_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, float *d_feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || !d_feats || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip"); // scrubjay_infer.c:55-59
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    return launch_cepstrum(c, c->stream, d_clips, n_clips, n_samples, nullptr, nullptr, nullptr, d_feats, 0, true);
+}
+
+int scrubjay_predict_batch_dev(scrubjay_ctx *c, const float *d_feats, long n, int32_t *d_labels, float *d_conf,
+                               float *d_score)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_feats || !d_labels || n < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    SJ_CUDA(c, sj_launch_svm(d_feats, n, c->d_tables, d_labels, d_conf, d_score, c->stream));
+    SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->have_timing = true;
+    if (n > 0) c->launches += 1;
+    return SJ_OK;
+}
+
+int scrubjay_infer_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int32_t *d_labels,
+                             float *d_conf, float *d_score, float *d_feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    return launch_cepstrum(c, c->stream, d_clips, n_clips, n_samples, d_labels, d_conf, d_score, d_feats, 1, true);
+}
+
+} // extern "C"
+
+namespace {
+
+// drain the outputs of a finished chunk from the stage's pinned buffers into the caller's arrays
+int drain(scrubjay_ctx *c, Stage &s, int32_t *labels, float *conf, float *score, float *feats)
+{
+    if (s.pending_first < 0) return SJ_OK;
+    SJ_CUDA(c, cudaEventSynchronize(s.done));
+    const long f = s.pending_first, n = s.pending_count;
+    if (labels) memcpy(labels + f, s.h_labels, (size_t)n * 4);
+    if (conf) memcpy(conf + f, s.h_conf, (size_t)n * 4);
+    if (score) memcpy(score + f, s.h_score, (size_t)n * 4);
+    if (feats) memcpy(feats + f * SJ_FEAT, s.h_feats, (size_t)n * SJ_FEAT * 4);
+    s.pending_first = -1;
+    return SJ_OK;
+}
+
+// host clips -> chunked 3-stage pipeline.  do_svm = 0 computes features only.
+int run_host_batch(scrubjay_ctx *c, const float *clips, long n_clips, int n_samples, int32_t *labels, float *conf,
+                   float *score, float *feats, int do_svm)
+{
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    int rc = ensure_stages(c, n_samples);
+    if (rc != SJ_OK) return rc;
+    long done = 0;
+    for (int i = 0; done < n_clips; ++i) {
+        Stage &s = c->st[i % kStages];
+        rc = drain(c, s, labels, conf, score, feats);
+        if (rc != SJ_OK) return rc;
+        const long n = (n_clips - done < c->chunk_clips) ? n_clips - done : c->chunk_clips;
+        SJ_CUDA(c, cudaMemcpyAsync(s.d_clips, clips + done * (long)n_samples, (size_t)n * n_samples * 4,
+                                   cudaMemcpyHostToDevice, s.stream));
+        rc = launch_cepstrum(c, s.stream, s.d_clips, n, n_samples, s.d_labels, s.d_conf, s.d_score,
+                             feats ? s.d_feats : nullptr, do_svm, false);
+        if (rc != SJ_OK) return rc;
+        if (do_svm) {
+            SJ_CUDA(c, cudaMemcpyAsync(s.h_labels, s.d_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream));
+            if (conf) SJ_CUDA(c, cudaMemcpyAsync(s.h_conf, s.d_conf, (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream));
+            if (score) SJ_CUDA(c, cudaMemcpyAsync(s.h_score, s.d_score, (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream));
+        }
+        if (feats)
+            SJ_CUDA(c, cudaMemcpyAsync(s.h_feats, s.d_feats, (size_t)n * SJ_FEAT * 4, cudaMemcpyDeviceToHost, s.stream));
+        SJ_CUDA(c, cudaEventRecord(s.done, s.stream));
+        s.pending_first = done;
+        s.pending_count = n;
+        done += n;
+    }
+    for (Stage &s : c->st) {
+        rc = drain(c, s, do_svm ? labels : nullptr, do_svm ? conf : nullptr, do_svm ? score : nullptr, feats);
+        if (rc != SJ_OK) return rc;
+    }
+    return SJ_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int scrubjay_infer_batch(scrubjay_ctx *c, const float *clips, long n_clips, int n_samples, int32_t *labels,
+                         float *conf, float *score, float *feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!clips || !labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    return run_host_batch(c, clips, n_clips, n_samples, labels, conf, score, feats, 1);
+}
+
+int scrubjay_mfcc_stats(scrubjay_ctx *c, const float *samples, long n_samples, float out[SJ_FEAT_DIM])
+{
+    if (!c) return SJ_EINVAL;
+    if (!samples || !out) return set_err(c, SJ_EINVAL, "NULL pointer");
+    if (n_samples <= 0 || n_samples > 0x7fffffffL) return set_err(c, SJ_EINVAL, "empty clip");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    float *d = nullptr;
+    SJ_CUDA(c, cudaMalloc(&d, (size_t)n_samples * 4));
+    cudaError_t e = cudaMemcpyAsync(d, samples, (size_t)n_samples * 4, cudaMemcpyHostToDevice, c->stream);
+    int rc = SJ_OK;
+    if (e == cudaSuccess)
+        rc = launch_cepstrum(c, c->stream, d, 1, (int)n_samples, nullptr, nullptr, nullptr, c->d_small, 0, false);
+    if (e == cudaSuccess && rc == SJ_OK)
+        e = cudaMemcpyAsync(out, c->d_small, SJ_FEAT * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && rc == SJ_OK) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return set_err(c, SJ_ECUDA, "scrubjay_mfcc_stats", e);
+    return rc;
+}
+
+int scrubjay_predict(scrubjay_ctx *c, const float feat[SJ_FEAT_DIM], float *conf)
+{
+    if (!c) return SJ_EINVAL;
+    if (!feat) return set_err(c, SJ_EINVAL, "NULL pointer");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    float *d_feat = c->d_small;            // [40]
+    int32_t *d_label = (int32_t *)(c->d_small + 64);
+    float *d_conf = c->d_small + 65, *d_score = c->d_small + 66;
+    SJ_CUDA(c, cudaMemcpyAsync(d_feat, feat, SJ_FEAT * 4, cudaMemcpyHostToDevice, c->stream));
+    SJ_CUDA(c, sj_launch_svm(d_feat, 1, c->d_tables, d_label, d_conf, d_score, c->stream));
+    c->launches += 1;
+    float host[3];
+    SJ_CUDA(c, cudaMemcpyAsync(host, c->d_small + 64, 12, cudaMemcpyDeviceToHost, c->stream));
+    SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    int32_t label;
+    memcpy(&label, &host[0], 4);
+    if (conf) *conf = host[1];
+    return (int)label;
+}
+
+int scrubjay_synth_clips_dev(scrubjay_ctx *c, float *d_out, long first_clip, long n_clips, int n_samples,
+                             unsigned seed)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_out || n_clips < 0 || n_samples <= 0) return set_err(c, SJ_EINVAL, "bad argument");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, sj_launch_synth(d_out, first_clip, n_clips, n_samples, seed, (float)c->samplerate, c->stream));
+    if (n_clips > 0) c->launches += 1;
+    return SJ_OK;
+}
+
+/* diagnostic (host only, no GPU): expand the kernel's chunked sparse mel tables back to a dense
+ * [40][1025] bank so tests can compare them with an independent construction */
+int scrubjay_debug_mel_dense(unsigned samplerate, float *out)
+{
+    if (!out) return SJ_EINVAL;
+    SjTables *t = new (std::nothrow) SjTables;
+    if (!t) return SJ_ENOMEM;
+    char err[256];
+    int rc = sj_build_tables(t, nullptr, 0, samplerate, err);
+    if (rc) { snprintf(g_create_err, sizeof g_create_err, "%s", err); delete t; return SJ_EINVAL; }
+    memset(out, 0, sizeof(float) * SJ_NFILT * SJ_NBINS);
+    // replay the kernel's walk: per lane, flush flag => next segment; segment -> filter via comb lists
+    const int maxseg = t->mel_maxseg, zero_slot = 2 * 32 * maxseg;
+    for (int L = 0; L < 32; ++L) {
+        int seg = 0;
+        for (int i = 0; i < t->mel_ch; ++i) {
+            const int k = t->mel_lo + L * t->mel_ch + i;
+            uint32_t bits;
+            memcpy(&bits, &t->melw[i][L].x, 4);
+            if (bits & 0x80000000u) ++seg;
+            const float wlo = fabsf(t->melw[i][L].x), whi = t->melw[i][L].y;
+            const int base = 2 * (L * maxseg + seg);
+            for (int m = 0; m < SJ_NFILT; ++m)
+                for (int e = 0; e < t->mel_ncomb; ++e) {
+                    const int idx = t->comb[e][m];
+                    if (idx == zero_slot || k >= SJ_NBINS) continue;
+                    if (idx == base && wlo != 0.f) out[m * SJ_NBINS + k] += wlo;
+                    if (idx == base + 1 && whi != 0.f) out[m * SJ_NBINS + k] += whi;
+                }
+        }
+    }
+    delete t;
+    return SJ_OK;
+}
+
+/* pinned host memory for callers that want full PCIe rate on the host-pointer entry points */
+int scrubjay_host_alloc(void **p, size_t bytes) { return cudaMallocHost(p, bytes) == cudaSuccess ? SJ_OK : SJ_ENOMEM; }
+void scrubjay_host_free(void *p) { cudaFreeHost(p); }
+
+} // extern "C"

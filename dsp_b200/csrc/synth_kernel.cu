@@ -1,0 +1,75 @@
+// synth_kernel.cu -- counter-based synthetic audio generator (bench / test input, not part of the
+// classification path).  Every sample is a pure function of (seed, clip index, sample index), so any
+// batch can be regenerated on any GPU without storing it:
+//   x[c][i] = 0.25*noise + sum_{k<3} a_k(c) * sin(2 pi chirp_k(c, i)) * gate_k(c, i)
+// with chirp bands drawn from {500-2500, 2500-5000, 5000-7000, 1000-3000} Hz; about 5 % of the clips
+// are all-zero or have a zero tail (exercises aubio's log10 floor and the donut path's Sxx > 0 test).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace {
+
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+__host__ __device__ __forceinline__ uint32_t hash3(uint32_t seed, uint32_t a, uint32_t b)
+{
+    return mix32(seed ^ mix32(a * 0x9e3779b9U + 0x85ebca6bU) ^ mix32(b * 0xc2b2ae35U + 0x27d4eb2fU));
+}
+__device__ __forceinline__ float u01(uint32_t h) { return (float)(h >> 8) * (1.0f / 16777216.0f); }
+
+struct Chirp { float f0, k, amp; int start, stop; };
+
+__global__ void synth_kernel(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs)
+{
+    const float lo_hz[4] = {500.f, 2500.f, 5000.f, 1000.f}, hi_hz[4] = {2500.f, 5000.f, 7000.f, 3000.f};
+    for (long c = blockIdx.x; c < n_clips; c += gridDim.x) {
+        const uint32_t cid = (uint32_t)(first_clip + c);
+        const uint32_t hc = hash3(seed, cid, 0xA5A5u);
+        int zero_from = n_samples; // first sample forced to zero
+        if (hc % 20u == 0u) zero_from = (hc & 0x100u) ? 0 : (int)(u01(mix32(hc)) * (float)n_samples);
+        Chirp ch[3];
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t h = hash3(seed, cid, 0x1000u + k);
+            const int band = h & 3;
+            const float a = u01(mix32(h + 1)), b = u01(mix32(h + 2));
+            const float f0 = lo_hz[band] + a * (hi_hz[band] - lo_hz[band]);
+            const float f1 = lo_hz[band] + b * (hi_hz[band] - lo_hz[band]);
+            const float dur = 0.1f + 0.6f * u01(mix32(h + 3));
+            const float st = u01(mix32(h + 4)) * (1.f - 0.3f);
+            ch[k].start = (int)(st * fs);
+            ch[k].stop = ch[k].start + (int)(dur * fs);
+            ch[k].f0 = f0 / fs;                                  // cycles per sample
+            ch[k].k = 0.5f * (f1 - f0) / (fs * dur * fs);        // cycles per sample^2
+            ch[k].amp = 0.2f * u01(mix32(h + 5));
+        }
+        float *dst = out + c * (long)n_samples;
+        for (int i = threadIdx.x; i < n_samples; i += blockDim.x) {
+            float x = 0.f;
+            if (i < zero_from) {
+                x = 0.25f * (2.f * u01(hash3(seed, cid, 0x10000u + (uint32_t)i)) - 1.f);
+                for (int k = 0; k < 3; ++k)
+                    if (i >= ch[k].start && i < ch[k].stop) {
+                        const float t = (float)(i - ch[k].start);
+                        float cyc = t * (ch[k].f0 + ch[k].k * t);
+                        cyc -= floorf(cyc);
+                        x += ch[k].amp * sinpif(2.f * cyc);
+                    }
+            }
+            dst[i] = x;
+        }
+    }
+}
+
+} // namespace
+
+cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
+                            cudaStream_t stream)
+{
+    if (n_clips <= 0) return cudaSuccess;
+    long blocks = n_clips < 148 * 16 ? n_clips : 148 * 16;
+    synth_kernel<<<(unsigned)blocks, 256, 0, stream>>>(out, first_clip, n_clips, n_samples, seed, fs);
+    return cudaGetLastError();
+}

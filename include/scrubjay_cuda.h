@@ -1,0 +1,118 @@
+/*
+ * scrubjay_cuda.h -- C ABI of libscrubjay_cuda: the batched, B200-native (sm_100a) drop-in for the
+ * audio-classification hot path of cornell-c2s2/dsp.
+ *
+ * Plain C: pointers and sizes only.  No torch types, no C++ in the signatures.  Every entry point
+ * names the reference interface it replaces (file:line under the reference tree).
+ *
+ * Two families of entry points:
+ *   *_dev   : pointers are DEVICE pointers on the context's GPU; work is enqueued on the context's
+ *             stream (scrubjay_set_stream) and is asynchronous with respect to the host.
+ *   others  : pointers are HOST pointers; the call stages through the context's pinned ring,
+ *             copies, computes, copies back and returns when the results are in the caller's arrays.
+ *
+ * Error handling: every call returns SJ_OK (0) or a negative SJ_E* code; scrubjay_last_error()
+ * returns a message.  The library never prints and never calls exit() (the reference does both:
+ * cepstrum/scrubjay_infer.c:22-26,84-91).  There is NO CPU fallback: without a usable sm_100 GPU
+ * scrubjay_create fails with SJ_ENODEVICE.
+ *
+ * Threading: one context per GPU; calls on one context must not overlap between host threads.
+ */
+#ifndef SCRUBJAY_CUDA_H
+#define SCRUBJAY_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SJ_API __attribute__((visibility("default")))
+#else
+#define SJ_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SJ_OK 0
+#define SJ_EINVAL (-1)    /* bad argument (NULL, negative size, empty clip: scrubjay_infer.c:55-59) */
+#define SJ_ENODEVICE (-2) /* no CUDA device / not sm_100 */
+#define SJ_ECUDA (-3)     /* CUDA runtime error, see scrubjay_last_error */
+#define SJ_EMODEL (-4)    /* malformed model blob */
+#define SJ_ENOMEM (-5)
+
+/* constants of the cepstrum path: cepstrum/scrubjay_infer.c:10-14 */
+#define SJ_N_MFCC 20
+#define SJ_FEAT_DIM 40
+#define SJ_WIN_SIZE 2048
+#define SJ_HOP_SIZE 1024
+#define SJ_N_FILTERS 40
+
+typedef struct scrubjay_ctx scrubjay_ctx;
+
+/* Replaces ort_init (cepstrum/scrubjay_infer.c:93-102) and the per-file new_aubio_pvoc /
+ * new_aubio_mfcc set-up (:29-30).  `model_blob` is an "SJSV" v1 blob (tools/export_svm.py) or NULL
+ * for the built-in export of cepstrum/scrubjay_svm.onnx.  `samplerate` is what aubio_source reports
+ * for the material (:28); it selects the Slaney filterbank. */
+SJ_API int scrubjay_create(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes,
+                    unsigned samplerate);
+SJ_API void scrubjay_destroy(scrubjay_ctx *ctx);
+/* ctx may be NULL: returns the message of the last failed scrubjay_create on this thread */
+SJ_API const char *scrubjay_last_error(const scrubjay_ctx *ctx);
+/* cudaStream_t as void*; NULL = the legacy default stream.  Device entry points enqueue here. */
+SJ_API int scrubjay_set_stream(scrubjay_ctx *ctx, void *cuda_stream);
+/* number of kernels this context has launched so far (for bench.py's gpu_launches) */
+SJ_API long scrubjay_launch_count(const scrubjay_ctx *ctx);
+/* milliseconds between the start and the end of the kernels of the most recent *_dev call,
+ * measured with CUDA events on the context's stream; synchronises the stream. */
+SJ_API int scrubjay_last_kernel_ms(scrubjay_ctx *ctx, float *ms);
+
+/* ---- cepstrum path ------------------------------------------------------------------------- */
+
+/* Batched mfcc_stats (cepstrum/scrubjay_infer.c:19-77) over in-memory mono clips instead of paths:
+ * d_clips is [n_clips][n_samples] float32 in [-1,1); d_feats is [n_clips][40] (mean[20] | std[20]).
+ * Frame count per clip = ceil(n_samples/1024) (the do/while at :39-53). */
+SJ_API int scrubjay_mfcc_stats_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips,
+                                  int n_samples, float *d_feats);
+
+/* Batched ort_predict (cepstrum/scrubjay_infer.c:105-141): Scaler -> SVMClassifier(RBF) -> label.
+ * d_labels[n] int32 0/1; d_conf[n] probability of the predicted class (:134); d_score[n] the
+ * decision value d (positive => class 1, = sklearn decision_function = -ORT score).  d_conf and
+ * d_score may be NULL. */
+SJ_API int scrubjay_predict_batch_dev(scrubjay_ctx *ctx, const float *d_feats, long n, int32_t *d_labels,
+                               float *d_conf, float *d_score);
+
+/* Fused mfcc_stats + ort_predict for a batch: the loop body of main (cepstrum/scrubjay_infer.c:
+ * 166-176) for n_clips clips in one kernel.  d_conf, d_score, d_feats may be NULL. */
+SJ_API int scrubjay_infer_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
+                             int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+
+/* Host-pointer forms.  scrubjay_mfcc_stats keeps the reference's contract: 0 on success, -1
+ * (SJ_EINVAL) on an empty clip. */
+SJ_API int scrubjay_mfcc_stats(scrubjay_ctx *ctx, const float *samples, long n_samples, float out[SJ_FEAT_DIM]);
+/* returns the label (0/1) like ort_predict, or a negative error */
+SJ_API int scrubjay_predict(scrubjay_ctx *ctx, const float feat[SJ_FEAT_DIM], float *conf);
+/* host clips [n_clips][n_samples] (pageable or pinned); chunks are pipelined H2D -> kernel -> D2H
+ * on internal streams.  conf / score / feats may be NULL. */
+SJ_API int scrubjay_infer_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
+                         int32_t *labels, float *conf, float *score, float *feats);
+
+/* Synthetic test/bench audio generated on the device: d_out[n_clips][n_samples], a pure function of
+ * (seed, first_clip + clip, sample) -- white noise floor + up to three gated chirps, ~5 % of clips
+ * silent or with a silent tail.  Not a reference function; the bench's "data": "synthetic". */
+SJ_API int scrubjay_synth_clips_dev(scrubjay_ctx *ctx, float *d_out, long first_clip, long n_clips,
+                                    int n_samples, unsigned seed);
+
+/* Diagnostic, host only (no GPU needed): the kernel's sparse filterbank tables for `samplerate`,
+ * expanded to a dense [40][1025] float array (weights carry a factor 0.5). */
+SJ_API int scrubjay_debug_mel_dense(unsigned samplerate, float *out);
+
+/* Pinned (page-locked) host memory: clips handed to the host-pointer entry points from such a
+ * buffer move at full PCIe rate; pageable memory works too, slower. */
+SJ_API int scrubjay_host_alloc(void **p, size_t bytes);
+SJ_API void scrubjay_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCRUBJAY_CUDA_H */

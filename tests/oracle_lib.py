@@ -1,0 +1,71 @@
+"""ctypes access to the CPU oracle (oracle/*.c).  Test infrastructure only: imported by tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs, never by dsp_b200."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+MODEL_BLOB = os.path.join(ROOT, "dsp_b200", "data", "scrubjay_svm.bin")
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
+
+
+class CepstrumOracle:
+    """oracle/cepstrum_oracle.c: restated aubio pvoc+mfcc (+ stats) and ORT Scaler+SVMClassifier."""
+
+    def __init__(self, samplerate=16000, precision="f64"):
+        path = os.path.join(ORACLE_DIR, "libsj_oracle_%s.so" % precision)
+        if not os.path.exists(path):
+            build_oracle()
+        L = ctypes.CDLL(path)
+        vp, c_long = ctypes.c_void_p, ctypes.c_long
+        L.sj_oracle_new.restype = vp
+        L.sj_oracle_new.argtypes = [ctypes.c_uint]
+        L.sj_oracle_free.argtypes = [vp]
+        L.sj_oracle_mfcc_stats.restype = c_long
+        L.sj_oracle_mfcc_stats.argtypes = [vp, vp, c_long, vp, vp]
+        L.sj_oracle_predict.restype = ctypes.c_int
+        L.sj_oracle_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float)]
+        L.sj_oracle_infer_batch.restype = c_long
+        L.sj_oracle_infer_batch.argtypes = [vp, vp, vp, c_long, c_long, vp, vp, vp, vp]
+        L.sj_oracle_fbank.restype = ctypes.POINTER(ctypes.c_float)
+        L.sj_oracle_fbank.argtypes = [vp]
+        self.L = L
+        self.h = L.sj_oracle_new(samplerate)
+        self.blob = open(MODEL_BLOB, "rb").read()
+
+    def fbank(self):
+        return np.ctypeslib.as_array(self.L.sj_oracle_fbank(self.h), shape=(40, 1025)).copy()
+
+    def mfcc_stats(self, x, want_frames=False):
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros(40, np.float32)
+        nfr = (x.size + 1023) // 1024
+        fr = np.zeros((max(nfr, 1), 20), np.float32)
+        n = self.L.sj_oracle_mfcc_stats(self.h, x.ctypes.data, x.size, out.ctypes.data, fr.ctypes.data)
+        if n < 0:
+            return None
+        return (out, fr[:n]) if want_frames else out
+
+    def predict(self, feat, blob=None):
+        f = np.ascontiguousarray(feat, np.float32)
+        c, s = ctypes.c_float(), ctypes.c_float()
+        label = self.L.sj_oracle_predict(blob or self.blob, f.ctypes.data, ctypes.byref(c), ctypes.byref(s))
+        return label, c.value, s.value
+
+    def infer_batch(self, clips):
+        clips = np.ascontiguousarray(clips, np.float32)
+        n, ns = clips.shape
+        labels = np.zeros(n, np.int32)
+        conf = np.zeros(n, np.float32)
+        score = np.zeros(n, np.float32)
+        feats = np.zeros((n, 40), np.float32)
+        r = self.L.sj_oracle_infer_batch(self.h, self.blob, clips.ctypes.data, n, ns, labels.ctypes.data,
+                                         conf.ctypes.data, score.ctypes.data, feats.ctypes.data)
+        assert r == n
+        return labels, conf, score, feats
