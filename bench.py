@@ -1,0 +1,336 @@
+#!/usr/bin/env python3
+"""bench.py -- clips/s of the batched cepstrum (MFCC mean/std) + RBF-SVM hot path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--clips C] [--impl ours|reference]
+  (N > 1: launched by torchrun, one rank per GPU; RANK/LOCAL_RANK/WORLD_SIZE from the env)
+
+Workload (BASELINE.json configs[1]): C = 1,000,000 synthetic 1 s / 16 kHz mono float32 clips per GPU
+(64 GB, resident in HBM; inputs >> 126 MB L2, so no L2 flush is needed between steps).  One step =
+one pass of libscrubjay_cuda's fused kernel over the whole resident batch -> label, confidence and
+decision value per clip.  Clips are independent units: N GPUs = N shards, no data-path collective;
+the only exchange is the final label/score all-gather (8 B/clip), done inside every timed step.
+
+Prints ONE JSON line (rank 0).  Keys beyond the base contract:
+  roofline      HBM roofline of the fused kernel: algorithmic bytes (64,008 B/clip: 16000 fp32 in,
+                int32 label + fp32 score out) / CUDA-event kernel time, vs MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline  the CPU restatement of the reference path (oracle/, float build; aubio/onnxruntime
+                are not available, so kind = "port") timed on this box's host cores on a bounded sample
+  e2e           same metric through the host-pointer C-ABI call scrubjay_infer_batch: pinned host
+                clips -> H2D -> kernel -> D2H labels/conf/score, all inside the timed region
+--impl reference times the CPU path alone on all host threads (rank 0 only).
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+N_SAMPLES = 16000
+BYTES_PER_CLIP = N_SAMPLES * 4 + 4 + 4  # fp32 clip in, int32 label + fp32 score out
+FRAMES_PER_CLIP = 16
+SEED = 0x5C2B
+METRIC = "clips/s (1 s @16 kHz) cepstrum+SVM"
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic_bytes_per_clip():
+    """dram read+write bytes per clip of the fused kernel from the committed ncu --set full capture"""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------- CPU path (oracle) timing
+def cpu_run(oracle, clips, threads):
+    """oracle.infer_batch over `clips`, split across `threads` OS threads (ctypes releases the GIL;
+    the oracle handle is read-only).  Returns seconds."""
+    import numpy as np
+    n = clips.shape[0]
+    bounds = [(n * i) // threads for i in range(threads + 1)]
+    out = [None] * threads
+
+    def work(i):
+        if bounds[i + 1] > bounds[i]:
+            out[i] = oracle.infer_batch(clips[bounds[i]:bounds[i + 1]])
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    t0 = time.perf_counter()
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    dt = time.perf_counter() - t0
+    labels = np.concatenate([o[0] for o in out if o is not None])
+    return dt, labels
+
+
+def cpu_baseline(clips_np, target_seconds=12.0):
+    """time the float 'port' build of the oracle on a bounded sample sized for ~target_seconds"""
+    import numpy as np
+    from oracle_lib import CepstrumOracle
+    oracle = CepstrumOracle(16000, "f32")
+    threads = host_threads()
+    dt1, _ = cpu_run(oracle, clips_np[:32], 1)  # single-thread rate, for the per-core figure
+    probe = clips_np[:max(threads * 4, 64)]
+    dt, _ = cpu_run(oracle, probe, threads)
+    rate = probe.shape[0] / dt
+    n = int(min(clips_np.shape[0], max(probe.shape[0], rate * target_seconds)))
+    dt, _ = cpu_run(oracle, clips_np[:n], threads)
+    return {"value": n / dt, "unit": "clips/s", "cores": threads, "kind": "port", "one_thread_value": 32 / dt1,
+            "sample": "%d of the step's clips (same bytes the GPU consumed), %.1f s wall, oracle/cepstrum_oracle.c "
+                      "float build -O3 (restated aubio+onnxruntime: the reference's own libraries are unavailable)"
+                      % (n, dt)}
+
+
+# ---------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    """samples SM clock and throttle reasons (NVML) while the timed region runs"""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unsampled"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+# ---------------------------------------------------------------- reference arm (CPU only)
+def run_reference(args, rank):
+    if rank != 0:
+        return 0
+    from oracle_lib import CepstrumOracle
+    from synth_np import synth_clips
+    oracle = CepstrumOracle(16000, "f32")
+    threads = host_threads()
+    per_step = threads * args.ref_clips_per_thread
+    clips = synth_clips(0, per_step, N_SAMPLES, SEED)
+    for _ in range(args.warmup):
+        cpu_run(oracle, clips, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_run(oracle, clips, threads)
+    dt = time.perf_counter() - t0
+    value = per_step * args.steps / dt
+    sample = ("each step = %d synthetic clips (%d per thread) of the 1M-clip workload, restated reference path "
+              "(oracle/cepstrum_oracle.c float build, -O3); aubio/onnxruntime not available so the reference "
+              "binary itself cannot be built" % (per_step, args.ref_clips_per_thread))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "batched cepstrum features + SVM on 1M synthetic 1 s 16 kHz mono clips (bounded sample)",
+                       "clips_per_step": per_step, "n_samples": N_SAMPLES},
+            "frames_per_s": value * FRAMES_PER_CLIP,
+            "cpu_baseline": {"value": value, "unit": "clips/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------- our arm
+def run_ours(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import dsp_b200
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no GPU (libscrubjay_cuda has no CPU fallback; use --impl reference for the CPU path)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    C = args.clips
+    sj = dsp_b200.ScrubJay(device=local_rank, samplerate=16000)
+    stream = torch.cuda.current_stream()
+    sj.set_stream(stream.cuda_stream)
+    clips = torch.empty((C, N_SAMPLES), dtype=torch.float32, device=dev)
+    labels = torch.empty(C, dtype=torch.int32, device=dev)
+    conf = torch.empty(C, dtype=torch.float32, device=dev)
+    score = torch.empty(C, dtype=torch.float32, device=dev)
+    # weak scaling: rank r owns global clips [r*C, (r+1)*C) of the counter-based synthetic set
+    sj.synth_clips_dev(clips, rank * C, C, N_SAMPLES, SEED)
+    if dist is not None:
+        all_labels = torch.empty(world * C, dtype=torch.int32, device=dev)
+        all_score = torch.empty(world * C, dtype=torch.float32, device=dev)
+
+    def step():
+        sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
+        if dist is not None:  # the path's only exchange: final label/score gather, 8 B per clip
+            dist.all_gather_into_tensor(all_labels, labels)
+            dist.all_gather_into_tensor(all_score, score)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = sj.launch_count
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    kms = []
+    with ClockSampler(local_rank) as clk:
+        ev[0].record(stream)
+        for i in range(args.steps):
+            step()
+            ev[i + 1].record(stream)
+        barrier()
+    total_ms = ev[0].elapsed_time(ev[args.steps])
+    launches = sj.launch_count - launches0
+    # kernel-only time, measured live: events bracketing the kernel alone (no gather), same stream
+    for i in range(min(args.steps, 5)):
+        sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
+        kms.append(sj.last_kernel_ms())
+    kernel_ms = statistics.mean(kms)
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * C * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host-pointer C-ABI call, pinned host clips, H2D + kernel + D2H inside the timed region
+    E = min(args.e2e_clips, C)
+    host = torch.empty((E, N_SAMPLES), dtype=torch.float32, pin_memory=True)
+    host.copy_(clips[:E])
+    torch.cuda.synchronize()
+    for _ in range(max(1, min(args.warmup, 2))):
+        sj.infer_batch(host.data_ptr(), n_clips=E, n_samples=N_SAMPLES)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        h_labels, h_conf, h_score = sj.infer_batch(host.data_ptr(), n_clips=E, n_samples=N_SAMPLES)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * E * args.e2e_steps / float(t.item())
+    assert np.array_equal(h_labels, labels[:E].cpu().numpy()), "host-path labels differ from device-path labels"
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
+        traffic = ncu_traffic_bytes_per_clip()
+        cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if args.cpu_baseline else None
+        line = {
+            "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "batched cepstrum features + SVM on 1M synthetic 1 s 16 kHz mono clips, per GPU",
+                       "clips_per_gpu": C, "n_samples": N_SAMPLES, "frames_per_clip": FRAMES_PER_CLIP,
+                       "sharding": "clip-sharded x%d, label/score all-gather (8 B/clip) inside each step" % world,
+                       "l2": "inputs (%.0f GB/GPU) >> L2, no flush needed" % (C * N_SAMPLES * 4 / 1e9),
+                       "timing": "CUDA events on the launching stream, max over ranks"},
+            "frames_per_s": value * FRAMES_PER_CLIP,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": (traffic or {}).get("dram_bytes_per_launch_1M_clips"),
+                         "peak_source": peak_src, "kernel": "cepstrum_kernel<12,true>",
+                         "kernel_ms": kernel_ms, "bytes_per_clip": BYTES_PER_CLIP,
+                         "note": "FFT arithmetic, not HBM, binds this kernel (see DESIGN.md): frac is of the HBM roofline"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": "clips/s", "h2d_bytes_per_step": E * N_SAMPLES * 4,
+                    "d2h_bytes_per_step": E * 12, "clips_per_step": E, "steps": args.e2e_steps,
+                    "api": "scrubjay_infer_batch (host pointers, pinned)"},
+            "gpu_launches": launches,
+            "clocks": clk.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    barrier()
+    sj.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--clips", type=int, default=1000000, help="resident clips per GPU per step")
+    ap.add_argument("--e2e-clips", type=int, default=65536, help="clips per end-to-end step (pinned host buffer)")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--ref-clips-per-thread", type=int, default=32)
+    ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = max(args.warmup, 1)
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank)
+    return run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

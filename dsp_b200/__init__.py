@@ -98,11 +98,16 @@ class ScrubJay:
         self.samplerate = samplerate
 
     def close(self):
-        if getattr(self, "_h", None) and self._h.value:
-            self._L.scrubjay_destroy(self._h)
-            self._h = ctypes.c_void_p()
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self._L.scrubjay_destroy(h)
+            h.value = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # interpreter shutdown
+            pass
 
     def __enter__(self):
         return self
