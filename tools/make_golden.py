@@ -139,5 +139,42 @@ def main():
     print("wrote golden fixtures:", os.listdir(out))
 
 
+
+
+def make_donut_golden():
+    """donut fixtures: (a) the reference's own IIR known-answer vector donut-classifier/_postbutter.txt
+    (first 6000 samples; input = channel 0 of donut-classifier/testing/1060-control.wav / 32768, filter
+    = the commented-out 48 kHz-design coefficient set of classifier.c:323-341); (b) labels, midpoint
+    counts and band sums of the UNMODIFIED reference builds (oracle/_ref) on seeded synthetic clips and
+    on the reference's 1 s / 16 kHz WAVs."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from donut_lib import DonutPort, DonutRef32, DonutRef64
+    from synth_np import synth_clips
+    out = os.path.join(ROOT, "tests", "golden")
+    pcm, sr = read_wav_ch0(os.path.join(REF, "donut-classifier", "testing", "1060-control.wav"))
+    want = np.loadtxt(os.path.join(REF, "donut-classifier", "_postbutter.txt"), max_rows=6000)
+    b48 = [0.00021314, 0., -0.00085255, 0., 0.00127883, 0., -0.00085255, 0., 0.00021314]
+    a48 = [1., -7.12847885, 22.41882266, -40.62891245, 46.40780141, -34.21333503, 15.89913237, -4.25840048, 0.50337536]
+    clips = synth_clips(1000, 96, 16000)
+    r32, r64, p64 = DonutRef32(), DonutRef64(), DonutPort("f64")
+    ref32_labels = np.array([r32.classify(c) for c in clips], np.int32)
+    ref64_nmid = np.array([len(r64.midpoints(c)) for c in clips], np.int32)
+    real = []
+    for name in ("good", "mic-1809bad", "old", "without_filter"):
+        p, _ = read_wav_ch0(os.path.join(REF, "donut-classifier", "try", name + ".wav"))
+        real.append(p[:16000])
+    real = np.array(real)
+    realf = real.astype(np.float32) / 32768.0
+    np.savez_compressed(os.path.join(out, "donut_golden.npz"), kat_pcm=pcm[:6000], kat_sr=sr, kat_out=want,
+                        kat_b=np.array(b48), kat_a=np.array(a48), synth_first=1000, synth_n=96,
+                        ref32_labels=ref32_labels, ref64_nmid=ref64_nmid, real_pcm=real,
+                        real_ref32_labels=np.array([r32.classify(c) for c in realf], np.int32),
+                        real_ref64_iir0=np.array([r64.filter(c, 1000, 3000)[-64:] for c in realf]),
+                        real_ref64_spec=np.array([r64.spectrogram(r64.filter(c, 3000, 7500))[40:44, 30:34] for c in realf]))
+    print("donut golden: ref32 positives %d/96, real labels %s" % (ref32_labels.sum(), [r32.classify(c) for c in realf]))
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    main()
+    make_donut_golden()
