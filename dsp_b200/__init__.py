@@ -58,6 +58,9 @@ def load_library():
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
     L.scrubjay_infer_batch.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_synth_clips_dev.argtypes = [vp, vp, c_long, c_long, c_int, c_uint]
+    L.scrubjay_donut_classify_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
+    L.scrubjay_donut_classify_batch.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
+    L.classify.argtypes = [vp, c_int]
     L.scrubjay_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
     L.scrubjay_host_free.argtypes = [vp]
     L.scrubjay_host_free.restype = None
@@ -149,6 +152,20 @@ class ScrubJay:
     def synth_clips_dev(self, d_out, first_clip, n_clips, n_samples, seed=0x5C2B):
         self._check(self._L.scrubjay_synth_clips_dev(self._h, _ptr(d_out), first_clip, n_clips, n_samples, seed))
 
+    def donut_classify_batch_dev(self, d_clips, n_clips, n_samples, variant, d_labels, d_detail=None):
+        self._check(self._L.scrubjay_donut_classify_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, variant,
+                                                              _ptr(d_labels), _ptr(d_detail)))
+
+    def donut_classify_batch(self, clips, variant):
+        """host clips [n][n_samples] -> (labels int32 [n], detail float32 [n][4])"""
+        clips = np.ascontiguousarray(clips, dtype=np.float32)
+        n, ns = clips.shape
+        labels = np.empty(n, np.int32)
+        detail = np.empty((n, 4), np.float32)
+        self._check(self._L.scrubjay_donut_classify_batch(self._h, clips.ctypes.data, n, ns, variant,
+                                                          labels.ctypes.data, detail.ctypes.data))
+        return labels, detail
+
     # ---- host-pointer entry points (numpy in, numpy out)
     def mfcc_stats(self, samples):
         x = np.ascontiguousarray(samples, dtype=np.float32)
@@ -175,6 +192,16 @@ class ScrubJay:
         self._check(self._L.scrubjay_infer_batch(self._h, _ptr(clips), n_clips, n_samples, labels.ctypes.data,
                                                  conf.ctypes.data, score.ctypes.data, _ptr(feats)))
         return (labels, conf, score, feats) if want_feats else (labels, conf, score)
+
+
+DONUT_DESKTOP_F64 = 0  # donut-classifier/classifier.c constants, double arithmetic
+DONUT_SYNC_F32 = 1     # sync/lib/classifier.cpp constants, float arithmetic
+
+
+def classify(data):
+    """int classify(float *data, int data_size) -- sync/lib/classifier.h:19, same symbol name"""
+    x = np.ascontiguousarray(data, dtype=np.float32)
+    return int(load_library().classify(x.ctypes.data, x.size))
 
 
 def shard_range(n_items, rank, world_size):

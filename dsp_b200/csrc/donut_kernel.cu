@@ -1,0 +1,488 @@
+// donut_kernel.cu -- fused donut classifier for sm_100a: the per-clip body of
+// `int classify(float *data, int data_size)` (sync/lib/classifier.cpp:9-136, float) and of main in
+// donut-classifier/classifier.c:84-198 (double), for a whole batch of clips in one launch.
+//
+// Mapping.  One warp per CTA; a warp owns 16 clips at a time, lane = 2*clip + filter:
+//   phase 1 (IIR, lane-parallel over clips): every lane advances ITS direct-form-II recurrence
+//     (butter_bandpass_filter, classifier.c:420-446) by one spectrogram hop, sequentially in time and
+//     with the reference's exact operation order (separate multiply and add, no FMA), so the filtered
+//     samples are bit-identical to the reference.  With ~10^6 independent clips there is ample
+//     parallelism across clips; a time-parallel scan would change the rounding.  The 256 most recent
+//     outputs of each lane live in a circular shared-memory row.
+//   phase 2 (spectrogram, 4 lanes per frame): rows are taken 8 at a time; 4 lanes share one frame:
+//     mean removal, Tukey window, 256-point real FFT as a 128-point complex FFT split 32 (register
+//     FFT per lane) x 4 (two shuffle butterflies across the lane quad), untangling with the partner
+//     lane, PSD scaling (compute_spectrogram, classifier.c:448-592).
+//     filter 1 (3000-7500 Hz): PSD cells go to a per-CTA scratch [clip][t][bin] (L2/HBM) and a running
+//     min/max of the positive cells is kept; filter 0 (1000-3000 Hz): only "any cell above the dB
+//     threshold" per frame is kept (find_midpoints, classifier.c:657-727), tested against the exact
+//     PSD value whose dB conversion first exceeds the threshold (no logarithm in the loop).
+//   epilogue: blob clustering -> midpoints (classifier.c:748-800), then the three band sums around each
+//     midpoint (sum_intense, :594-655) over dB-normalised cells recomputed from the scratch with the
+//     reference's double-precision log10, and the verdict (:184).
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "donut_kernel.h"
+#include "fft_gen.inc"
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kRow = 264; // row stride in elements: = 8 (mod 32) floats / = 8 (mod 16) doubles => conflict-free 64/128-bit reads
+
+template <typename T> struct V2;
+template <> struct V2<float> { typedef float2 type; };
+template <> struct V2<double> { typedef double2 type; };
+
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
+
+__device__ __forceinline__ void fft32(float2 (&v)[32]) { sj_fft32(v); }
+__device__ __forceinline__ void fft32(double2 (&v)[32]) { sj_fft32d(v); }
+
+// dB value exactly as the reference forms it: (T)(10 * log10((double)s / 1e-12))
+template <typename T> __device__ __forceinline__ T to_db(T s) { return (T)(10.0 * log10((double)s / 1e-12)); }
+
+template <typename T> __host__ __device__ constexpr size_t smem_bytes_t()
+{
+    return sizeof(SjDonutTables<T>) + sizeof(T) * 32 * kRow + sizeof(T) * DN_CLIPS_PER_WARP * DN_MAX_MID + 64;
+}
+
+} // namespace
+
+namespace {
+
+// eight steps of the direct-form-II recurrence with the state in a rotating register file:
+// before step s the value w[n-j] sits in w[(s - j) & 7]
+template <typename T>
+__device__ __forceinline__ void iir8(const T (&x)[8], T (&w)[8], const T (&a)[9], const T (&b)[9], T (&y)[8])
+{
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        T w0 = x[s];
+#pragma unroll
+        for (int j = 1; j < 9; ++j) w0 = sub_rn(w0, mul_rn(a[j], w[(s - j + 8) & 7]));
+        T yy = mul_rn(b[0], w0);
+#pragma unroll
+        for (int j = 2; j < 9; j += 2) yy = add_rn(yy, mul_rn(b[j], w[(s - j + 8) & 7])); // b[odd] == 0
+        w[s] = w0;
+        y[s] = yy;
+    }
+}
+
+template <typename T> struct RowState {
+    T min_s[32], max_s[32];
+    uint32_t flags[32][3];
+    int n_mid[DN_CLIPS_PER_WARP];
+    T mids[DN_CLIPS_PER_WARP][DN_MAX_MID];
+    T mean[32];                 // per-row frame mean, summed sequentially like the reference
+    float2 xbuf[2][16 * 17];    // 16x16 transpose buffers of the exact float FFT (two frames per pass)
+};
+
+__host__ __device__ constexpr int brev4(int x) { return ((x & 1) << 3) | ((x & 2) << 1) | ((x & 4) >> 1) | ((x & 8) >> 3); }
+
+// one butterfly of the reference's float FFT, operation for operation (PlainFFT.cpp:64-71)
+__device__ __forceinline__ void bfly(float2 &lo, float2 &hi, float u1, float u2)
+{
+    const float t1 = sub_rn(mul_rn(u1, hi.x), mul_rn(u2, hi.y));
+    const float t2 = add_rn(mul_rn(u1, hi.y), mul_rn(u2, hi.x));
+    hi.x = sub_rn(lo.x, t1);
+    hi.y = sub_rn(lo.y, t2);
+    lo.x = add_rn(lo.x, t1);
+    lo.y = add_rn(lo.y, t2);
+}
+
+// Float variant: spectrogram column t of all 32 rows with the reference's exact arithmetic
+// (compute_spectrogram, sync/lib/classifier.cpp:307-366 + PlainFFT::Compute).  The butterfly network
+// and its twiddles are data-independent, so running the same butterflies in a different order and in
+// parallel gives bit-identical results.  16 lanes per frame (2 frames per pass, 16 passes): index
+// i = 16*h + r; stages 0-3 act on r inside a lane (lane = h), a 16x16 transpose through shared memory,
+// stages 4-7 act on h inside a lane (lane = r).
+__device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, int pos, int t, int tb,
+                                                             const SjDonutTables<float> *tab, RowState<float> *st,
+                                                             float *scratch, int lane)
+{
+    const int half = lane >> 4, h = lane & 15;
+    float2 *xb = st->xbuf[half];
+    const float U = tab->U, s_thr = tab->s_thr;
+    for (int p = 0; p < 16; ++p) {
+        const int r = 2 * p + half;
+        const float *rowp = rows + r * kRow;
+        const float mean = st->mean[r];
+        float2 v[16];
+        // bit-reversed load: position i = 16h + rr holds sample brev8(i) = 16*brev4(rr) + brev4(h)
+        const int hb = brev4(h);
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const int n = 16 * brev4(rr) + hb;
+            const float x = rowp[(pos + n) & 255];
+            v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
+        }
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const int l1 = 1 << l;
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if ((i & l1) == 0) bfly(v[i], v[i + l1], tab->bourke[l1 - 1 + (i & (l1 - 1))][0], tab->bourke[l1 - 1 + (i & (l1 - 1))][1]);
+        }
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) xb[h * 17 + rr] = v[rr];
+        __syncwarp();
+#pragma unroll
+        for (int hh = 0; hh < 16; ++hh) v[hh] = xb[hh * 17 + h]; // now lane = r (low index bits), register = h
+        __syncwarp();
+#pragma unroll
+        for (int l = 4; l < 8; ++l) {
+            const int l1h = 1 << (l - 4), l1 = 16 << (l - 4);
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if ((i & l1h) == 0) {
+                    const int m = (i & (l1h - 1)) * 16 + h;
+                    bfly(v[i], v[i + l1h], tab->bourke[l1 - 1 + m][0], tab->bourke[l1 - 1 + m][1]);
+                }
+        }
+        // PSD of bins k = 16*hh + lane16 <= 128 (classifier.cpp:349-364) and the per-row bookkeeping
+        const bool is_band = r & 1;
+        float *cell = scratch + (size_t(r >> 1) * tb + t) * DN_BINS;
+        float lmin = INFINITY, lmax = 0.f;
+        bool any = false;
+#pragma unroll
+        for (int hh = 0; hh < 9; ++hh) {
+            const int k = 16 * hh + h;
+            if (hh < 8 || h == 0) {
+                float s = div_rn(add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y)), U);
+                if (k >= 1 && k <= DN_BINS - 2) s = s * 2.0f;
+                if (is_band) {
+                    cell[k] = s;
+                    if (s > 0) { lmin = fminf(lmin, s); lmax = fmaxf(lmax, s); }
+                } else any = any || (s >= s_thr);
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+            lmin = fminf(lmin, __shfl_xor_sync(kFull, lmin, o));
+            lmax = fmaxf(lmax, __shfl_xor_sync(kFull, lmax, o));
+        }
+        const unsigned ballot = __ballot_sync(kFull, any);
+        if (h == 0) {
+            if (is_band) {
+                st->min_s[r] = fminf(st->min_s[r], lmin);
+                st->max_s[r] = fmaxf(st->max_s[r], lmax);
+            } else if ((ballot >> (16 * half)) & 0xFFFFu) st->flags[r][t >> 5] |= 1u << (t & 31);
+        }
+    }
+}
+
+template <typename T, bool ALIGNED>
+__global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
+{
+    typedef typename V2<T>::type T2;
+    extern __shared__ __align__(16) unsigned char smem[];
+    SjDonutTables<T> *tab = reinterpret_cast<SjDonutTables<T> *>(smem);
+    constexpr size_t kTabBytes = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
+    T *rows = reinterpret_cast<T *>(smem + kTabBytes);
+    RowState<T> *st = reinterpret_cast<RowState<T> *>(rows + 32 * kRow);
+    const int lane = threadIdx.x;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
+        for (int i = lane; i < int(sizeof(SjDonutTables<T>) / 4); i += 32) dst[i] = __ldg(src + i);
+    }
+    __syncwarp();
+
+    const int f = lane & 1, ci = lane >> 1, tb = a.tb, n_samples = a.n_samples;
+    T ca[9], cb[9];
+#pragma unroll
+    for (int j = 0; j < 9; ++j) { ca[j] = tab->a[f][j]; cb[j] = tab->b[f][j]; }
+    T *myrow = rows + lane * kRow;
+    T *scratch = reinterpret_cast<T *>(a.scratch) + size_t(blockIdx.x) * DN_CLIPS_PER_WARP * tb * DN_BINS;
+    const int q = lane >> 2, g = lane & 3;
+    const int k2 = ((g & 1) << 1) | (g >> 1); // which quarter of the 128-point spectrum this lane ends up holding
+    const T U = tab->U, s_thr = tab->s_thr;
+
+    for (long base = long(blockIdx.x) * DN_CLIPS_PER_WARP; base < a.n_clips; base += long(gridDim.x) * DN_CLIPS_PER_WARP) {
+        long clip = base + ci;
+        if (clip >= a.n_clips) clip = a.n_clips - 1; // idle lanes shadow the last clip; nothing is written for them
+        const float *src = a.clips + clip * (long)n_samples;
+        T w[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = 0;
+        st->min_s[lane] = (T)INFINITY;
+        st->max_s[lane] = 0;
+        st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
+        int pos = 0, sample = 0;
+        T acc_cur = 0, acc_next = 0; // running sums of the current frame and of the next one (32-sample overlap)
+        __syncwarp();
+
+        for (int t = 0; t < tb; ++t) {
+            // ---- phase 1: advance this lane's IIR by one hop (256 samples for the first frame)
+            const int nnew = t == 0 ? DN_WIN : DN_HOP;
+            for (int i = 0; i < nnew; i += 8) {
+                T x[8], y[8];
+                if (ALIGNED) {
+                    const float4 u0 = __ldg(reinterpret_cast<const float4 *>(src + sample + i));
+                    const float4 u1 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 4));
+                    x[0] = u0.x; x[1] = u0.y; x[2] = u0.z; x[3] = u0.w; x[4] = u1.x; x[5] = u1.y; x[6] = u1.z; x[7] = u1.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
+                }
+                iir8<T>(x, w, ca, cb, y);
+                // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
+                const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    acc_cur = add_rn(acc_cur, y[k]);
+                    if (tail) acc_next = add_rn(acc_next, y[k]);
+                }
+                T *dst = myrow + ((pos + i) & 255);
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) *reinterpret_cast<T2 *>(dst + k) = T2{y[k], y[k + 1]};
+            }
+            sample += nnew;
+            pos = (pos + nnew) & 255; // = offset of the oldest of the 256 most recent samples = frame start
+            st->mean[lane] = div_rn(acc_cur, (T)DN_WIN);
+            acc_cur = acc_next;
+            acc_next = 0;
+            __syncwarp();
+
+            // ---- phase 2: spectrogram column t of all 32 rows
+            if constexpr (sizeof(T) == 4) {
+                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane);
+            } else
+            // double: 8 rows per pass, 4 lanes per row (no bit-exact FFT to follow: FFTW's order is unknown)
+            for (int bq = 0; bq < 4; ++bq) {
+                const int r = 8 * bq + q;
+                const T *rowp = rows + r * kRow;
+                T2 v[32];
+                const T mean = st->mean[r];
+#pragma unroll
+                for (int n = 0; n < 32; ++n) {
+                    v[n] = *reinterpret_cast<const T2 *>(rowp + ((pos + 8 * n + 2 * g) & 255));
+                    const T2 wv = *reinterpret_cast<const T2 *>(&tab->window[8 * n + 2 * g]);
+                    v[n].x = mul_rn(sub_rn(v[n].x, mean), wv.x);
+                    v[n].y = mul_rn(sub_rn(v[n].y, mean), wv.y);
+                }
+                fft32(v); // over n: Y_g[k1] in v[SJ_BREV32(k1)]
+#pragma unroll
+                for (int k1 = 1; k1 < 32; ++k1) {
+                    const T wr = tab->tw128[k1][g][0], wi = tab->tw128[k1][g][1];
+                    T2 &y = v[SJ_BREV32(k1)];
+                    const T yr = y.x * wr - y.y * wi;
+                    y.y = y.x * wi + y.y * wr;
+                    y.x = yr;
+                }
+                // 4-point DFT across the lane quad (g = n mod 4): afterwards this lane holds Z[k1 + 32*k2]
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    T ox = __shfl_xor_sync(kFull, v[i].x, 2), oy = __shfl_xor_sync(kFull, v[i].y, 2);
+                    if (g & 2) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
+                    if (g == 3) { const T tx = v[i].y; v[i].y = -v[i].x; v[i].x = tx; } // times -i
+                    ox = __shfl_xor_sync(kFull, v[i].x, 1); oy = __shfl_xor_sync(kFull, v[i].y, 1);
+                    if (g & 1) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
+                }
+                // untangle the real FFT, PSD scaling, and per-row bookkeeping
+                const bool is_band = r & 1; // filter 1 = 3000-7500 Hz: cells are kept; filter 0: midpoint flags
+                T *cell = scratch + (size_t(r >> 1) * tb + t) * DN_BINS;
+                T lmin = (T)INFINITY, lmax = 0;
+                bool any = false;
+                auto emit = [&](int bin, T x2, T y2) { // (x2, y2) = 2 X[bin]
+                    const T re = (T)0.5 * x2, im = (T)0.5 * y2;
+                    T s = div_rn(add_rn(mul_rn(re, re), mul_rn(im, im)), U);
+                    if (bin >= 1 && bin <= DN_BINS - 2) s = s * (T)2;
+                    if (is_band) {
+                        cell[bin] = s;
+                        if (s > 0) { lmin = s < lmin ? s : lmin; lmax = s > lmax ? s : lmax; }
+                    } else any = any || (s >= s_thr);
+                };
+                auto pair = [&](T2 A, T bx, T by, int k, T &xa, T &ya, T &xb, T &yb) {
+                    // A = Z[k], (bx, by) = Z[128 - k]; returns 2 X[k] and 2 conj-partner for bin 128 - k
+                    const T ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
+                    const T wr = tab->tw256[k][0], wi = tab->tw256[k][1];
+                    const T tx = wr * dy + wi * dx, ty = wi * dy - wr * dx;
+                    xa = ex + tx; ya = ey + ty; xb = ex - tx; yb = ey - ty;
+                };
+#pragma unroll
+                for (int k1 = 1; k1 < 16; ++k1) {
+                    const T2 S = v[SJ_BREV32(32 - k1)];
+                    const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
+                    const int k = k1 + 32 * k2;
+                    T xa, ya, xb, yb;
+                    pair(v[SJ_BREV32(k1)], bx, by, k, xa, ya, xb, yb);
+                    emit(k, xa, ya);
+                    emit(DN_WIN / 2 - k, xb, yb);
+                }
+                {   // k1 = 16: partner Z[16 + 32 (3 - k2)] sits in the mirror lane, same register
+                    const T2 S = v[SJ_BREV32(16)];
+                    const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
+                    T xa, ya, xb, yb;
+                    pair(S, bx, by, 16 + 32 * k2, xa, ya, xb, yb);
+                    emit(16 + 32 * k2, xa, ya);
+                }
+                {   // k1 = 0: bins 0, 32, 64, 96 (and 128 from the k2 = 0 lane)
+                    const T2 S = v[0];
+                    T bx = __shfl_xor_sync(kFull, S.x, 1), by = __shfl_xor_sync(kFull, S.y, 1);
+                    if (g < 2) { bx = S.x; by = S.y; } // k2 = 0 and k2 = 2 are their own partners
+                    T xa, ya, xb, yb;
+                    pair(S, bx, by, 32 * k2, xa, ya, xb, yb);
+                    emit(32 * k2, xa, ya);
+                    if (k2 == 0) emit(DN_WIN / 2, xb, yb);
+                }
+                // combine the quad's partial results; the quad leader updates the row state
+                lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 1)); lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 2));
+                lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 1)); lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 2));
+                const unsigned ballot = __ballot_sync(kFull, any);
+                if (g == 0) {
+                    if (is_band) {
+                        st->min_s[r] = fmin(st->min_s[r], lmin);
+                        st->max_s[r] = fmax(st->max_s[r], lmax);
+                    } else if ((ballot >> (4 * q)) & 0xFu) st->flags[r][t >> 5] |= 1u << (t & 31);
+                }
+            }
+            __syncwarp();
+        }
+
+        // ---- epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
+        const T fs = tab->fs;
+        if (lane < DN_CLIPS_PER_WARP) {
+            const uint32_t *fl = st->flags[2 * lane];
+            const T tol = tab->gap_tol, mind = tab->min_dur;
+            int count = 0, size = 0;
+            T first = 0, last = 0, tsum = 0;
+            for (int j = 0; j <= tb; ++j) {
+                const bool on = j < tb && ((fl[j >> 5] >> (j & 31)) & 1u);
+                const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                const bool joins = on && size > 0 && sub_rn(tj, last) <= tol;
+                if (size > 0 && (!on ? j == tb : !joins)) {
+                    // close the running cluster (also reached at j == tb)
+                    if (sub_rn(last, first) >= mind) {
+                        if (count < DN_MAX_MID) st->mids[lane][count] = div_rn(tsum, (T)size);
+                        ++count;
+                    }
+                    size = 0;
+                }
+                if (on) {
+                    if (size == 0) { first = tj; tsum = 0; }
+                    tsum = add_rn(tsum, tj);
+                    last = tj;
+                    ++size;
+                }
+            }
+            st->n_mid[lane] = count;
+        }
+        __syncwarp();
+
+        // ---- epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip
+        for (int c2 = 0; c2 < DN_CLIPS_PER_WARP; ++c2) {
+            if (base + c2 >= a.n_clips) break;
+            const int nm = st->n_mid[c2];
+            int label = 0;
+            T s_above = 0, s_mid = 0, s_below = 0;
+            if (nm > 0) {
+                const T mn = to_db<T>(st->min_s[2 * c2 + 1]), mx = to_db<T>(st->max_s[2 * c2 + 1]);
+                const T range = sub_rn(mx, mn), lo = tab->lo_norm, hi = tab->hi_norm;
+                const T *scr = scratch + size_t(c2) * tb * DN_BINS;
+                auto box = [&](T lower, T upper, T half, T midpoint) -> T {
+                    // index search exactly as sum_intense (classifier.c:596-640)
+                    int f0 = 0, f1 = DN_BINS - 1, t0 = 0, t1 = tb - 1;
+                    while (f0 < DN_BINS && div_rn(mul_rn((T)f0, fs), (T)DN_WIN) < lower) f0++;
+                    while (f1 >= 0 && div_rn(mul_rn((T)f1, fs), (T)DN_WIN) > upper) f1--;
+                    if (f0 >= DN_BINS) f0 = DN_BINS - 1;
+                    if (f1 < 0) f1 = 0;
+                    if (f0 > f1) { const int x = f0; f0 = f1; f1 = x; }
+                    const T tlo = sub_rn(midpoint, half), thi = add_rn(midpoint, half);
+                    while (t0 < tb && div_rn((T)(t0 * DN_HOP + DN_WIN / 2), fs) < tlo) t0++;
+                    while (t1 >= 0 && div_rn((T)(t1 * DN_HOP + DN_WIN / 2), fs) > thi) t1--;
+                    if (t0 >= tb) t0 = tb - 1;
+                    if (t1 < 0) t1 = 0;
+                    if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
+                    double acc = 0.0;
+                    for (int j = t0; j <= t1; ++j)
+                        for (int i = f0 + lane; i <= f1; i += 32) {
+                            const T s = scr[j * DN_BINS + i];
+                            if (s > 0) {
+                                const T nv = div_rn(sub_rn(to_db<T>(s), mn), range);
+                                if (nv > lo && nv < hi) acc += (double)nv;
+                            }
+                        }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+                    return (T)acc;
+                };
+                const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
+                for (int m = 0; m < cap; ++m) {
+                    const T mp = st->mids[c2][m];
+                    s_above = box((T)5000, (T)7000, (T)0.18, mp);
+                    s_mid = box((T)2500, (T)5000, (T)0.05, mp);
+                    s_below = box((T)500, (T)2500, (T)0.18, mp);
+                    if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
+                }
+            }
+            if (lane == 0) {
+                a.labels[base + c2] = label;
+                if (a.detail) {
+                    float *d = a.detail + (base + c2) * 4;
+                    d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template <typename T> size_t smem_total()
+{
+    return ((sizeof(SjDonutTables<T>) + 15) & ~size_t(15)) + sizeof(T) * 32 * kRow + sizeof(RowState<T>);
+}
+
+} // namespace
+
+cudaError_t sj_donut_setup()
+{
+    cudaError_t e;
+    e = cudaFuncSetAttribute(donut_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<float>());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(donut_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<float>());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(donut_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<double>());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(donut_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<double>());
+}
+
+int sj_donut_grid(int num_sms, bool f64)
+{
+    int per_sm = 0;
+    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true>, 32, smem_total<double>());
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true>, 32, smem_total<float>());
+    if (per_sm < 1) per_sm = 1;
+    return num_sms * per_sm;
+}
+
+size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
+{
+    return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
+}
+
+cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream_t stream)
+{
+    if (a.n_clips <= 0) return cudaSuccess;
+    long groups = (a.n_clips + DN_CLIPS_PER_WARP - 1) / DN_CLIPS_PER_WARP;
+    if (groups < grid) grid = (int)groups;
+    const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
+    if (f64) {
+        if (aligned) donut_kernel<double, true><<<grid, 32, smem_total<double>(), stream>>>(a);
+        else donut_kernel<double, false><<<grid, 32, smem_total<double>(), stream>>>(a);
+    } else {
+        if (aligned) donut_kernel<float, true><<<grid, 32, smem_total<float>(), stream>>>(a);
+        else donut_kernel<float, false><<<grid, 32, smem_total<float>(), stream>>>(a);
+    }
+    return cudaGetLastError();
+}

@@ -1,0 +1,101 @@
+// donut_tables.cpp -- host-side constants of the donut kernel.  The window, U and the dB threshold are
+// computed with the reference's own formulas on the host libm so that they carry the same bits as
+// the reference's run-time values (classifier.c:484-530 / classifier.cpp:263-305).
+#include <math.h>
+#include <string.h>
+
+#include "donut_kernel.h"
+
+void sj_donut_default_params(SjDonutParams *p, int variant)
+{
+    p->gap_tol = 0.05; p->min_dur = 0.15;
+    if (variant == 0) { p->lo_norm = 0.70; p->hi_norm = 0.85; p->mid_thr_db = 45.0; p->thr_mid = 75; p->thr_above = 300; p->thr_below = 100; }
+    else              { p->lo_norm = 0.65; p->hi_norm = 0.80; p->mid_thr_db = 70.0; p->thr_mid = 100; p->thr_above = 200; p->thr_below = 80; }
+}
+
+namespace {
+
+const double kPi = 3.14159265358979323846;
+// scipy.signal.butter(4, [lo, hi], 'band', fs=16000) as hard-coded in classifier.c:342-360,383-401
+const double kB[2][9] = {{0.01020948, 0., -0.04083792, 0., 0.06125688, 0., -0.04083792, 0., 0.01020948},
+                         {0.1362017, 0., -0.5448068, 0., 0.8172102, 0., -0.5448068, 0., 0.1362017}};
+const double kA[2][9] = {{1., -4.56803686, 9.95922498, -13.49912589, 12.43979269, -7.94997696, 3.43760562, -0.92305481, 0.1203896},
+                         {1., 2.60935592, 2.32553038, 1.20262614, 1.11690211, 0.76154474, 0.10005124, -0.0129829, 0.02236815}};
+
+inline float tukey_rise(float n) { return 0.5f * (1.0f + cosf((float)kPi * (-1.0f + 2.0f * n / (0.25f * (257.0f - 1.0f))))); }
+inline float tukey_fall(float n) { return 0.5f * (1.0f + cosf((float)kPi * (-2.0f / 0.25f + 1.0f + 2.0f * n / (0.25f * (257.0f - 1.0f))))); }
+inline double tukey_rise(double n) { return 0.5 * (1 + cos(kPi * (-1 + 2.0 * n / (0.25 * (257 - 1))))); }
+inline double tukey_fall(double n) { return 0.5 * (1 + cos(kPi * (-2.0 / 0.25 + 1 + 2.0 * n / (0.25 * (257 - 1))))); }
+
+inline bool db_exceeds(float s, float thr) { return (float)(10 * log10(s / 1e-12)) > thr; }
+inline bool db_exceeds(double s, double thr) { return 10 * log10(s / 1e-12) > thr; }
+
+template <typename T, typename U> T smallest_exceeding(T thr)
+{
+    // positive IEEE values are ordered like their bit patterns; dB(s) is monotone in s
+    U lo = 1, hi;
+    T top;
+    if (sizeof(T) == 4) { hi = (U)0x7f7fffffu; } else { hi = (U)0x7fefffffffffffffull; }
+    memcpy(&top, &hi, sizeof top);
+    if (!db_exceeds(top, thr)) return top; // never exceeded
+    while (lo < hi) {
+        U mid = lo + (hi - lo) / 2;
+        T v;
+        memcpy(&v, &mid, sizeof v);
+        if (db_exceeds(v, thr)) hi = mid; else lo = mid + 1;
+    }
+    T v;
+    memcpy(&v, &lo, sizeof v);
+    return v;
+}
+
+template <typename T, typename U> void build(SjDonutTables<T> *t, const SjDonutParams &p, int fs)
+{
+    memset(t, 0, sizeof *t);
+    for (int n = 0; n <= 32; n++) t->window[n] = tukey_rise((T)n);
+    for (int n = 33; n <= 257 - 32 - 2; n++) t->window[n] = 1;
+    for (int n = 257 - 32 - 1; n < DN_WIN; n++) t->window[n] = tukey_fall((T)n);
+    T u = 0;
+    for (int i = 0; i < DN_WIN; i++) u += t->window[i] * t->window[i];
+    t->U = u * (T)fs;
+    t->fs = (T)fs;
+    for (int k1 = 0; k1 < 32; k1++)
+        for (int g = 0; g < 4; g++) {
+            double ang = 2 * kPi * (g * k1) / 128.0;
+            t->tw128[k1][g][0] = (T)cos(ang);
+            t->tw128[k1][g][1] = (T)(-sin(ang));
+        }
+    for (int k = 0; k <= 128; k++) {
+        double ang = 2 * kPi * k / 256.0;
+        t->tw256[k][0] = (T)cos(ang);
+        t->tw256[k][1] = (T)(-sin(ang));
+    }
+    {   // the twiddle sequence PlainFFT::Compute generates at run time, in its own float arithmetic:
+        // u <- u * c per butterfly offset, c <- half-angle of c per stage (sqrt evaluated in double)
+        float c1 = -1.0f, c2 = 0.0f;
+        for (int l = 0, l1 = 1; l < 8; ++l, l1 <<= 1) {
+            float u1 = 1.0f, u2 = 0.0f;
+            for (int m = 0; m < l1; ++m) {
+                t->bourke[l1 - 1 + m][0] = (T)u1;
+                t->bourke[l1 - 1 + m][1] = (T)u2;
+                const float z = (u1 * c1) - (u2 * c2);
+                u2 = (u1 * c2) + (u2 * c1);
+                u1 = z;
+            }
+            c2 = (float)sqrt((1.0 - c1) / 2.0);
+            c2 = -c2; // forward transform
+            c1 = (float)sqrt((1.0 + c1) / 2.0);
+        }
+    }
+    for (int w = 0; w < 2; w++)
+        for (int j = 0; j < 9; j++) { t->a[w][j] = (T)kA[w][j]; t->b[w][j] = (T)kB[w][j]; }
+    t->s_thr = smallest_exceeding<T, U>((T)p.mid_thr_db);
+    t->lo_norm = (T)p.lo_norm; t->hi_norm = (T)p.hi_norm;
+    t->gap_tol = (T)p.gap_tol; t->min_dur = (T)p.min_dur;
+    t->thr_mid = (T)p.thr_mid; t->thr_above = (T)p.thr_above; t->thr_below = (T)p.thr_below;
+}
+
+} // namespace
+
+void sj_donut_build_tables_f32(SjDonutTables<float> *t, const SjDonutParams &p, int fs) { build<float, uint32_t>(t, p, fs); }
+void sj_donut_build_tables_f64(SjDonutTables<double> *t, const SjDonutParams &p, int fs) { build<double, uint64_t>(t, p, fs); }

@@ -3,12 +3,14 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
 
 #include "../../include/scrubjay_cuda.h"
 #include "cepstrum_kernel.h"
+#include "donut_kernel.h"
 #include "sj_tables.h"
 
 cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
@@ -48,6 +50,16 @@ struct scrubjay_ctx {
     int chunk_n_samples = 0;
     // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
     float *d_small = nullptr;
+    // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
+    void *d_donut_tables[2] = {nullptr, nullptr};
+    int donut_grid[2] = {0, 0};
+    void *d_donut_scratch = nullptr;
+    size_t donut_scratch_bytes = 0;
+    float *d_donut_clips = nullptr; // host-path staging
+    int32_t *d_donut_labels = nullptr;
+    float *d_donut_detail = nullptr;
+    long donut_stage_clips = 0;
+    int donut_stage_samples = 0;
 };
 
 namespace {
@@ -178,6 +190,8 @@ void scrubjay_destroy(scrubjay_ctx *c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
+    cudaFree(c->d_donut_tables[0]); cudaFree(c->d_donut_tables[1]); cudaFree(c->d_donut_scratch);
+    cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
     delete c->h_tables;
     delete c;
 }
@@ -392,5 +406,135 @@ int scrubjay_debug_mel_dense(unsigned samplerate, float *out)
 /* pinned host memory for callers that want full PCIe rate on the host-pointer entry points */
 int scrubjay_host_alloc(void **p, size_t bytes) { return cudaMallocHost(p, bytes) == cudaSuccess ? SJ_OK : SJ_ENOMEM; }
 void scrubjay_host_free(void *p) { cudaFreeHost(p); }
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// donut path: int classify(float*, int) (sync/lib/classifier.h:19) and its batched forms
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+int donut_prepare(scrubjay_ctx *c, int variant, int n_samples, int *tb_out)
+{
+    if (variant != SJ_DONUT_DESKTOP_F64 && variant != SJ_DONUT_SYNC_F32)
+        return set_err(c, SJ_EINVAL, "unknown donut variant");
+    if (c->samplerate != 16000)
+        return set_err(c, SJ_EINVAL, "donut path: only 16 kHz has filter coefficients (classifier.c:403-407)");
+    const int tb = n_samples >= DN_WIN ? (n_samples - DN_WIN) / DN_HOP + 1 : 0;
+    if (tb < 1) return set_err(c, SJ_EINVAL, "donut path: clip shorter than one 256-sample frame");
+    if (tb > DN_MAX_TB) return set_err(c, SJ_EINVAL, "donut path: clip longer than 21536 samples");
+    const bool f64 = variant == SJ_DONUT_DESKTOP_F64;
+    if (!c->d_donut_tables[variant]) {
+        SJ_CUDA(c, sj_donut_setup());
+        SjDonutParams p;
+        sj_donut_default_params(&p, variant);
+        if (f64) {
+            SjDonutTables<double> t;
+            sj_donut_build_tables_f64(&t, p, 16000);
+            SJ_CUDA(c, cudaMalloc(&c->d_donut_tables[variant], sizeof t));
+            SJ_CUDA(c, cudaMemcpy(c->d_donut_tables[variant], &t, sizeof t, cudaMemcpyHostToDevice));
+        } else {
+            SjDonutTables<float> t;
+            sj_donut_build_tables_f32(&t, p, 16000);
+            SJ_CUDA(c, cudaMalloc(&c->d_donut_tables[variant], sizeof t));
+            SJ_CUDA(c, cudaMemcpy(c->d_donut_tables[variant], &t, sizeof t, cudaMemcpyHostToDevice));
+        }
+        c->donut_grid[variant] = sj_donut_grid(c->num_sms, f64);
+    }
+    const size_t need = sj_donut_scratch_bytes_per_cta(tb, f64) * (size_t)c->donut_grid[variant];
+    if (need > c->donut_scratch_bytes) {
+        SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_donut_scratch);
+        c->d_donut_scratch = nullptr;
+        c->donut_scratch_bytes = 0;
+        SJ_CUDA(c, cudaMalloc(&c->d_donut_scratch, need));
+        c->donut_scratch_bytes = need;
+    }
+    *tb_out = tb;
+    return SJ_OK;
+}
+
+int donut_launch(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant, int tb,
+                 int32_t *d_labels, float *d_detail)
+{
+    SjDonutArgs a;
+    a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tb = tb;
+    a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail;
+    SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    SJ_CUDA(c, sj_launch_donut(a, variant == SJ_DONUT_DESKTOP_F64, c->donut_grid[variant], c->stream));
+    SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->have_timing = true;
+    if (n_clips > 0) c->launches += 1;
+    return SJ_OK;
+}
+
+scrubjay_ctx *g_default_ctx = nullptr;
+
+} // namespace
+
+extern "C" {
+
+int scrubjay_donut_classify_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant,
+                                      int32_t *d_labels, float *d_detail)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    int tb = 0, rc = donut_prepare(c, variant, n_samples, &tb);
+    if (rc != SJ_OK) return rc;
+    return donut_launch(c, d_clips, n_clips, n_samples, variant, tb, d_labels, d_detail);
+}
+
+int scrubjay_donut_classify_batch(scrubjay_ctx *c, const float *clips, long n_clips, int n_samples, int variant,
+                                  int32_t *labels, float *detail)
+{
+    if (!c) return SJ_EINVAL;
+    if (!clips || !labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    int tb = 0, rc = donut_prepare(c, variant, n_samples, &tb);
+    if (rc != SJ_OK) return rc;
+    long chunk = kChunkBytes / ((long)n_samples * 4);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_clips && n_clips > 0) chunk = n_clips;
+    if (c->donut_stage_clips < chunk || c->donut_stage_samples != n_samples) {
+        SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
+        c->d_donut_clips = nullptr; c->d_donut_labels = nullptr; c->d_donut_detail = nullptr;
+        c->donut_stage_clips = 0;
+        SJ_CUDA(c, cudaMalloc(&c->d_donut_clips, (size_t)chunk * n_samples * 4));
+        SJ_CUDA(c, cudaMalloc(&c->d_donut_labels, (size_t)chunk * 4));
+        SJ_CUDA(c, cudaMalloc(&c->d_donut_detail, (size_t)chunk * 16));
+        c->donut_stage_clips = chunk;
+        c->donut_stage_samples = n_samples;
+    }
+    for (long done = 0; done < n_clips; done += chunk) {
+        const long n = n_clips - done < chunk ? n_clips - done : chunk;
+        SJ_CUDA(c, cudaMemcpyAsync(c->d_donut_clips, clips + done * (long)n_samples, (size_t)n * n_samples * 4,
+                                   cudaMemcpyHostToDevice, c->stream));
+        rc = donut_launch(c, c->d_donut_clips, n, n_samples, variant, tb, c->d_donut_labels, c->d_donut_detail);
+        if (rc != SJ_OK) return rc;
+        SJ_CUDA(c, cudaMemcpyAsync(labels + done, c->d_donut_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (detail)
+            SJ_CUDA(c, cudaMemcpyAsync(detail + done * 4, c->d_donut_detail, (size_t)n * 16, cudaMemcpyDeviceToHost, c->stream));
+        SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return SJ_OK;
+}
+
+/* The reference's own entry point, same name and signature (sync/lib/classifier.h:19; called as
+ * classify(buffer, 16000) from sync/sync.cpp:202).  Uses a process-wide context on device
+ * $SCRUBJAY_DEVICE (default 0), created on first use.  Returns 1/0 like the reference, and 0 on any
+ * failure (the reference returns 0 when find_midpoints fails, classifier.cpp:87-91). */
+int classify(float *data, int data_size)
+{
+    if (!g_default_ctx) {
+        const char *env = getenv("SCRUBJAY_DEVICE");
+        if (scrubjay_create(&g_default_ctx, env ? atoi(env) : 0, nullptr, 0, 16000) != SJ_OK) return 0;
+    }
+    int32_t label = 0;
+    if (scrubjay_donut_classify_batch(g_default_ctx, data, 1, data_size, SJ_DONUT_SYNC_F32, &label, nullptr) != SJ_OK)
+        return 0;
+    return (int)label;
+}
 
 } // extern "C"

@@ -97,6 +97,26 @@ SJ_API int scrubjay_predict(scrubjay_ctx *ctx, const float feat[SJ_FEAT_DIM], fl
 SJ_API int scrubjay_infer_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
                          int32_t *labels, float *conf, float *score, float *feats);
 
+/* ---- donut path ---------------------------------------------------------------------------- */
+
+/* variants: which reference binary's constants and precision to follow */
+#define SJ_DONUT_DESKTOP_F64 0 /* donut-classifier/classifier.c: double, band 0.70-0.85, 45 dB, mid<75 above>300 below>100 */
+#define SJ_DONUT_SYNC_F32 1    /* sync/lib/classifier.cpp: float, band 0.65-0.80, 70 dB, mid<100 above>200 below>80 */
+
+/* The reference's own entry point, same name and signature: sync/lib/classifier.h:19, called as
+ * classify(buffer, 16000) at sync/sync.cpp:202.  Host pointer in, 1/0 out (0 also on failure, as the
+ * reference does at classifier.cpp:87-91).  Runs on a process-wide context (device $SCRUBJAY_DEVICE). */
+SJ_API int classify(float *data, int data_size);
+
+/* Batched classify: the per-file body of main (classifier.c:84-198) / classify (classifier.cpp:9-136)
+ * for n_clips clips [n_clips][n_samples] (256 <= n_samples <= 21536).  d_labels[n] int32 0/1;
+ * d_detail (may be NULL) [n][4] = number of midpoints (find_midpoints), then the above / middle / below
+ * band sums (sum_intense) of the last midpoint the reference would have evaluated. */
+SJ_API int scrubjay_donut_classify_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips,
+                                             int n_samples, int variant, int32_t *d_labels, float *d_detail);
+SJ_API int scrubjay_donut_classify_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
+                                         int variant, int32_t *labels, float *detail);
+
 /* Synthetic test/bench audio generated on the device: d_out[n_clips][n_samples], a pure function of
  * (seed, first_clip + clip, sample) -- white noise floor + up to three gated chirps, ~5 % of clips
  * silent or with a silent tail.  Not a reference function; the bench's "data": "synthetic". */

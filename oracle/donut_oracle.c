@@ -124,6 +124,44 @@ static void cfft256(dreal *re, dreal *im, const dreal *wr, const dreal *wi)
     }
 }
 
+/* The float reference transforms with PlainFFT::Compute (sync/lib/PlainFFT.cpp:29-94): radix-2
+ * decimation in time after a bit-reversal permutation, the twiddle (u1, u2) advanced by a float
+ * recurrence per butterfly offset and the per-stage rotation (c1, c2) by half-angle square roots
+ * evaluated in double.  Restated here operation for operation, because the spectrogram's global
+ * minimum (classifier.cpp:34-55) sits on round-off-level cells and is therefore sensitive to the
+ * exact rounding of the transform. */
+static void cfft256_plain_f32(float *re, float *im)
+{
+    const int n = DN_WIN;
+    for (int i = 1, j = 0; i < n; i++) {
+        int bit = n >> 1;
+        for (; j & bit; bit >>= 1) j ^= bit;
+        j ^= bit;
+        if (i < j) { float t = re[i]; re[i] = re[j]; re[j] = t; t = im[i]; im[i] = im[j]; im[j] = t; }
+    }
+    float c1 = -1.0f, c2 = 0.0f;
+    for (int l = 0, l2 = 1; l < 8; l++) {
+        const int l1 = l2;
+        l2 <<= 1;
+        float u1 = 1.0f, u2 = 0.0f;
+        for (int m = 0; m < l1; m++) {
+            for (int i = m; i < n; i += l2) {
+                const int i1 = i + l1;
+                const float t1 = u1 * re[i1] - u2 * im[i1];
+                const float t2 = u1 * im[i1] + u2 * re[i1];
+                re[i1] = re[i] - t1; im[i1] = im[i] - t2;
+                re[i] += t1; im[i] += t2;
+            }
+            const float z = (u1 * c1) - (u2 * c2);
+            u2 = (u1 * c2) + (u2 * c1);
+            u1 = z;
+        }
+        c2 = (float)sqrt((1.0 - c1) / 2.0);
+        c2 = -c2;
+        c1 = (float)sqrt((1.0 + c1) / 2.0);
+    }
+}
+
 /* compute_spectrogram (classifier.c:448-592 / classifier.cpp:221-368).  Sxx is dense [129][tb]
  * (row = frequency bin, like the reference's Sxx[f][t]); returns tb = (n-256)/224+1 (may be <= 0). */
 int sj_oracle_donut_spectrogram(const dreal *sig, int n, int fs, dreal *Sxx, int tb_cap)
@@ -145,7 +183,8 @@ int sj_oracle_donut_spectrogram(const dreal *sig, int n, int fs, dreal *Sxx, int
         const dreal mean = sum / (dreal)DN_WIN;
         for (int i = 0; i < DN_WIN; i++) re[i] -= mean;
         for (int i = 0; i < DN_WIN; i++) re[i] *= window[i];
-        cfft256(re, im, wr, wi);
+        if (sizeof(dreal) == 4) cfft256_plain_f32((float *)re, (float *)im);
+        else cfft256(re, im, wr, wi);
         for (int f = 0; f < DN_BINS; f++) {
             dreal m2 = re[f] * re[f] + im[f] * im[f];
             Sxx[f * tb + t] = m2 / U;

@@ -1,0 +1,151 @@
+"""GPU parity tests of the donut path through the C ABI.
+
+Checkers: the UNMODIFIED reference builds in oracle/_ref (when shipped) and the port
+oracle/donut_oracle.c that is pinned against them (tests/test_donut_oracle_cpu.py).
+
+Parity bar.  The IIR stage is bit-identical to the reference (same operation order, no FMA).  The FFT
+is a different algorithm from PlainFFT/FFTW, so PSD cells differ by rounding (~1e-7 relative in float,
+~1e-15 in double); a cell sitting within that distance of a hard threshold (band 0.65/0.80, 70 dB) can
+flip, which moves a band sum by one cell value (<= 0.85).  Hence:
+  * midpoint counts identical,
+  * band sums within 2.0 absolute (float variant) / 1e-6 relative (double variant),
+  * labels identical on every clip whose sums are not within that slack of a verdict threshold
+    (such clips are counted; the count must stay small)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+pytestmark = pytest.mark.gpu
+
+
+def _ctx():
+    import dsp_b200
+    return dsp_b200.ScrubJay(device=0, samplerate=16000)
+
+
+def _synth(sj, first, n, ns=16000):
+    import torch
+    d = torch.empty((n, ns), dtype=torch.float32, device="cuda")
+    sj.set_stream(torch.cuda.current_stream().cuda_stream)
+    sj.synth_clips_dev(d, first, n, ns)
+    torch.cuda.synchronize()
+    return d
+
+
+def _gpu(sj, d, variant):
+    import torch
+    n, ns = d.shape
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    detail = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    sj.donut_classify_batch_dev(d, n, ns, variant, labels, detail)
+    torch.cuda.synchronize()
+    return labels.cpu().numpy(), detail.cpu().numpy()
+
+
+def _compare(gl, gd, ol, od, variant, sum_tol):
+    thr = {0: (300, 75, 100), 1: (200, 100, 80)}[variant]
+    assert np.array_equal(gd[:, 0], od[:, 0]), "midpoint counts differ on %d clips" % (gd[:, 0] != od[:, 0]).sum()
+    has = od[:, 0] > 0
+    diff = np.abs(gd[:, 1:] - od[:, 1:])
+    assert not has.any() or diff[has].max() <= sum_tol, "band sums differ by %g" % diff[has].max()
+    near = has & (np.abs(od[:, 1:] - np.array(thr)) <= sum_tol).any(axis=1)
+    bad = (gl != ol) & ~near
+    assert not bad.any(), "labels differ on %d clips away from any threshold" % bad.sum()
+    assert near.mean() < 0.05
+    return int((gl != ol).sum()), int(near.sum())
+
+
+def test_f64_variant_matches_port_and_reference():
+    import dsp_b200
+    from donut_lib import DonutPort
+    sj = _ctx()
+    d = _synth(sj, 0, 1024)
+    gl, gd = _gpu(sj, d, dsp_b200.DONUT_DESKTOP_F64)
+    ol, od = DonutPort("f64").classify_batch(d.cpu().numpy(), variant=0)
+    mism, near = _compare(gl, gd, ol, od, 0, sum_tol=1e-3)
+    assert mism == 0
+    assert (od[:, 0] > 0).mean() > 0.5, "workload must exercise the midpoint/band-sum branch"
+
+
+def test_f32_variant_matches_port():
+    import dsp_b200
+    from donut_lib import DonutPort
+    sj = _ctx()
+    d = _synth(sj, 5000, 1024)
+    gl, gd = _gpu(sj, d, dsp_b200.DONUT_SYNC_F32)
+    ol, od = DonutPort("f32").classify_batch(d.cpu().numpy(), variant=1)
+    # same FFT arithmetic as the reference (PlainFFT butterflies): PSD cells are bit-identical, what is
+    # left is the band sum's accumulation order and last-bit differences of log10
+    mism, near = _compare(gl, gd, ol, od, 1, sum_tol=0.01)
+    assert mism == 0
+    assert 0 < ol.sum() < ol.size, "need both verdicts in the sample"
+    print("f32 variant: %d label mismatches, %d clips within slack of a threshold, of %d" % (mism, near, ol.size))
+
+
+def test_f32_variant_matches_unmodified_reference_classify():
+    """labels of the reference's own classify() (oracle/_ref/libdonut_ref_f32.so) on the same bytes"""
+    import dsp_b200
+    from donut_lib import DonutPort, DonutRef32, have_ref
+    if not have_ref():
+        pytest.skip("oracle/_ref not shipped")
+    sj = _ctx()
+    d = _synth(sj, 9000, 256)
+    clips = d.cpu().numpy()
+    gl, gd = _gpu(sj, d, dsp_b200.DONUT_SYNC_F32)
+    r = DonutRef32()
+    ref = np.array([r.classify(c) for c in clips], np.int32)
+    _, od = DonutPort("f32").classify_batch(clips, variant=1)
+    assert np.array_equal(gl, ref), "labels differ from the reference's classify() on %d clips" % (gl != ref).sum()
+    assert 0 < ref.sum() < ref.size
+
+
+def test_golden_real_clips_and_reference_symbol():
+    """the four 1 s / 16 kHz recordings of donut-classifier/try: labels of the reference build, via the
+    reference's own symbol name classify(float*, int)"""
+    import dsp_b200
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "donut_golden.npz"))
+    real = g["real_pcm"].astype(np.float32) / 32768.0
+    got = [dsp_b200.classify(c) for c in real]
+    assert got == g["real_ref32_labels"].tolist()
+    sj = _ctx()
+    labels, detail = sj.donut_classify_batch(real, dsp_b200.DONUT_SYNC_F32)
+    assert labels.tolist() == got
+
+
+@pytest.mark.parametrize("ns", [256, 479, 480, 3001, 7200, 16000, 20480])
+def test_ragged_lengths(ns):
+    import dsp_b200
+    from donut_lib import DonutPort
+    rng = np.random.default_rng(ns)
+    t = np.arange(ns) / 16000.0
+    clips = (0.2 * rng.uniform(-1, 1, (19, ns)) + 0.3 * np.sin(2 * np.pi * 2000 * t)[None, :]).astype(np.float32)
+    sj = _ctx()
+    for variant, prec, tol in ((0, "f64", 1e-3), (1, "f32", 0.01)):
+        gl, gd = sj.donut_classify_batch(clips, variant)
+        ol, od = DonutPort(prec).classify_batch(clips, variant)
+        _compare(gl, gd, ol, od, variant, tol)
+
+
+def test_too_short_and_silent():
+    import dsp_b200
+    sj = _ctx()
+    with pytest.raises(dsp_b200.ScrubJayError):
+        sj.donut_classify_batch(np.zeros((2, 100), np.float32), 1)
+    labels, detail = sj.donut_classify_batch(np.zeros((3, 16000), np.float32), 1)
+    assert labels.tolist() == [0, 0, 0] and detail[:, 0].tolist() == [0, 0, 0]
+
+
+def test_permutation_equivariance_large():
+    import torch
+    import dsp_b200
+    sj = _ctx()
+    n = 8192 + 5
+    d = _synth(sj, 777, n)
+    perm = torch.randperm(n, device="cuda")
+    a = _gpu(sj, d, dsp_b200.DONUT_SYNC_F32)
+    b = _gpu(sj, d[perm].contiguous(), dsp_b200.DONUT_SYNC_F32)
+    p = perm.cpu().numpy()
+    assert np.array_equal(a[0][p], b[0]) and np.array_equal(a[1][p], b[1])
