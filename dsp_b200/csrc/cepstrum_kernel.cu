@@ -21,7 +21,9 @@
 //   * after the last hop: mean/std -> Scaler -> 55-SV RBF -> Platt probability (libsvm's
 //     multiclass_probability for k = 2) -> label, confidence, decision value.
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "fft_gen.inc"
 #include "sj_tables.h"
@@ -33,7 +35,7 @@ constexpr int kTStride = 33;                 // padded row stride of the transpo
 constexpr int kTFloats = 32 * kTStride;      // 1056 floats: transpose plane, then |X| bins 0..1024
 constexpr int kLogFloats = 64;               // 40 log-energies (+pad)
 
-__host__ __device__ constexpr int p_floats(int maxseg) { return ((2 * 32 * maxseg + 2) + 3) & ~3; }
+__host__ __device__ constexpr int p_floats(int maxseg) { return ((32 * maxseg + 2) + 3) & ~3; }
 __host__ __device__ constexpr int warp_floats(int maxseg)
 {
     return 2 * SJ_HOP + kTFloats + kLogFloats + p_floats(maxseg);
@@ -76,7 +78,7 @@ __device__ __forceinline__ void fence_proxy_async()
 __device__ __forceinline__ float fast_sqrt(float x)
 {
     float r;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); // one MUFU.SQRT; |X| below 1e-19 flushes to 0
     return r;
 }
 
@@ -114,7 +116,10 @@ __device__ void platt_pair(double s, double A, double B, double p[2])
 
 namespace {
 
-static_assert(sizeof(SjTables) % 16 == 0, "tables are staged with 16-byte copies");
+// only the per-frame tables are staged in shared memory; the SVM weights (used once per clip) are read
+// through L1/L2 from the global copy, which leaves room for more resident warps
+constexpr size_t kHotBytes = offsetof(SjTables, sv_off);
+static_assert(kHotBytes % 16 == 0, "tables are staged with 16-byte copies");
 constexpr unsigned kFull = 0xffffffffu;
 
 struct SvmOut { int label; float conf, score; };
@@ -144,13 +149,13 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
     return r;
 }
 
-template <int WARPS, bool TMA>
+template <int WARPS, bool TMA, int MELCH>
 __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstrumArgs a, const int maxseg)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     SjTables *T = reinterpret_cast<SjTables *>(smem_raw);
-    size_t off = (sizeof(SjTables) + 127) & ~size_t(127);
+    size_t off = (kHotBytes + 127) & ~size_t(127);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + off) + 2 * warp;
     off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
     float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * warp_floats(maxseg);
@@ -161,13 +166,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     {   // stage the tables
         const int4 *src = reinterpret_cast<const int4 *>(a.tables);
         int4 *dst = reinterpret_cast<int4 *>(T);
-        for (int i = tid; i < int(sizeof(SjTables) / 16); i += WARPS * 32) dst[i] = __ldg(src + i);
+        for (int i = tid; i < int(kHotBytes / 16); i += WARPS * 32) dst[i] = __ldg(src + i);
     }
     if (lane == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
-        P[2 * 32 * maxseg] = 0.f;
-        P[2 * 32 * maxseg + 1] = 0.f;
+        P[32 * maxseg] = 0.f; // the combine lists' zero slot
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -287,22 +291,28 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             }
             __syncwarp();
 
-            // ---- sparse Slaney mel sums over this lane's bin chunk
+            // ---- sparse Slaney mel sums over this lane's bin chunk: two running sums (filter f, f+1);
+            // where f steps, the finished sum goes to the lane's next slot and the f+1 sum moves down
             {
                 float lo = 0.f, hi = 0.f;
-                float2 *Pw = reinterpret_cast<float2 *>(P) + lane * maxseg;
-                for (int i = 0; i < mel_ch; ++i) {
+                float *Pw = P + lane * maxseg;
+                auto bin = [&](int i) {
                     const float av = tb[mel_base + i];
                     const SjPair w = T->melw[i][lane];
-                    if (__float_as_uint(w.x) & 0x80000000u) {
-                        *Pw++ = make_float2(lo, hi);
-                        lo = 0.f;
-                        hi = 0.f;
-                    }
-                    lo = fmaf(fabsf(w.x), av, lo);
-                    hi = fmaf(w.y, av, hi);
+                    const bool step = __float_as_int(w.x) < 0;
+                    if (step) *Pw = lo;
+                    Pw += step;
+                    lo = fmaf(fabsf(w.x), av, step ? hi : lo);
+                    hi = fmaf(w.y, av, step ? 0.f : hi);
+                };
+                if (MELCH > 0) {
+#pragma unroll
+                    for (int i = 0; i < MELCH; ++i) bin(i);
+                } else {
+                    for (int i = 0; i < mel_ch; ++i) bin(i);
                 }
-                *Pw = make_float2(lo, hi);
+                Pw[0] = lo;
+                Pw[1] = hi;
             }
             __syncwarp();
             {
@@ -311,16 +321,26 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                     e0 += P[T->comb[e][lane]];
                     e1 += P[T->comb[e][lane + 32]];
                 }
-                // aubio fvec_log10: log10(max(x, 2e-42))
-                lg[lane] = log10f(fmaxf(e0, 2.e-42f));
-                if (lane < SJ_NFILT - 32) lg[lane + 32] = log10f(fmaxf(e1, 2.e-42f));
+                // aubio fvec_log10: log10(max(x, 2e-42)); lane m holds band m, lanes 0..7 also band m+32
+                e0 = log10f(fmaxf(e0, 2.e-42f));
+                e1 = log10f(fmaxf(e1, 2.e-42f));
+                // DCT-II symmetry D[c][39-m] = (-1)^c D[c][m]: fold the 40 log energies into 20 sums
+                // (even c) and 20 differences (odd c)
+                const float far0 = __shfl_sync(kFull, e0, (39 - lane) & 31); // band 39-m for m = 8..19
+                const float far1 = __shfl_sync(kFull, e1, (7 - lane) & 31);  // band 39-m for m = 0..7
+                const float far = lane < 8 ? far1 : far0;
+                if (lane < SJ_NCOEF) {
+                    lg[lane] = e0 + far;
+                    lg[SJ_NCOEF + lane] = e0 - far;
+                }
             }
             __syncwarp();
             // ---- DCT-II (first 20 rows) and the reference's double accumulators
             {
                 float acc = 0.f;
-#pragma unroll 8
-                for (int m = 0; m < SJ_NFILT; ++m) acc = fmaf(T->dct[m][lane], lg[m], acc);
+                const float *eo = lg + (lane & 1) * SJ_NCOEF;
+#pragma unroll
+                for (int m = 0; m < SJ_NFILT / 2; ++m) acc = fmaf(T->dct[m][lane], eo[m], acc);
                 const double dv = (double)acc;
                 sum += dv;
                 sq += dv * dv;
@@ -337,12 +357,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 a.feats[clip * SJ_FEAT + lane] = fm;
                 a.feats[clip * SJ_FEAT + SJ_NCOEF + lane] = fs;
             }
-            lg[lane] = (fm - T->sv_off[lane]) * T->sv_scale[lane];
-            lg[lane + SJ_NCOEF] = (fs - T->sv_off[lane + SJ_NCOEF]) * T->sv_scale[lane + SJ_NCOEF];
+            const SjTables *G = a.tables;
+            lg[lane] = (fm - __ldg(&G->sv_off[lane])) * __ldg(&G->sv_scale[lane]);
+            lg[lane + SJ_NCOEF] = (fs - __ldg(&G->sv_off[lane + SJ_NCOEF])) * __ldg(&G->sv_scale[lane + SJ_NCOEF]);
         }
         __syncwarp();
         if (a.do_svm) {
-            const SvmOut r = svm_eval(T, lg, lane);
+            const SvmOut r = svm_eval(a.tables, lg, lane);
             if (lane == 0) {
                 if (a.labels) a.labels[clip] = r.label;
                 if (a.conf) a.conf[clip] = r.conf;
@@ -373,38 +394,50 @@ __global__ void __launch_bounds__(256) svm_kernel(const float *feats, long n, co
     }
 }
 
-constexpr int kWarps = 12;
-
-size_t smem_bytes(int maxseg)
+template <int WARPS> size_t smem_bytes(int maxseg)
 {
-    size_t off = (sizeof(SjTables) + 127) & ~size_t(127);
-    off += (size_t(kWarps) * 2 * 8 + 127) & ~size_t(127);
-    return off + size_t(kWarps) * warp_floats(maxseg) * sizeof(float);
+    size_t off = (kHotBytes + 127) & ~size_t(127);
+    off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
+    return off + size_t(WARPS) * warp_floats(maxseg) * sizeof(float);
+}
+
+constexpr int kWarps = 12;  // 14 fit too (128 registers) but measured no faster: the kernel is issue/LSU bound
+constexpr int kMelFast = 27; // bins per lane of the 16 kHz Slaney bank: fully unrolled mel loop
+
+template <bool TMA, int MELCH> cudaError_t setup_one(int maxseg)
+{
+    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, MELCH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem_bytes<kWarps>(maxseg));
+}
+
+template <bool TMA, int MELCH>
+cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
+{
+    long ctas = (a.n_clips + kWarps - 1) / kWarps;
+    if (ctas > num_sms) ctas = num_sms;
+    cepstrum_kernel<kWarps, TMA, MELCH><<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg), stream>>>(a, maxseg);
+    return cudaGetLastError();
 }
 
 } // namespace
 
 cudaError_t sj_cepstrum_setup(int maxseg)
 {
-    const int bytes = (int)smem_bytes(maxseg);
-    cudaError_t e = cudaFuncSetAttribute(cepstrum_kernel<kWarps, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    cudaError_t e = setup_one<true, kMelFast>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, kMelFast>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, 0>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, 0>(maxseg);
+    return e;
 }
 
-cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
+cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, int maxseg, int mel_ch, int num_sms, cudaStream_t stream)
 {
     if (a.n_clips <= 0) return cudaSuccess;
-    long ctas = (a.n_clips + kWarps - 1) / kWarps;
-    if (ctas > num_sms) ctas = num_sms;
-    const size_t bytes = smem_bytes(maxseg);
     // the bulk-copy path needs 16-byte aligned hop addresses and sizes
     const bool tma = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
-    if (tma)
-        cepstrum_kernel<kWarps, true><<<(unsigned)ctas, kWarps * 32, bytes, stream>>>(a, maxseg);
-    else
-        cepstrum_kernel<kWarps, false><<<(unsigned)ctas, kWarps * 32, bytes, stream>>>(a, maxseg);
-    return cudaGetLastError();
+    if (mel_ch == kMelFast)
+        return tma ? launch_one<true, kMelFast>(a, maxseg, num_sms, stream) : launch_one<false, kMelFast>(a, maxseg, num_sms, stream);
+    return tma ? launch_one<true, 0>(a, maxseg, num_sms, stream) : launch_one<false, 0>(a, maxseg, num_sms, stream);
 }
 
 cudaError_t sj_launch_svm(const float *feats, long n, const SjTables *tables, int32_t *labels, float *conf,

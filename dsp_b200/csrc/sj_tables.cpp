@@ -97,41 +97,44 @@ static int build_mel(SjTables *t, unsigned samplerate, char *err)
     if (lo + 32 * ch > 1056) lo = 1056 - 32 * ch; // stay inside the per-warp magnitude buffer
     t->mel_lo = lo;
     t->mel_ch = ch;
-    // segments: per lane, maximal runs of bins with the same f (bins without a filter join the run)
-    struct Seg { int f; };
-    std::vector<std::vector<Seg>> segs(32);
-    int maxseg = 1;
+    // Per lane: walk the chunk; f (lowest filter touching the bin) never decreases and steps by one at
+    // a triangle edge.  The lane keeps two running sums (filter f, filter f+1); at a step the sum of
+    // filter f is complete for this lane and is stored, the f+1 sum becomes the new "lower" sum.
+    // Slot s of lane L therefore holds the lane's partial energy of filter first_f[L] + s.
+    std::vector<int> first_f(32, -1), last_f(32, -1);
+    int maxslot = 2;
     for (int L = 0; L < 32; ++L) {
         int cur = -1;
         for (int i = 0; i < ch; ++i) {
             int k = lo + L * ch + i;
             float a = 0.f, b = 0.f;
-            bool flush = false;
+            bool step = false;
             if (k < SJ_NBINS && f0[k] >= 0) {
                 a = 0.5f * wlo[k];
                 b = 0.5f * whi[k];
-                if (cur < 0) { cur = f0[k]; segs[L].push_back({cur}); }
-                else if (f0[k] != cur) { cur = f0[k]; segs[L].push_back({cur}); flush = true; }
+                if (cur < 0) { cur = f0[k]; first_f[L] = cur; }
+                else if (f0[k] != cur) {
+                    if (f0[k] != cur + 1) return fail(err, "filterbank edges skip a filter inside a bin chunk (unsupported samplerate)");
+                    cur = f0[k];
+                    step = true;
+                }
             }
-            // flush flag = sign bit of w_lo (weights are >= 0); -0.0f works for a zero weight
-            t->melw[i][L].x = flush ? -a : a;
+            // step flag = sign bit of w_lo (weights are >= 0); -0.0f works for a zero weight
+            t->melw[i][L].x = step ? -a : a;
             t->melw[i][L].y = b;
-            if (flush && a == 0.f) { uint32_t bits = 0x80000000u; memcpy(&t->melw[i][L].x, &bits, 4); }
+            if (step && a == 0.f) { uint32_t bits = 0x80000000u; memcpy(&t->melw[i][L].x, &bits, 4); }
         }
-        if ((int)segs[L].size() > maxseg) maxseg = (int)segs[L].size();
+        last_f[L] = cur;
+        if (cur >= 0 && cur - first_f[L] + 2 > maxslot) maxslot = cur - first_f[L] + 2;
     }
-    t->mel_maxseg = maxseg;
-    // combine lists.  Partial (L, s) lives at float index 2*(L*maxseg + s) (+1 for the f+1 part);
-    // the zero slot is float index 2*32*maxseg.
-    const int zero_slot = 2 * 32 * maxseg;
-    if (zero_slot + 2 > 65535) return fail(err, "too many mel segments");
+    t->mel_maxseg = maxslot;
+    // combine lists: partial (L, s) lives at float index L*maxslot + s; the zero slot is 32*maxslot
+    const int zero_slot = 32 * maxslot;
     std::vector<std::vector<int>> lists(64);
-    for (int L = 0; L < 32; ++L)
-        for (size_t s = 0; s < segs[L].size(); ++s) {
-            int f = segs[L][s].f, base = 2 * (L * maxseg + (int)s);
-            lists[f].push_back(base);
-            if (f + 1 < SJ_NFILT) lists[f + 1].push_back(base + 1);
-        }
+    for (int L = 0; L < 32; ++L) {
+        if (first_f[L] < 0) continue;
+        for (int f = first_f[L]; f <= last_f[L] + 1 && f < SJ_NFILT; ++f) lists[f].push_back(L * maxslot + (f - first_f[L]));
+    }
     size_t ncomb = 1;
     for (int m = 0; m < SJ_NFILT; ++m) if (lists[m].size() > ncomb) ncomb = lists[m].size();
     if (ncomb > SJ_MAX_COMB) return fail(err, "mel combine list too long");

@@ -26,11 +26,13 @@ struct SjTables {
     // sparse Slaney bank, chunked: lane L owns bins mel_lo + L*mel_ch + i, i < mel_ch.
     // melw[i][L] = (w_lo, w_hi): weights of that bin for filters f and f+1 where f is the lowest
     // filter touching the bin; weights already carry the 0.5 that the untangling step leaves out.
-    // The sign bit of w_lo is set on the first bin of a new segment (f changed): flush partials.
+    // The sign bit of w_lo is set on the first bin where f has stepped to f+1: the running sum of the
+    // old f is stored to the lane's next slot and the f+1 sum becomes the lower sum.
+    // mel_maxseg = slots per lane (filters a lane's chunk can touch).
     SjPair melw[SJ_MAX_CH][32];
     int32_t mel_lo, mel_ch, mel_maxseg, mel_ncomb;
     // combine lists: energy of filter m = sum_e P[comb[e][m]] over e < mel_ncomb, P = flat float
-    // array of per-(lane,segment) partial pairs; unused entries point at a zero slot.
+    // array [lane][slot] of per-lane partial energies; unused entries point at a zero slot.
     uint16_t comb[SJ_MAX_COMB][64];
     // orthonormal DCT-II, transposed: dct[m][c], c < 20 (padded to 32)
     float dct[SJ_NFILT][32];
