@@ -22,7 +22,7 @@ WIN_SIZE = 2048
 HOP_SIZE = 1024
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libscrubjay_cuda.so")
+LIB_PATH = os.environ.get("SCRUBJAY_LIB") or os.path.join(_HERE, "libscrubjay_cuda.so")  # override: A/B builds of the same ABI
 DEFAULT_MODEL = os.path.join(_HERE, "data", "scrubjay_svm.bin")
 
 _lib = None

@@ -11,9 +11,10 @@
 //     h+1 is in flight while frame h is computed.  Each sample is used by two frames (50 % overlap)
 //     but read from HBM once.
 //   * frame = [hop h-1 | hop h] * periodic Hann -> 2048-point real FFT done as a 1024-point complex
-//     FFT split 32 x 32: a 32-point FFT in registers per lane, twiddle, ONE transpose through
-//     shared memory, a second 32-point register FFT, then the real-FFT untangling with the partner
-//     bin fetched by one warp shuffle.  aubio's fvec_shift (half swap) only flips the sign of odd
+//     FFT split 32 x 32: a 32-point FFT in registers per lane, ONE transpose through shared memory
+//     (scalar stores, 128-bit loads), a second 32-point register FFT whose first butterfly stage
+//     absorbs the step-2 twiddles, then the real-FFT untangling with the partner bin fetched by one
+//     warp shuffle.  The upper window half is 1 - w, so only 1024 window values are read.  aubio's fvec_shift (half swap) only flips the sign of odd
 //     bins and is dropped because only |X| is used.
 //   * |X| (bins mel_lo..) -> sparse Slaney mel sums (<= 2 filters per bin, lane-contiguous chunks
 //     with an odd stride = conflict-free) -> log10 with aubio's 2e-42 floor -> 20x40 DCT -> the
@@ -31,11 +32,15 @@
 
 namespace {
 
-constexpr int kTStride = 33;                 // padded row stride of the transpose buffer
-constexpr int kTFloats = 32 * kTStride;      // 1056 floats: transpose plane, then |X| bins 0..1024
+constexpr int kTStride = 36;                 // row stride of the transpose plane: 144 B => conflict-free 128-bit row reads
+constexpr int kTFloats = 32 * kTStride;      // 1152 floats: transpose plane, then |X| bins 0..1024
 constexpr int kLogFloats = 64;               // 40 log-energies (+pad)
 
-__host__ __device__ constexpr int p_floats(int maxseg) { return ((32 * maxseg + 2) + 3) & ~3; }
+// mel partial sums: generic layout 32*maxseg, fast layout 32*SJ_MEL_FAST_SLOTS, + the zero slot
+__host__ __device__ constexpr int p_floats(int maxseg)
+{
+    return (32 * (maxseg > SJ_MEL_FAST_SLOTS ? maxseg : SJ_MEL_FAST_SLOTS) + 4) & ~3;
+}
 __host__ __device__ constexpr int warp_floats(int maxseg)
 {
     return 2 * SJ_HOP + kTFloats + kLogFloats + p_floats(maxseg);
@@ -74,6 +79,17 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 __device__ __forceinline__ void fence_proxy_async()
 {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// log10(max(x, 2e-42)) (aubio fvec_log10 / SAFE_LOG10) on one MUFU.LG2: values below 1e-30 (the floor
+// itself is subnormal) are scaled by 2^64 first.  Absolute error <= 2 ulp of log2(x) * 0.30103.
+__device__ __forceinline__ float floor_log10(float x)
+{
+    x = fmaxf(x, 2.e-42f);
+    const bool tiny = x < 1e-30f;
+    const float y = tiny ? x * 18446744073709551616.f : x;
+    float l;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(y));
+    return fmaf(l, 0.30102999566398120f, tiny ? -19.265919722494797f : 0.f);
 }
 __device__ __forceinline__ float fast_sqrt(float x)
 {
@@ -149,7 +165,9 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
     return r;
 }
 
-template <int WARPS, bool TMA, int MELCH>
+// FAST: the 16 kHz layout (28-bin lane chunks, static flush slots, <= 5 combine entries, mirror bins of
+// the first 4 untangling rows skipped); otherwise every mel parameter is read from the tables.
+template <int WARPS, bool TMA, bool FAST>
 __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstrumArgs a, const int maxseg)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -171,9 +189,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     if (lane == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
-        P[32 * maxseg] = 0.f; // the combine lists' zero slot
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = lane; i < p_floats(maxseg); i += 32) P[i] = 0.f; // includes the combine lists' zero slot
     __syncthreads();
 
     const int n_samples = a.n_samples;
@@ -181,9 +199,14 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const int last_valid = n_samples - (F - 1) * SJ_HOP;
     const long stride = long(gridDim.x) * WARPS;
     long clip = long(blockIdx.x) * WARPS + warp;
-    const float2 *win2 = reinterpret_cast<const float2 *>(T->window);
-    const int mel_ch = T->mel_ch, mel_base = T->mel_lo + lane * T->mel_ch, ncomb = T->mel_ncomb;
+    const float2 *win2 = reinterpret_cast<const float2 *>(T->window) + lane;
+    const float4 *tw4 = reinterpret_cast<const float4 *>(T->tw4) + lane;
+    const float4 *tp4 = reinterpret_cast<const float4 *>(T->tp4) + lane;
+    const float4 *mw4 = reinterpret_cast<const float4 *>(T->melw4) + lane;
+    const int mel_ch = FAST ? SJ_MEL_FAST_CH : T->mel_ch, ncomb = FAST ? 5 : T->mel_ncomb;
+    const float4 *X4 = reinterpret_cast<const float4 *>(tb + T->mel_lo + lane * mel_ch);
     const int partner = (32 - lane) & 31;
+    constexpr int PSKIP = FAST ? 4 : 0;
 
     // fetch hop `h` of clip `c` into ring slot `slot`
     auto fetch = [&](long c, int h, int slot) {
@@ -210,33 +233,29 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
         for (int t = 0; t < F; ++t, ++q) {
             const int slot = q & 1;
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
-            const float2 *cur = reinterpret_cast<const float2 *>(wbase + slot * SJ_HOP);
-            const float2 *prv = reinterpret_cast<const float2 *>(wbase + (slot ^ 1) * SJ_HOP);
+            float *curf = wbase + slot * SJ_HOP;
+            if (t == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
+                for (int i = last_valid + lane; i < SJ_HOP; i += 32) curf[i] = 0.f;
+                __syncwarp();
+            }
+            const float2 *cur = reinterpret_cast<const float2 *>(curf) + lane;
+            const float2 *prv = reinterpret_cast<const float2 *>(wbase + (slot ^ 1) * SJ_HOP) + lane;
             float2 v[32];
-            // ---- frame = [hop t-1 | hop t] * hann, packed z[m] = (y[2m], y[2m+1]), m = 32*m1 + lane
+            // ---- frame = [hop t-1 | hop t] * hann, packed z[m] = (y[2m], y[2m+1]), m = 32*m1 + lane;
+            // hann[i + 1024] = 1 - hann[i]
             if (t == 0) {
 #pragma unroll
-                for (int m1 = 0; m1 < 16; ++m1) v[m1] = make_float2(0.f, 0.f);
+                for (int m1 = 0; m1 < 16; ++m1) {
+                    const float2 w = win2[32 * m1], c = cur[32 * m1];
+                    v[m1] = make_float2(0.f, 0.f);
+                    v[m1 + 16] = make_float2(fmaf(-c.x, w.x, c.x), fmaf(-c.y, w.y, c.y));
+                }
             } else {
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
-                    float2 s = prv[32 * m1 + lane], w = win2[32 * m1 + lane];
+                    const float2 w = win2[32 * m1], c = cur[32 * m1], s = prv[32 * m1];
                     v[m1] = make_float2(s.x * w.x, s.y * w.y);
-                }
-            }
-            const int valid = (t == F - 1) ? last_valid : SJ_HOP;
-            if (valid == SJ_HOP) {
-#pragma unroll
-                for (int m1 = 16; m1 < 32; ++m1) {
-                    float2 s = cur[32 * (m1 - 16) + lane], w = win2[32 * m1 + lane];
-                    v[m1] = make_float2(s.x * w.x, s.y * w.y);
-                }
-            } else {
-#pragma unroll
-                for (int m1 = 16; m1 < 32; ++m1) {
-                    const int i0 = 64 * (m1 - 16) + 2 * lane;
-                    float2 s = cur[32 * (m1 - 16) + lane], w = win2[32 * m1 + lane];
-                    v[m1] = make_float2(i0 < valid ? s.x * w.x : 0.f, i0 + 1 < valid ? s.y * w.y : 0.f);
+                    v[m1 + 16] = make_float2(fmaf(-c.x, w.x, c.x), fmaf(-c.y, w.y, c.y));
                 }
             }
             __syncwarp();
@@ -248,42 +267,52 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             }
             // ---- 1024-point complex FFT, 32 x 32 split
             sj_fft32(v); // over m1: Y[k1] in v[SJ_BREV32(k1)]
-#pragma unroll
-            for (int k1 = 1; k1 < 32; ++k1) {
-                const SjPair w = T->tw32[k1][lane];
-                float2 &y = v[SJ_BREV32(k1)];
-                const float yr = y.x * w.x - y.y * w.y;
-                y.y = fmaf(y.x, w.y, y.y * w.x);
-                y.x = yr;
-            }
             // transpose (lane = m2, reg = k1) -> (lane = k1, reg = m2), one float plane at a time
+            {
+                const float4 *row = reinterpret_cast<const float4 *>(tb + lane * kTStride);
 #pragma unroll
-            for (int k1 = 0; k1 < 32; ++k1) tb[k1 * kTStride + lane] = v[SJ_BREV32(k1)].x;
-            __syncwarp();
+                for (int k1 = 0; k1 < 32; ++k1) tb[k1 * kTStride + lane] = v[SJ_BREV32(k1)].x;
+                __syncwarp();
+                float4 r[8];
 #pragma unroll
-            for (int m2 = 0; m2 < 32; ++m2) v[m2].x = tb[lane * kTStride + m2];
-            __syncwarp();
+                for (int g = 0; g < 8; ++g) r[g] = row[g];
+                __syncwarp();
 #pragma unroll
-            for (int k1 = 0; k1 < 32; ++k1) tb[k1 * kTStride + lane] = v[SJ_BREV32(k1)].y;
-            __syncwarp();
+                for (int k1 = 0; k1 < 32; ++k1) tb[k1 * kTStride + lane] = v[SJ_BREV32(k1)].y;
+                __syncwarp();
 #pragma unroll
-            for (int m2 = 0; m2 < 32; ++m2) v[m2].y = tb[lane * kTStride + m2];
-            __syncwarp();
-            sj_fft32(v); // over m2: Z[lane + 32*k2] in v[SJ_BREV32(k2)]
+                for (int g = 0; g < 8; ++g) {
+                    const float4 i4 = row[g];
+                    v[4 * g + 0] = make_float2(r[g].x, i4.x);
+                    v[4 * g + 1] = make_float2(r[g].y, i4.y);
+                    v[4 * g + 2] = make_float2(r[g].z, i4.z);
+                    v[4 * g + 3] = make_float2(r[g].w, i4.w);
+                }
+                __syncwarp();
+            }
+            sj_fft32tw(v, tw4); // twiddles W^(lane*m2), then over m2: Z[lane + 32*k2] in v[SJ_BREV32(k2)]
 
             // ---- untangle the real FFT: bins k = lane + 32 j and 1024 - k, j < 16 (values are 2|X|)
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float2 A = v[SJ_BREV32(j)];
-                const float2 S = v[SJ_BREV32(31 - j)];
-                float bx = __shfl_sync(kFull, S.x, partner), by = __shfl_sync(kFull, S.y, partner);
-                if (lane == 0) { bx = v[SJ_BREV32((32 - j) & 31)].x; by = v[SJ_BREV32((32 - j) & 31)].y; }
-                const float ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
-                const SjPair w = T->twpost[lane + 32 * j];
-                const float tx = fmaf(w.x, dy, w.y * dx), ty = fmaf(w.y, dy, -w.x * dx);
-                const float xa = ex + tx, ya = ey + ty, xb = ex - tx, yb = ey - ty;
-                tb[lane + 32 * j] = fast_sqrt(fmaf(xa, xa, ya * ya));
-                tb[1024 - lane - 32 * j] = fast_sqrt(fmaf(xb, xb, yb * yb));
+            for (int jj = 0; jj < 8; ++jj) {
+                const float4 w4 = tp4[32 * jj];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int j = 2 * jj + h;
+                    const float wx = h ? w4.z : w4.x, wy = h ? w4.w : w4.y;
+                    const float2 A = v[SJ_BREV32(j)];
+                    const float2 S = v[SJ_BREV32(31 - j)];
+                    float bx = __shfl_sync(kFull, S.x, partner), by = __shfl_sync(kFull, S.y, partner);
+                    if (lane == 0) { bx = v[SJ_BREV32((32 - j) & 31)].x; by = v[SJ_BREV32((32 - j) & 31)].y; }
+                    const float ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
+                    const float tx = fmaf(wx, dy, wy * dx), ty = fmaf(wy, dy, -wx * dx);
+                    const float xa = ex + tx, ya = ey + ty;
+                    tb[lane + 32 * j] = fast_sqrt(fmaf(xa, xa, ya * ya));
+                    if (j >= PSKIP) { // the mirrors of the first rows lie above the filterbank
+                        const float xb = ex - tx, yb = ey - ty;
+                        tb[1024 - lane - 32 * j] = fast_sqrt(fmaf(xb, xb, yb * yb));
+                    }
+                }
             }
             if (lane == 0) {
                 const float2 c = v[SJ_BREV32(16)];
@@ -292,38 +321,67 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             __syncwarp();
 
             // ---- sparse Slaney mel sums over this lane's bin chunk: two running sums (filter f, f+1);
-            // where f steps, the finished sum goes to the lane's next slot and the f+1 sum moves down
+            // where f steps, the finished sum is flushed and the f+1 sum moves down
             {
                 float lo = 0.f, hi = 0.f;
-                float *Pw = P + lane * maxseg;
-                auto bin = [&](int i) {
-                    const float av = tb[mel_base + i];
-                    const SjPair w = T->melw[i][lane];
-                    const bool step = __float_as_int(w.x) < 0;
-                    if (step) *Pw = lo;
-                    Pw += step;
-                    lo = fmaf(fabsf(w.x), av, step ? hi : lo);
-                    hi = fmaf(w.y, av, step ? 0.f : hi);
-                };
-                if (MELCH > 0) {
+                if (FAST) {
+                    float *Pl = P + lane;
 #pragma unroll
-                    for (int i = 0; i < MELCH; ++i) bin(i);
+                    for (int b = 0; b < SJ_MEL_FAST_CH / 4; ++b) {
+                        const float4 x = X4[b], wa = mw4[64 * b], wb = mw4[64 * b + 32];
+                        auto bin = [&](int i, float av, float wx, float wy) {
+                            const bool step = __float_as_int(wx) < 0;
+                            if (step) Pl[(i >> 3) * 32] = lo;
+                            lo = fmaf(fabsf(wx), av, step ? hi : lo);
+                            hi = fmaf(wy, av, step ? 0.f : hi);
+                        };
+                        bin(4 * b + 0, x.x, wa.x, wa.y);
+                        bin(4 * b + 1, x.y, wa.z, wa.w);
+                        bin(4 * b + 2, x.z, wb.x, wb.y);
+                        bin(4 * b + 3, x.w, wb.z, wb.w);
+                    }
+                    Pl[(SJ_MEL_FAST_SLOTS - 2) * 32] = lo;
+                    Pl[(SJ_MEL_FAST_SLOTS - 1) * 32] = hi;
                 } else {
-                    for (int i = 0; i < mel_ch; ++i) bin(i);
+                    float *Pw = P + lane * maxseg;
+                    for (int b = 0; b < mel_ch / 4; ++b) {
+                        const float4 x = X4[b], wa = mw4[64 * b], wb = mw4[64 * b + 32];
+                        auto bin = [&](float av, float wx, float wy) {
+                            const bool step = __float_as_int(wx) < 0;
+                            if (step) *Pw = lo;
+                            Pw += step;
+                            lo = fmaf(fabsf(wx), av, step ? hi : lo);
+                            hi = fmaf(wy, av, step ? 0.f : hi);
+                        };
+                        bin(x.x, wa.x, wa.y);
+                        bin(x.y, wa.z, wa.w);
+                        bin(x.z, wb.x, wb.y);
+                        bin(x.w, wb.z, wb.w);
+                    }
+                    Pw[0] = lo;
+                    Pw[1] = hi;
                 }
-                Pw[0] = lo;
-                Pw[1] = hi;
             }
             __syncwarp();
             {
                 float e0 = 0.f, e1 = 0.f;
-                for (int e = 0; e < ncomb; ++e) {
-                    e0 += P[T->comb[e][lane]];
-                    e1 += P[T->comb[e][lane + 32]];
+                if (FAST) {
+#pragma unroll
+                    for (int e = 0; e < 5; ++e) {
+                        const uint32_t c = T->comb2[e][lane];
+                        e0 += P[c & 0xffffu];
+                        e1 += P[c >> 16];
+                    }
+                } else {
+                    for (int e = 0; e < ncomb; ++e) {
+                        const uint32_t c = T->comb2[e][lane];
+                        e0 += P[c & 0xffffu];
+                        e1 += P[c >> 16];
+                    }
                 }
                 // aubio fvec_log10: log10(max(x, 2e-42)); lane m holds band m, lanes 0..7 also band m+32
-                e0 = log10f(fmaxf(e0, 2.e-42f));
-                e1 = log10f(fmaxf(e1, 2.e-42f));
+                e0 = floor_log10(e0);
+                e1 = floor_log10(e1);
                 // DCT-II symmetry D[c][39-m] = (-1)^c D[c][m]: fold the 40 log energies into 20 sums
                 // (even c) and 20 differences (odd c)
                 const float far0 = __shfl_sync(kFull, e0, (39 - lane) & 31); // band 39-m for m = 8..19
@@ -401,21 +459,23 @@ template <int WARPS> size_t smem_bytes(int maxseg)
     return off + size_t(WARPS) * warp_floats(maxseg) * sizeof(float);
 }
 
-constexpr int kWarps = 12;  // 14 fit too (128 registers) but measured no faster: the kernel is issue/LSU bound
-constexpr int kMelFast = 27; // bins per lane of the 16 kHz Slaney bank: fully unrolled mel loop
+#ifndef SJ_WARPS
+#define SJ_WARPS 12
+#endif
+constexpr int kWarps = SJ_WARPS;
 
-template <bool TMA, int MELCH> cudaError_t setup_one(int maxseg)
+template <bool TMA, bool FAST> cudaError_t setup_one(int maxseg)
 {
-    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, MELCH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem_bytes<kWarps>(maxseg));
 }
 
-template <bool TMA, int MELCH>
+template <bool TMA, bool FAST>
 cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
 {
     long ctas = (a.n_clips + kWarps - 1) / kWarps;
     if (ctas > num_sms) ctas = num_sms;
-    cepstrum_kernel<kWarps, TMA, MELCH><<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg), stream>>>(a, maxseg);
+    cepstrum_kernel<kWarps, TMA, FAST><<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg), stream>>>(a, maxseg);
     return cudaGetLastError();
 }
 
@@ -423,21 +483,24 @@ cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStr
 
 cudaError_t sj_cepstrum_setup(int maxseg)
 {
-    cudaError_t e = setup_one<true, kMelFast>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, kMelFast>(maxseg);
-    if (e == cudaSuccess) e = setup_one<true, 0>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, 0>(maxseg);
+    cudaError_t e = setup_one<true, true>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, true>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, false>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, false>(maxseg);
     return e;
 }
 
-cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, int maxseg, int mel_ch, int num_sms, cudaStream_t stream)
+cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
 {
     if (a.n_clips <= 0) return cudaSuccess;
     // the bulk-copy path needs 16-byte aligned hop addresses and sizes
     const bool tma = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
-    if (mel_ch == kMelFast)
-        return tma ? launch_one<true, kMelFast>(a, maxseg, num_sms, stream) : launch_one<false, kMelFast>(a, maxseg, num_sms, stream);
-    return tma ? launch_one<true, 0>(a, maxseg, num_sms, stream) : launch_one<false, 0>(a, maxseg, num_sms, stream);
+    // the fast instantiation hard-codes the 16 kHz layout: 28-bin chunks, static flush slots, <= 5
+    // combine entries, the mirrors of the first 4 untangling rows above the bank
+    const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4;
+    const int maxseg = h->mel_maxseg;
+    if (fast) return tma ? launch_one<true, true>(a, maxseg, num_sms, stream) : launch_one<false, true>(a, maxseg, num_sms, stream);
+    return tma ? launch_one<true, false>(a, maxseg, num_sms, stream) : launch_one<false, false>(a, maxseg, num_sms, stream);
 }
 
 cudaError_t sj_launch_svm(const float *feats, long n, const SjTables *tables, int32_t *labels, float *conf,

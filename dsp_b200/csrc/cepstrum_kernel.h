@@ -17,9 +17,9 @@ struct SjCepstrumArgs {
     int do_svm;           // 0: features only
 };
 
-// Enqueues the kernel on `stream`.  `mel_maxseg` is tables->mel_maxseg (host copy), `num_sms` the
-// SM count of the device.  Returns the cudaError_t of the launch.
-cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, int mel_maxseg, int mel_ch, int num_sms, cudaStream_t stream);
+// Enqueues the kernel on `stream`.  `host_tables` is the host copy of a.tables (selects the mel layout),
+// `num_sms` the SM count of the device.  Returns the cudaError_t of the launch.
+cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *host_tables, int num_sms, cudaStream_t stream);
 // one-time attribute set-up (max dynamic shared memory); returns cudaError_t
 cudaError_t sj_cepstrum_setup(int mel_maxseg);
 // batched standalone SVM: feats [n][40] -> labels/conf/score

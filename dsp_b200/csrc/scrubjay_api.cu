@@ -123,7 +123,7 @@ int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, 
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
     a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
     if (timed) SJ_CUDA(c, cudaEventRecord(c->ev0, stream));
-    SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables->mel_maxseg, c->h_tables->mel_ch, c->num_sms, stream));
+    SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables, c->num_sms, stream));
     if (timed) { SJ_CUDA(c, cudaEventRecord(c->ev1, stream)); c->have_timing = true; }
     c->launches += 1;
     return SJ_OK;
@@ -378,28 +378,7 @@ int scrubjay_debug_mel_dense(unsigned samplerate, float *out)
     char err[256];
     int rc = sj_build_tables(t, nullptr, 0, samplerate, err);
     if (rc) { snprintf(g_create_err, sizeof g_create_err, "%s", err); delete t; return SJ_EINVAL; }
-    memset(out, 0, sizeof(float) * SJ_NFILT * SJ_NBINS);
-    // replay the kernel's walk: per lane two running sums (slot, slot+1); a step flag advances the slot
-    const int maxslot = t->mel_maxseg, zero_slot = 32 * maxslot;
-    for (int L = 0; L < 32; ++L) {
-        int slot = 0;
-        for (int i = 0; i < t->mel_ch; ++i) {
-            const int k = t->mel_lo + L * t->mel_ch + i;
-            uint32_t bits;
-            memcpy(&bits, &t->melw[i][L].x, 4);
-            if (bits & 0x80000000u) ++slot;
-            const float wlo = fabsf(t->melw[i][L].x), whi = t->melw[i][L].y;
-            const int base = L * maxslot + slot;
-            if (k >= SJ_NBINS) continue;
-            for (int m = 0; m < SJ_NFILT; ++m)
-                for (int e = 0; e < t->mel_ncomb; ++e) {
-                    const int idx = t->comb[e][m];
-                    if (idx == zero_slot) continue;
-                    if (idx == base && wlo != 0.f) out[m * SJ_NBINS + k] += wlo;
-                    if (idx == base + 1 && whi != 0.f) out[m * SJ_NBINS + k] += whi;
-                }
-        }
-    }
+    sj_replay_mel_dense(t, out);
     delete t;
     return SJ_OK;
 }

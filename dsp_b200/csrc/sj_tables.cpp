@@ -91,22 +91,31 @@ static int build_mel(SjTables *t, unsigned samplerate, char *err)
         if ((lo == 0 && wlo[0] != 0.f) || hi == SJ_NBINS - 1)
             return fail(err, "filterbank touches the DC/Nyquist bin (unsupported samplerate)");
     }
-    int ch = (hi - lo + 1 + 31) / 32;
-    if ((ch & 1) == 0) ++ch; // odd stride => conflict-free shared-memory reads across lanes
+    // the untangling step can skip the mirror bin 1024-k of the first `pskip` rows (k = lane + 32 j,
+    // j < pskip) when those mirrors lie above the bank's support
+    int pskip = 0;
+    while (pskip < 16 && 1024 - 32 * pskip - 31 > hi) ++pskip;
+    t->mel_pskip = pskip;
+    // chunk layout: lane L owns bins base + L*ch + i; base and ch multiples of 4 (128-bit loads)
+    const int base = lo & ~3;
+    int ch = (hi - base + 1 + 31) / 32;
+    ch = (ch + 3) & ~3;
     if (ch > SJ_MAX_CH) return fail(err, "filterbank support too wide");
-    if (lo + 32 * ch > 1056) lo = 1056 - 32 * ch; // stay inside the per-warp magnitude buffer
-    t->mel_lo = lo;
-    t->mel_ch = ch;
+    bool fast = ch <= SJ_MEL_FAST_CH;
+    if (fast) ch = SJ_MEL_FAST_CH;
+    int lo_al = base;
+    if (lo_al + 32 * ch > 1152) lo_al = (1152 - 32 * ch) & ~3; // stay inside the per-warp magnitude buffer
     // Per lane: walk the chunk; f (lowest filter touching the bin) never decreases and steps by one at
     // a triangle edge.  The lane keeps two running sums (filter f, filter f+1); at a step the sum of
-    // filter f is complete for this lane and is stored, the f+1 sum becomes the new "lower" sum.
-    // Slot s of lane L therefore holds the lane's partial energy of filter first_f[L] + s.
+    // filter f is complete for this lane and is flushed, the f+1 sum becomes the new "lower" sum.
     std::vector<int> first_f(32, -1), last_f(32, -1);
+    std::vector<std::vector<int>> step_at(32); // chunk positions of the steps of each lane
     int maxslot = 2;
+    memset(t->melw4, 0, sizeof t->melw4);
     for (int L = 0; L < 32; ++L) {
         int cur = -1;
         for (int i = 0; i < ch; ++i) {
-            int k = lo + L * ch + i;
+            int k = lo_al + L * ch + i;
             float a = 0.f, b = 0.f;
             bool step = false;
             if (k < SJ_NBINS && f0[k] >= 0) {
@@ -117,32 +126,98 @@ static int build_mel(SjTables *t, unsigned samplerate, char *err)
                     if (f0[k] != cur + 1) return fail(err, "filterbank edges skip a filter inside a bin chunk (unsupported samplerate)");
                     cur = f0[k];
                     step = true;
+                    step_at[L].push_back(i);
                 }
             }
             // step flag = sign bit of w_lo (weights are >= 0); -0.0f works for a zero weight
-            t->melw[i][L].x = step ? -a : a;
-            t->melw[i][L].y = b;
-            if (step && a == 0.f) { uint32_t bits = 0x80000000u; memcpy(&t->melw[i][L].x, &bits, 4); }
+            float ax = step ? -a : a;
+            if (step && a == 0.f) { uint32_t bits = 0x80000000u; memcpy(&ax, &bits, 4); }
+            SjQuad &q = t->melw4[i >> 1][L];
+            if (i & 1) { q.z = ax; q.w = b; } else { q.x = ax; q.y = b; }
         }
         last_f[L] = cur;
         if (cur >= 0 && cur - first_f[L] + 2 > maxslot) maxslot = cur - first_f[L] + 2;
+        for (size_t s = 1; s < step_at[L].size(); ++s)
+            if (step_at[L][s] / 8 == step_at[L][s - 1] / 8) fast = false; // two steps in one group of 8 bins
     }
+    t->mel_lo = lo_al;
+    t->mel_ch = ch;
     t->mel_maxseg = maxslot;
-    // combine lists: partial (L, s) lives at float index L*maxslot + s; the zero slot is 32*maxslot
-    const int zero_slot = 32 * maxslot;
+    t->mel_fast = fast ? 1 : 0;
+    // combine lists.  Slot s (in flush order) of lane L holds the lane's partial energy of filter
+    // first_f[L] + s; its position in P depends on the layout.
+    const int zero_slot = fast ? 32 * SJ_MEL_FAST_SLOTS : 32 * maxslot;
     std::vector<std::vector<int>> lists(64);
     for (int L = 0; L < 32; ++L) {
         if (first_f[L] < 0) continue;
-        for (int f = first_f[L]; f <= last_f[L] + 1 && f < SJ_NFILT; ++f) lists[f].push_back(L * maxslot + (f - first_f[L]));
+        const int nstep = (int)step_at[L].size();
+        for (int s = 0; s <= nstep + 1; ++s) {
+            const int f = first_f[L] + s;
+            if (f >= SJ_NFILT) continue;
+            int idx;
+            if (!fast) idx = L * maxslot + s;
+            else if (s < nstep) idx = (step_at[L][s] / 8) * 32 + L;
+            else idx = (SJ_MEL_FAST_SLOTS - 2 + (s - nstep)) * 32 + L;
+            lists[f].push_back(idx);
+        }
     }
     size_t ncomb = 1;
     for (int m = 0; m < SJ_NFILT; ++m) if (lists[m].size() > ncomb) ncomb = lists[m].size();
     if (ncomb > SJ_MAX_COMB) return fail(err, "mel combine list too long");
     t->mel_ncomb = (int)ncomb;
     for (size_t e = 0; e < SJ_MAX_COMB; ++e)
-        for (int m = 0; m < 64; ++m)
-            t->comb[e][m] = (uint16_t)((m < SJ_NFILT && e < lists[m].size()) ? lists[m][e] : zero_slot);
+        for (int m = 0; m < 32; ++m) {
+            const uint32_t i0 = (uint32_t)((m < SJ_NFILT && e < lists[m].size()) ? lists[m][e] : zero_slot);
+            const uint32_t i1 = (uint32_t)((m + 32 < SJ_NFILT && e < lists[m + 32].size()) ? lists[m + 32][e] : zero_slot);
+            t->comb2[e][m] = i0 | (i1 << 16);
+        }
     return 0;
+}
+
+// Replays the kernel's mel walk symbolically and expands the chunked sparse tables back to a dense
+// [40][1025] bank (diagnostic; tests compare it with an independent construction).
+void sj_replay_mel_dense(const SjTables *t, float *out)
+{
+    memset(out, 0, sizeof(float) * SJ_NFILT * SJ_NBINS);
+    const bool fast = t->mel_fast != 0;
+    const int nP = (fast ? 32 * SJ_MEL_FAST_SLOTS : 32 * t->mel_maxseg) + 1;
+    typedef std::vector<std::pair<int, float>> Terms; // (bin, weight)
+    std::vector<Terms> P(nP);
+    for (int L = 0; L < 32; ++L) {
+        Terms lo, hi;
+        int slot = 0;
+        for (int i = 0; i < t->mel_ch; ++i) {
+            const SjQuad &q = t->melw4[i >> 1][L];
+            const float wx = (i & 1) ? q.z : q.x, wy = (i & 1) ? q.w : q.y;
+            uint32_t bits;
+            memcpy(&bits, &wx, 4);
+            if (bits & 0x80000000u) {
+                const int idx = fast ? (i / 8) * 32 + L : L * t->mel_maxseg + slot;
+                P[idx] = lo;
+                ++slot;
+                lo = hi;
+                hi.clear();
+            }
+            const int k = t->mel_lo + L * t->mel_ch + i;
+            lo.push_back({k, fabsf(wx)});
+            hi.push_back({k, wy});
+        }
+        if (fast) {
+            P[(SJ_MEL_FAST_SLOTS - 2) * 32 + L] = lo;
+            P[(SJ_MEL_FAST_SLOTS - 1) * 32 + L] = hi;
+        } else {
+            P[L * t->mel_maxseg + slot] = lo;
+            if (slot + 1 < t->mel_maxseg) P[L * t->mel_maxseg + slot + 1] = hi;
+        }
+    }
+    for (int m = 0; m < SJ_NFILT; ++m)
+        for (int e = 0; e < t->mel_ncomb; ++e) {
+            const uint32_t c = t->comb2[e][m & 31];
+            const int idx = (m < 32) ? (int)(c & 0xffffu) : (int)(c >> 16);
+            if (idx >= nP - 1) continue;
+            for (auto &bw : P[idx])
+                if (bw.first < SJ_NBINS && bw.second != 0.f) out[(size_t)m * SJ_NBINS + bw.first] += bw.second;
+        }
 }
 
 struct SjsvHeader {
@@ -155,18 +230,23 @@ int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned s
     memset(t, 0, sizeof(*t));
     if (samplerate == 0) return fail(err, "samplerate must be > 0");
     const double two_pi = 6.283185307179586476925286766559;
-    for (int i = 0; i < SJ_WIN; ++i) t->window[i] = (float)(0.5 * (1.0 - cos(two_pi * i / SJ_WIN)));
-    for (int a = 0; a < 32; ++a)
+    for (int i = 0; i < SJ_HOP; ++i) t->window[i] = (float)(0.5 * (1.0 - cos(two_pi * i / SJ_WIN)));
+    for (int a = 0; a < 16; ++a)
         for (int b = 0; b < 32; ++b) {
-            double ang = two_pi * (double)(a * b) / 1024.0;
-            t->tw32[a][b].x = (float)cos(ang);
-            t->tw32[a][b].y = (float)(-sin(ang));
+            double a0 = two_pi * (double)(a * b) / 1024.0, a1 = two_pi * (double)((a + 16) * b) / 1024.0;
+            t->tw4[a][b].x = (float)cos(a0);
+            t->tw4[a][b].y = (float)(-sin(a0));
+            t->tw4[a][b].z = (float)cos(a1);
+            t->tw4[a][b].w = (float)(-sin(a1));
         }
-    for (int k = 0; k < 512; ++k) {
-        double ang = two_pi * k / 2048.0;
-        t->twpost[k].x = (float)cos(ang);
-        t->twpost[k].y = (float)(-sin(ang));
-    }
+    for (int jj = 0; jj < 8; ++jj)
+        for (int b = 0; b < 32; ++b) {
+            double a0 = two_pi * (b + 64 * jj) / 2048.0, a1 = two_pi * (b + 64 * jj + 32) / 2048.0;
+            t->tp4[jj][b].x = (float)cos(a0);
+            t->tp4[jj][b].y = (float)(-sin(a0));
+            t->tp4[jj][b].z = (float)cos(a1);
+            t->tp4[jj][b].w = (float)(-sin(a1));
+        }
     if (build_mel(t, samplerate, err)) return -1;
     // aubio mfcc.c: orthonormal DCT-II over the 40 log energies, first 20 rows kept
     const double pi = two_pi / 2;

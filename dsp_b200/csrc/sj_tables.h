@@ -1,6 +1,7 @@
 // sj_tables.h -- constant tables of the cepstrum kernel, built once per context on the host
 // (sj_tables.cpp) and copied to device global memory; every CTA stages them into shared memory.
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 
 #define SJ_WIN 2048
@@ -10,30 +11,41 @@
 #define SJ_NCOEF 20
 #define SJ_FEAT 40
 #define SJ_MAX_SV 64  /* support vectors are padded to 64 (the shipped model has 55) */
-#define SJ_MAX_CH 33  /* max bins per lane chunk in the sparse mel stage */
+#define SJ_MAX_CH 32  /* max bins per lane chunk in the sparse mel stage */
 #define SJ_MAX_COMB 16
 
 struct SjPair { float x, y; };
+struct SjQuad { float x, y, z, w; };
+
+#define SJ_MEL_FAST_CH 28   /* bins per lane of the fast mel path (multiple of 4) */
+#define SJ_MEL_FAST_SLOTS 6 /* fast path: one flush slot per aligned group of 8 bins (4) + the two final sums */
 
 // Everything the kernel reads besides the clips.  Plain POD, identical layout on host and device.
+// The per-frame ("hot") tables come first; the kernel stages everything before sv_off into shared memory.
 struct SjTables {
-    // aubio "hanningz" window, w[i] = 0.5(1-cos(2 pi i/2048))  (pvoc.c / mathutils.c new_aubio_window)
-    float window[SJ_WIN];
-    // step-2 twiddles of the 32x32 split of the 1024-point complex FFT: W_1024^(k1*m2) at [k1][m2]
-    SjPair tw32[32][32];
-    // real-FFT untangling twiddles W_2048^k, k = 0..511
-    SjPair twpost[512];
-    // sparse Slaney bank, chunked: lane L owns bins mel_lo + L*mel_ch + i, i < mel_ch.
-    // melw[i][L] = (w_lo, w_hi): weights of that bin for filters f and f+1 where f is the lowest
-    // filter touching the bin; weights already carry the 0.5 that the untangling step leaves out.
-    // The sign bit of w_lo is set on the first bin where f has stepped to f+1: the running sum of the
-    // old f is stored to the lane's next slot and the f+1 sum becomes the lower sum.
-    // mel_maxseg = slots per lane (filters a lane's chunk can touch).
-    SjPair melw[SJ_MAX_CH][32];
+    // lower half of aubio's "hanningz" window, w[i] = 0.5(1-cos(2 pi i/2048)), i < 1024 (pvoc.c /
+    // mathutils.c new_aubio_window); the upper half is 1 - w[i].
+    float window[SJ_HOP];
+    // step-2 twiddles of the 32x32 split of the 1024-point complex FFT, paired for the merged first
+    // butterfly stage: tw4[n][lane] = (W^(n*lane), W^((n+16)*lane)), W = exp(-2 pi i/1024)
+    SjQuad tw4[16][32];
+    // real-FFT untangling twiddles W_2048^k for k = lane + 64 jj and k + 32
+    SjQuad tp4[8][32];
+    // sparse Slaney bank, chunked: lane L owns bins mel_lo + L*mel_ch + i, i < mel_ch (mel_lo and
+    // mel_ch are multiples of 4).  melw4[g][L] = (w_lo, w_hi) of bins 2g and 2g+1 of the chunk: weights
+    // for filters f and f+1 where f is the lowest filter touching the bin; they carry the 0.5 that the
+    // untangling step leaves out.  The sign bit of w_lo is set on the first bin where f has stepped to
+    // f+1: the running sum of the old f is flushed and the f+1 sum becomes the lower sum.
+    //   fast layout (mel_fast = 1, mel_ch = 28): the flush of a step at chunk bin i goes to slot i/8 (a
+    //     chunk never holds two steps in one aligned group of 8 bins), the two final sums to slots 4, 5;
+    //     partial (slot, L) lives at P[slot*32 + L].
+    //   generic layout: slots are filled in order, partial (L, s) at P[L*mel_maxseg + s].
+    SjQuad melw4[SJ_MAX_CH / 2][32];
     int32_t mel_lo, mel_ch, mel_maxseg, mel_ncomb;
-    // combine lists: energy of filter m = sum_e P[comb[e][m]] over e < mel_ncomb, P = flat float
-    // array [lane][slot] of per-lane partial energies; unused entries point at a zero slot.
-    uint16_t comb[SJ_MAX_COMB][64];
+    int32_t mel_fast, mel_pskip, pad_a, pad_b;
+    // combine lists: energy of filter m = sum_e P[comb[e][m]] over e < mel_ncomb; unused entries point
+    // at a zero slot.  comb2[e][lane] packs the entries of filters lane (low 16 bits) and lane+32 (high).
+    uint32_t comb2[SJ_MAX_COMB][32];
     // orthonormal DCT-II, transposed: dct[m][c], c < 20 (padded to 32)
     float dct[SJ_NFILT][32];
     // SVM (ONNX ai.onnx.ml Scaler + SVMClassifier attributes)
@@ -48,3 +60,5 @@ struct SjTables {
 int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned samplerate, char *err);
 // dense [40][1025] Slaney bank (aubio filterbank_mel.c semantics), used by the builder and by tests
 void sj_dense_slaney(float *fb /*[40][1025]*/, unsigned samplerate);
+// dense [40][1025] bank recovered by replaying the kernel's sparse walk over the built tables (weights carry 0.5)
+void sj_replay_mel_dense(const SjTables *t, float *out);
