@@ -140,6 +140,16 @@ constexpr unsigned kFull = 0xffffffffu;
 
 struct SvmOut { int label; float conf, score; };
 
+// 0.5 cos(2 pi m1/32) and 0.5 sin(2 pi m1/32), m1 < 16 (window rebuilt in registers, see the kernel)
+__device__ constexpr float kWinC[16] = {0.5f, 0.49039264020161522f, 0.46193976625564337f, 0.41573480615127262f,
+                                        0.35355339059327379f, 0.27778511650980114f, 0.19134171618254492f, 0.09754516100806417f,
+                                        0.f, -0.09754516100806417f, -0.19134171618254492f, -0.27778511650980114f,
+                                        -0.35355339059327379f, -0.41573480615127262f, -0.46193976625564337f, -0.49039264020161522f};
+__device__ constexpr float kWinS[16] = {0.f, 0.09754516100806417f, 0.19134171618254492f, 0.27778511650980114f,
+                                        0.35355339059327379f, 0.41573480615127262f, 0.46193976625564337f, 0.49039264020161522f,
+                                        0.5f, 0.49039264020161522f, 0.46193976625564337f, 0.41573480615127262f,
+                                        0.35355339059327379f, 0.27778511650980114f, 0.19134171618254492f, 0.09754516100806417f};
+
 // Scaler + RBF SVM + Platt for one 40-d feature vector held as z[40] (already standardised) in
 // shared memory.  All 32 lanes participate; the result is valid on every lane.
 __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, int lane)
@@ -199,7 +209,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const int last_valid = n_samples - (F - 1) * SJ_HOP;
     const long stride = long(gridDim.x) * WARPS;
     long clip = long(blockIdx.x) * WARPS + warp;
-    const float2 *win2 = reinterpret_cast<const float2 *>(T->window) + lane;
+    // hann[64 m1 + 2 lane + d] = 0.5 - 0.5 cos(a + b), a = 2 pi m1/32, b = pi (2 lane + d)/1024
+    float sb0, cb0, sb1, cb1;
+    sincospif((float)(2 * lane) * (1.f / 1024.f), &sb0, &cb0);
+    sincospif((float)(2 * lane + 1) * (1.f / 1024.f), &sb1, &cb1);
     const float4 *tw4 = reinterpret_cast<const float4 *>(T->tw4) + lane;
     const float4 *tp4 = reinterpret_cast<const float4 *>(T->tp4) + lane;
     const float4 *mw4 = reinterpret_cast<const float4 *>(T->melw4) + lane;
@@ -243,19 +256,26 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             float2 v[32];
             // ---- frame = [hop t-1 | hop t] * hann, packed z[m] = (y[2m], y[2m+1]), m = 32*m1 + lane;
             // hann[i + 1024] = 1 - hann[i]
+            // The window is rebuilt from the angle sum 2 pi (64 m1 + 2 lane + d)/2048: 0.5 cos/sin of the m1 part
+            // are immediates, cos/sin of the lane part sit in four registers -- two FMAs per pair of samples
+            // instead of a table read (shared-memory bandwidth binds this kernel, not issue).
             if (t == 0) {
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
-                    const float2 w = win2[32 * m1], c = cur[32 * m1];
+                    const float2 c = cur[32 * m1];
+                    const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
+                    const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
                     v[m1] = make_float2(0.f, 0.f);
-                    v[m1 + 16] = make_float2(fmaf(-c.x, w.x, c.x), fmaf(-c.y, w.y, c.y));
+                    v[m1 + 16] = make_float2(fmaf(-c.x, wx, c.x), fmaf(-c.y, wy, c.y));
                 }
             } else {
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
-                    const float2 w = win2[32 * m1], c = cur[32 * m1], s = prv[32 * m1];
-                    v[m1] = make_float2(s.x * w.x, s.y * w.y);
-                    v[m1 + 16] = make_float2(fmaf(-c.x, w.x, c.x), fmaf(-c.y, w.y, c.y));
+                    const float2 c = cur[32 * m1], s = prv[32 * m1];
+                    const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
+                    const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
+                    v[m1] = make_float2(s.x * wx, s.y * wy);
+                    v[m1 + 16] = make_float2(fmaf(-c.x, wx, c.x), fmaf(-c.y, wy, c.y));
                 }
             }
             __syncwarp();

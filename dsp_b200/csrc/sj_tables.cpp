@@ -230,7 +230,6 @@ int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned s
     memset(t, 0, sizeof(*t));
     if (samplerate == 0) return fail(err, "samplerate must be > 0");
     const double two_pi = 6.283185307179586476925286766559;
-    for (int i = 0; i < SJ_HOP; ++i) t->window[i] = (float)(0.5 * (1.0 - cos(two_pi * i / SJ_WIN)));
     for (int a = 0; a < 16; ++a)
         for (int b = 0; b < 32; ++b) {
             double a0 = two_pi * (double)(a * b) / 1024.0, a1 = two_pi * (double)((a + 16) * b) / 1024.0;

@@ -23,9 +23,6 @@ struct SjQuad { float x, y, z, w; };
 // Everything the kernel reads besides the clips.  Plain POD, identical layout on host and device.
 // The per-frame ("hot") tables come first; the kernel stages everything before sv_off into shared memory.
 struct SjTables {
-    // lower half of aubio's "hanningz" window, w[i] = 0.5(1-cos(2 pi i/2048)), i < 1024 (pvoc.c /
-    // mathutils.c new_aubio_window); the upper half is 1 - w[i].
-    float window[SJ_HOP];
     // step-2 twiddles of the 32x32 split of the 1024-point complex FFT, paired for the merged first
     // butterfly stage: tw4[n][lane] = (W^(n*lane), W^((n+16)*lane)), W = exp(-2 pi i/1024)
     SjQuad tw4[16][32];
