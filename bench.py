@@ -292,9 +292,9 @@ def run_ours(args, rank, local_rank, world):
             "frames_per_s": value * FRAMES_PER_CLIP,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (traffic or {}).get("dram_bytes_per_launch_1M_clips"),
-                         "peak_source": peak_src, "kernel": "cepstrum_kernel<12,true>",
+                         "peak_source": peak_src, "kernel": "cepstrum_kernel<12 warps, TMA, fast-16k>",
                          "kernel_ms": kernel_ms, "bytes_per_clip": BYTES_PER_CLIP,
-                         "note": "FFT arithmetic, not HBM, binds this kernel (see DESIGN.md): frac is of the HBM roofline"},
+                         "note": "shared-memory bandwidth and instruction issue of the FFT, not HBM, bind this kernel (see DESIGN.md): frac is of the HBM roofline"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "clips/s", "h2d_bytes_per_step": E * N_SAMPLES * 4,
                     "d2h_bytes_per_step": E * 12, "clips_per_step": E, "steps": args.e2e_steps,
@@ -319,7 +319,7 @@ def main():
     ap.add_argument("--e2e-clips", type=int, default=65536, help="clips per end-to-end step (pinned host buffer)")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--ref-clips-per-thread", type=int, default=32)
+    ap.add_argument("--ref-clips-per-thread", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
