@@ -36,6 +36,21 @@ template <typename T> struct V2;
 template <> struct V2<float> { typedef float2 type; };
 template <> struct V2<double> { typedef double2 type; };
 
+// bit-pattern views for the threshold searches (positive IEEE values are ordered like their bit patterns)
+template <typename T> struct Bits;
+template <> struct Bits<float> {
+    typedef uint32_t type;
+    static __device__ __forceinline__ uint32_t of(float x) { return __float_as_uint(x); }
+    static __device__ __forceinline__ float from(uint32_t b) { return __uint_as_float(b); }
+    static __device__ __forceinline__ uint32_t shfl(uint32_t b, int src) { return __shfl_sync(0xffffffffu, b, src); }
+};
+template <> struct Bits<double> {
+    typedef unsigned long long type;
+    static __device__ __forceinline__ unsigned long long of(double x) { return (unsigned long long)__double_as_longlong(x); }
+    static __device__ __forceinline__ double from(unsigned long long b) { return __longlong_as_double((long long)b); }
+    static __device__ __forceinline__ unsigned long long shfl(unsigned long long b, int src) { return __shfl_sync(0xffffffffu, b, src); }
+};
+
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
@@ -79,7 +94,9 @@ __device__ __forceinline__ void iir8(const T (&x)[8], T (&w)[8], const T (&a)[9]
 }
 
 template <typename T> struct RowState {
-    T min_s[32], max_s[32];
+    T min_in[32], max_in[32];   // min / max of a = re^2 + im^2 over the cells with Sxx > 0: inner bins 1..127 (doubled)
+    T min_ed[32], max_ed[32];   // ... and the edge bins 0 and 128
+    T queue[64];                // band-sum epilogue: a values of the cells that passed the level test
     uint32_t flags[32][3];
     int n_mid[DN_CLIPS_PER_WARP];
     T mids[DN_CLIPS_PER_WARP][DN_MAX_MID];
@@ -112,7 +129,7 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
 {
     const int half = lane >> 4, h = lane & 15;
     float2 *xb = st->xbuf[half];
-    const float U = tab->U, s_thr = tab->s_thr;
+    const float a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
     for (int p = 0; p < 16; ++p) {
         const int r = 2 * p + half;
         const float *rowp = rows + r * kRow;
@@ -152,18 +169,23 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
         // PSD of bins k = 16*hh + lane16 <= 128 (classifier.cpp:349-364) and the per-row bookkeeping
         const bool is_band = r & 1;
         float *cell = scratch + (size_t(r >> 1) * tb + t) * DN_BINS;
-        float lmin = INFINITY, lmax = 0.f;
+        float lmin = INFINITY, lmax = 0.f, emin = INFINITY, emax = 0.f;
         bool any = false;
+        // a = re^2 + im^2 with the reference's operations; "/ U", "* 2" (classifier.cpp:349-364) are applied
+        // later, only where a value is needed; the tests on Sxx use exact thresholds on a
 #pragma unroll
         for (int hh = 0; hh < 9; ++hh) {
             const int k = 16 * hh + h;
             if (hh < 8 || h == 0) {
-                float s = div_rn(add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y)), U);
-                if (k >= 1 && k <= DN_BINS - 2) s = s * 2.0f;
+                const float av = add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y));
+                const bool edge = (hh == 0 || hh == 8) && h == 0;
                 if (is_band) {
-                    cell[k] = s;
-                    if (s > 0) { lmin = fminf(lmin, s); lmax = fmaxf(lmax, s); }
-                } else any = any || (s >= s_thr);
+                    cell[k] = av;
+                    if (av >= a_pos) {
+                        if (edge) { emin = fminf(emin, av); emax = fmaxf(emax, av); }
+                        else { lmin = fminf(lmin, av); lmax = fmaxf(lmax, av); }
+                    }
+                } else any = any || (av >= (edge ? a_thr_e : a_thr_i));
             }
         }
 #pragma unroll
@@ -174,8 +196,10 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
         const unsigned ballot = __ballot_sync(kFull, any);
         if (h == 0) {
             if (is_band) {
-                st->min_s[r] = fminf(st->min_s[r], lmin);
-                st->max_s[r] = fmaxf(st->max_s[r], lmax);
+                st->min_in[r] = fminf(st->min_in[r], lmin);
+                st->max_in[r] = fmaxf(st->max_in[r], lmax);
+                st->min_ed[r] = fminf(st->min_ed[r], emin); // edge bins live in lane h == 0 only
+                st->max_ed[r] = fmaxf(st->max_ed[r], emax);
             } else if ((ballot >> (16 * half)) & 0xFFFFu) st->flags[r][t >> 5] |= 1u << (t & 31);
         }
     }
@@ -206,7 +230,7 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
     T *scratch = reinterpret_cast<T *>(a.scratch) + size_t(blockIdx.x) * DN_CLIPS_PER_WARP * tb * DN_BINS;
     const int q = lane >> 2, g = lane & 3;
     const int k2 = ((g & 1) << 1) | (g >> 1); // which quarter of the 128-point spectrum this lane ends up holding
-    const T U = tab->U, s_thr = tab->s_thr;
+    const T U = tab->U, a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
 
     for (long base = long(blockIdx.x) * DN_CLIPS_PER_WARP; base < a.n_clips; base += long(gridDim.x) * DN_CLIPS_PER_WARP) {
         long clip = base + ci;
@@ -215,10 +239,15 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         T w[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) w[j] = 0;
-        st->min_s[lane] = (T)INFINITY;
-        st->max_s[lane] = 0;
+        st->min_in[lane] = st->min_ed[lane] = (T)INFINITY;
+        st->max_in[lane] = st->max_ed[lane] = 0;
         st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
         int pos = 0, sample = 0;
+        float4 nx0 = make_float4(0.f, 0.f, 0.f, 0.f), nx1 = nx0;
+        if (ALIGNED) { // tb >= 1 guarantees 256 samples
+            nx0 = __ldg(reinterpret_cast<const float4 *>(src));
+            nx1 = __ldg(reinterpret_cast<const float4 *>(src + 4));
+        }
         T acc_cur = 0, acc_next = 0; // running sums of the current frame and of the next one (32-sample overlap)
         __syncwarp();
 
@@ -228,9 +257,13 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
             for (int i = 0; i < nnew; i += 8) {
                 T x[8], y[8];
                 if (ALIGNED) {
-                    const float4 u0 = __ldg(reinterpret_cast<const float4 *>(src + sample + i));
-                    const float4 u1 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 4));
-                    x[0] = u0.x; x[1] = u0.y; x[2] = u0.z; x[3] = u0.w; x[4] = u1.x; x[5] = u1.y; x[6] = u1.z; x[7] = u1.w;
+                    // software pipeline: the block after this one is requested before this one is filtered
+                    // (one warp per CTA and a serial recurrence leave nothing else to hide the load latency)
+                    x[0] = nx0.x; x[1] = nx0.y; x[2] = nx0.z; x[3] = nx0.w; x[4] = nx1.x; x[5] = nx1.y; x[6] = nx1.z; x[7] = nx1.w;
+                    if (sample + i + 16 <= n_samples) {
+                        nx0 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8));
+                        nx1 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 12));
+                    }
                 } else {
 #pragma unroll
                     for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
@@ -292,16 +325,19 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                 // untangle the real FFT, PSD scaling, and per-row bookkeeping
                 const bool is_band = r & 1; // filter 1 = 3000-7500 Hz: cells are kept; filter 0: midpoint flags
                 T *cell = scratch + (size_t(r >> 1) * tb + t) * DN_BINS;
-                T lmin = (T)INFINITY, lmax = 0;
+                T lmin = (T)INFINITY, lmax = 0, emin = (T)INFINITY, emax = 0;
                 bool any = false;
                 auto emit = [&](int bin, T x2, T y2) { // (x2, y2) = 2 X[bin]
                     const T re = (T)0.5 * x2, im = (T)0.5 * y2;
-                    T s = div_rn(add_rn(mul_rn(re, re), mul_rn(im, im)), U);
-                    if (bin >= 1 && bin <= DN_BINS - 2) s = s * (T)2;
+                    const T av = add_rn(mul_rn(re, re), mul_rn(im, im)); // Sxx = av / U (* 2 for inner bins), applied later
+                    const bool edge = bin == 0 || bin == DN_BINS - 1;
                     if (is_band) {
-                        cell[bin] = s;
-                        if (s > 0) { lmin = s < lmin ? s : lmin; lmax = s > lmax ? s : lmax; }
-                    } else any = any || (s >= s_thr);
+                        cell[bin] = av;
+                        if (av >= a_pos) {
+                            if (edge) { emin = av < emin ? av : emin; emax = av > emax ? av : emax; }
+                            else { lmin = av < lmin ? av : lmin; lmax = av > lmax ? av : lmax; }
+                        }
+                    } else any = any || (av >= (edge ? a_thr_e : a_thr_i));
                 };
                 auto pair = [&](T2 A, T bx, T by, int k, T &xa, T &ya, T &xb, T &yb) {
                     // A = Z[k], (bx, by) = Z[128 - k]; returns 2 X[k] and 2 conj-partner for bin 128 - k
@@ -339,11 +375,15 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                 // combine the quad's partial results; the quad leader updates the row state
                 lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 1)); lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 2));
                 lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 1)); lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 2));
+                emin = fmin(emin, __shfl_xor_sync(kFull, emin, 1)); emin = fmin(emin, __shfl_xor_sync(kFull, emin, 2));
+                emax = fmax(emax, __shfl_xor_sync(kFull, emax, 1)); emax = fmax(emax, __shfl_xor_sync(kFull, emax, 2));
                 const unsigned ballot = __ballot_sync(kFull, any);
                 if (g == 0) {
                     if (is_band) {
-                        st->min_s[r] = fmin(st->min_s[r], lmin);
-                        st->max_s[r] = fmax(st->max_s[r], lmax);
+                        st->min_in[r] = fmin(st->min_in[r], lmin);
+                        st->max_in[r] = fmax(st->max_in[r], lmax);
+                        st->min_ed[r] = fmin(st->min_ed[r], emin);
+                        st->max_ed[r] = fmax(st->max_ed[r], emax);
                     } else if ((ballot >> (4 * q)) & 0xFu) st->flags[r][t >> 5] |= 1u << (t & 31);
                 }
             }
@@ -380,39 +420,95 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         }
         __syncwarp();
 
-        // ---- epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip
+        // ---- epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip.
+        // A cell counts when its normalised dB level nv lies strictly inside (lo_norm, hi_norm)
+        // (classifier.c:128-156).  nv is a monotone function of a, so the two level tests become
+        // a_lo <= a < a_hi with per-clip thresholds found by a 32-way search over bit patterns that evaluates
+        // the reference's own expression (double log10 included); the logarithm is then only taken for the
+        // cells that pass, compacted through a small queue so that all 32 lanes work on passing cells.
         for (int c2 = 0; c2 < DN_CLIPS_PER_WARP; ++c2) {
             if (base + c2 >= a.n_clips) break;
             const int nm = st->n_mid[c2];
             int label = 0;
             T s_above = 0, s_mid = 0, s_below = 0;
             if (nm > 0) {
-                const T mn = to_db<T>(st->min_s[2 * c2 + 1]), mx = to_db<T>(st->max_s[2 * c2 + 1]);
+                const int rb = 2 * c2 + 1;
+                T smin = (T)INFINITY, smax = 0;
+                if (st->max_in[rb] > 0) { smin = mul_rn(div_rn(st->min_in[rb], U), (T)2); smax = mul_rn(div_rn(st->max_in[rb], U), (T)2); }
+                if (st->max_ed[rb] > 0) {
+                    const T e0 = div_rn(st->min_ed[rb], U), e1 = div_rn(st->max_ed[rb], U);
+                    smin = e0 < smin ? e0 : smin;
+                    smax = e1 > smax ? e1 : smax;
+                }
+                const T mn = to_db<T>(smin), mx = to_db<T>(smax);
                 const T range = sub_rn(mx, mn), lo = tab->lo_norm, hi = tab->hi_norm;
+                auto level = [&](T av) -> T { // normalised dB level of an inner-bin cell, the reference's operations
+                    const T sv = mul_rn(div_rn(av, U), (T)2);
+                    return div_rn(sub_rn(to_db<T>(sv), mn), range);
+                };
+                // smallest a in [a_pos, max] with pred true (pred monotone); "none" = +inf
+                auto first_true = [&](auto pred) -> T {
+                    typedef typename Bits<T>::type UI;
+                    UI blo = Bits<T>::of(a_pos), bhi = Bits<T>::of(st->max_in[rb]);
+                    if (!(st->max_in[rb] >= a_pos) || !pred(st->max_in[rb])) return (T)INFINITY;
+                    while (blo < bhi) {
+                        const UI step = (bhi - blo) / 32 + 1;
+                        UI cand = blo + step * (UI)(lane + 1) - 1;
+                        if (cand > bhi || cand < blo) cand = bhi;
+                        const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(cand)));
+                        const int first = __ffs(bal) - 1; // lane 31 holds bhi, where pred is true
+                        const UI at = Bits<T>::shfl(cand, first), before = Bits<T>::shfl(cand, first > 0 ? first - 1 : 0);
+                        bhi = at;
+                        if (first > 0) blo = before + 1;
+                    }
+                    return Bits<T>::from(bhi);
+                };
+                T a_lo = (T)INFINITY, a_hi = (T)INFINITY;
+                if (range > 0) { // range == 0 makes every level NaN/inf in the reference: nothing passes
+                    a_lo = first_true([&](T av) { return level(av) > lo; });
+                    a_hi = first_true([&](T av) { return !(level(av) < hi); });
+                }
                 const T *scr = scratch + size_t(c2) * tb * DN_BINS;
-                auto box = [&](T lower, T upper, T half, T midpoint) -> T {
-                    // index search exactly as sum_intense (classifier.c:596-640)
-                    int f0 = 0, f1 = DN_BINS - 1, t0 = 0, t1 = tb - 1;
-                    while (f0 < DN_BINS && div_rn(mul_rn((T)f0, fs), (T)DN_WIN) < lower) f0++;
-                    while (f1 >= 0 && div_rn(mul_rn((T)f1, fs), (T)DN_WIN) > upper) f1--;
-                    if (f0 >= DN_BINS) f0 = DN_BINS - 1;
-                    if (f1 < 0) f1 = 0;
-                    if (f0 > f1) { const int x = f0; f0 = f1; f1 = x; }
+                auto box = [&](int band, T half, T midpoint) -> T {
+                    const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
+                    // time index search exactly as sum_intense (classifier.c:619-640), evaluated lane-parallel:
+                    // times are increasing, so the loops count the frames before / after the window
                     const T tlo = sub_rn(midpoint, half), thi = add_rn(midpoint, half);
-                    while (t0 < tb && div_rn((T)(t0 * DN_HOP + DN_WIN / 2), fs) < tlo) t0++;
-                    while (t1 >= 0 && div_rn((T)(t1 * DN_HOP + DN_WIN / 2), fs) > thi) t1--;
+                    int nb = 0, na = 0;
+                    for (int j = lane; j < DN_MAX_TB; j += 32) {
+                        const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                        nb += __popc(__ballot_sync(kFull, j < tb && tj < tlo));
+                        na += __popc(__ballot_sync(kFull, j < tb && tj > thi));
+                    }
+                    int t0 = nb, t1 = tb - 1 - na;
                     if (t0 >= tb) t0 = tb - 1;
                     if (t1 < 0) t1 = 0;
                     if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
                     double acc = 0.0;
-                    for (int j = t0; j <= t1; ++j)
-                        for (int i = f0 + lane; i <= f1; i += 32) {
-                            const T s = scr[j * DN_BINS + i];
-                            if (s > 0) {
-                                const T nv = div_rn(sub_rn(to_db<T>(s), mn), range);
-                                if (nv > lo && nv < hi) acc += (double)nv;
-                            }
+                    const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
+                    int nq = 0; // queued cells (warp-uniform)
+                    for (int c0 = 0; c0 < ncell; c0 += 32) {
+                        const int c = c0 + lane;
+                        T av = 0;
+                        if (c < ncell) {
+                            const int j = c / nf, i = c - j * nf;
+                            av = scr[(t0 + j) * DN_BINS + f0 + i];
                         }
+                        const bool pass = c < ncell && av >= a_lo && av < a_hi;
+                        const unsigned bal = __ballot_sync(kFull, pass);
+                        if (pass) st->queue[nq + __popc(bal & ((1u << lane) - 1u))] = av;
+                        nq += __popc(bal);
+                        __syncwarp();
+                        if (nq >= 32) {
+                            acc += (double)level(st->queue[lane]);
+                            nq -= 32;
+                            __syncwarp();
+                            if (lane < nq) st->queue[lane] = st->queue[32 + lane];
+                            __syncwarp();
+                        }
+                    }
+                    if (lane < nq) acc += (double)level(st->queue[lane]);
+                    __syncwarp();
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
                     return (T)acc;
@@ -420,9 +516,9 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                 const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
                 for (int m = 0; m < cap; ++m) {
                     const T mp = st->mids[c2][m];
-                    s_above = box((T)5000, (T)7000, (T)0.18, mp);
-                    s_mid = box((T)2500, (T)5000, (T)0.05, mp);
-                    s_below = box((T)500, (T)2500, (T)0.18, mp);
+                    s_above = box(0, (T)0.18, mp);
+                    s_mid = box(1, (T)0.05, mp);
+                    s_below = box(2, (T)0.18, mp);
                     if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
                 }
             }

@@ -30,6 +30,12 @@ template <typename T> struct SjDonutTables {
     T U;                       // fs * sum(window^2)
     T fs;
     T s_thr;                   // smallest Sxx whose dB value exceeds mid_thr_db (exact, by bisection)
+    // The kernel works on a = re^2 + im^2 and applies the reference's "/ U" and "* 2" only where a value is
+    // needed; every test on Sxx is moved to a through exact thresholds (Sxx is a monotone function of a):
+    T a_thr[2];                // smallest a with Sxx(a) >= s_thr: [0] edge bins (0, 128), [1] inner bins (doubled)
+    T a_pos;                   // smallest a with a / U > 0 (the reference's "Sxx > 0" test)
+    int32_t box_f[3][2];       // sum_intense's inclusive frequency-bin range of the above / middle / below band
+    int32_t pad_i[2];
     T lo_norm, hi_norm, gap_tol, min_dur, thr_mid, thr_above, thr_below;
     T pad;
 };

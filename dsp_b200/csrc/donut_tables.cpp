@@ -49,6 +49,25 @@ template <typename T, typename U> T smallest_exceeding(T thr)
     return v;
 }
 
+// smallest positive a with pred(a) true, pred monotone (false ... false true ... true); max value if never
+template <typename T, typename U, typename P> T smallest_with(P pred)
+{
+    U lo = 1, hi;
+    T top;
+    if (sizeof(T) == 4) { hi = (U)0x7f7fffffu; } else { hi = (U)0x7fefffffffffffffull; }
+    memcpy(&top, &hi, sizeof top);
+    if (!pred(top)) return top;
+    while (lo < hi) {
+        U mid = lo + (hi - lo) / 2;
+        T v;
+        memcpy(&v, &mid, sizeof v);
+        if (pred(v)) hi = mid; else lo = mid + 1;
+    }
+    T v;
+    memcpy(&v, &lo, sizeof v);
+    return v;
+}
+
 template <typename T, typename U> void build(SjDonutTables<T> *t, const SjDonutParams &p, int fs)
 {
     memset(t, 0, sizeof *t);
@@ -90,6 +109,24 @@ template <typename T, typename U> void build(SjDonutTables<T> *t, const SjDonutP
     for (int w = 0; w < 2; w++)
         for (int j = 0; j < 9; j++) { t->a[w][j] = (T)kA[w][j]; t->b[w][j] = (T)kB[w][j]; }
     t->s_thr = smallest_exceeding<T, U>((T)p.mid_thr_db);
+    {
+        const volatile T Uv = t->U, thr = t->s_thr; // volatile: keep the divisions as written (no reciprocal tricks)
+        t->a_thr[0] = smallest_with<T, U>([&](T a) { T s = a / Uv; return s >= thr; });
+        t->a_thr[1] = smallest_with<T, U>([&](T a) { T s = a / Uv; s = s * (T)2; return s >= thr; });
+        t->a_pos = smallest_with<T, U>([&](T a) { T s = a / Uv; return s > (T)0; });
+        // sum_intense's index search (classifier.c:596-617 / classifier.cpp:372-393) for the three fixed bands
+        const T band[3][2] = {{5000, 7000}, {2500, 5000}, {500, 2500}};
+        for (int b = 0; b < 3; ++b) {
+            int f0 = 0, f1 = DN_BINS - 1;
+            while (f0 < DN_BINS && (T)f0 * t->fs / (T)DN_WIN < band[b][0]) f0++;
+            while (f1 >= 0 && (T)f1 * t->fs / (T)DN_WIN > band[b][1]) f1--;
+            if (f0 >= DN_BINS) f0 = DN_BINS - 1;
+            if (f1 < 0) f1 = 0;
+            if (f0 > f1) { const int x = f0; f0 = f1; f1 = x; }
+            t->box_f[b][0] = f0;
+            t->box_f[b][1] = f1;
+        }
+    }
     t->lo_norm = (T)p.lo_norm; t->hi_norm = (T)p.hi_norm;
     t->gap_tol = (T)p.gap_tol; t->min_dur = (T)p.min_dur;
     t->thr_mid = (T)p.thr_mid; t->thr_above = (T)p.thr_above; t->thr_below = (T)p.thr_below;
