@@ -143,8 +143,26 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
             const float x = rowp[(pos + n) & 255];
             v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
         }
+        // stages 0 and 1 act on purely real data with the twiddles (1, 0) and (0, -1) (exact in the reference's
+        // recurrence): products with 0 and 1 and sums with 0 are exact, so the ten operations of a butterfly
+        // collapse to the two that change a value (the sign of a zero is the only thing lost; it squares away)
 #pragma unroll
-        for (int l = 0; l < 4; ++l) {
+        for (int i = 0; i < 16; i += 2) {
+            const float t1 = v[i + 1].x;
+            v[i + 1].x = sub_rn(v[i].x, t1);
+            v[i].x = add_rn(v[i].x, t1);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float t1 = v[i + 2].x; // twiddle (1, 0)
+            v[i + 2].x = sub_rn(v[i].x, t1);
+            v[i].x = add_rn(v[i].x, t1);
+            const float t2 = v[i + 3].x; // twiddle (0, -1): t = (hi.y, -hi.x) = (0, -t2)
+            v[i + 3] = make_float2(v[i + 1].x, t2);
+            v[i + 1].y = -t2;
+        }
+#pragma unroll
+        for (int l = 2; l < 4; ++l) {
             const int l1 = 1 << l;
 #pragma unroll
             for (int i = 0; i < 16; ++i)
@@ -243,10 +261,18 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         st->max_in[lane] = st->max_ed[lane] = 0;
         st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
         int pos = 0, sample = 0;
-        float4 nx0 = make_float4(0.f, 0.f, 0.f, 0.f), nx1 = nx0;
-        if (ALIGNED) { // tb >= 1 guarantees 256 samples
-            nx0 = __ldg(reinterpret_cast<const float4 *>(src));
-            nx1 = __ldg(reinterpret_cast<const float4 *>(src + 4));
+        // software pipeline of the input: a register ring of kPre blocks of 8 samples, each block requested
+        // kPre blocks (~1 us of recurrence) before it is filtered -- one warp per CTA and a serial
+        // recurrence leave nothing else to hide the DRAM latency
+        constexpr int kPre = 4;
+        float4 ring[kPre][2];
+#pragma unroll
+        for (int j = 0; j < kPre; ++j) {
+            ring[j][0] = ring[j][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ALIGNED) { // tb >= 1 guarantees 256 samples
+                ring[j][0] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j));
+                ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j + 4));
+            }
         }
         T acc_cur = 0, acc_next = 0; // running sums of the current frame and of the next one (32-sample overlap)
         __syncwarp();
@@ -254,31 +280,34 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         for (int t = 0; t < tb; ++t) {
             // ---- phase 1: advance this lane's IIR by one hop (256 samples for the first frame)
             const int nnew = t == 0 ? DN_WIN : DN_HOP;
-            for (int i = 0; i < nnew; i += 8) {
-                T x[8], y[8];
-                if (ALIGNED) {
-                    // software pipeline: the block after this one is requested before this one is filtered
-                    // (one warp per CTA and a serial recurrence leave nothing else to hide the load latency)
-                    x[0] = nx0.x; x[1] = nx0.y; x[2] = nx0.z; x[3] = nx0.w; x[4] = nx1.x; x[5] = nx1.y; x[6] = nx1.z; x[7] = nx1.w;
-                    if (sample + i + 16 <= n_samples) {
-                        nx0 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8));
-                        nx1 = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 12));
+            for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) { // 224 and 256 are multiples of 32
+#pragma unroll
+                for (int j = 0; j < kPre; ++j) {
+                    const int i = i0 + 8 * j;
+                    T x[8], y[8];
+                    if (ALIGNED) {
+                        const float4 u0 = ring[j][0], u1 = ring[j][1];
+                        x[0] = u0.x; x[1] = u0.y; x[2] = u0.z; x[3] = u0.w; x[4] = u1.x; x[5] = u1.y; x[6] = u1.z; x[7] = u1.w;
+                        if (sample + i + 8 * kPre + 8 <= n_samples) {
+                            ring[j][0] = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8 * kPre));
+                            ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8 * kPre + 4));
+                        }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
                     }
-                } else {
+                    iir8<T>(x, w, ca, cb, y);
+                    // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
+                    const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
+                    for (int k = 0; k < 8; ++k) {
+                        acc_cur = add_rn(acc_cur, y[k]);
+                        if (tail) acc_next = add_rn(acc_next, y[k]);
+                    }
+                    T *dst = myrow + ((pos + i) & 255);
+#pragma unroll
+                    for (int k = 0; k < 8; k += 2) *reinterpret_cast<T2 *>(dst + k) = T2{y[k], y[k + 1]};
                 }
-                iir8<T>(x, w, ca, cb, y);
-                // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
-                const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
-#pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    acc_cur = add_rn(acc_cur, y[k]);
-                    if (tail) acc_next = add_rn(acc_next, y[k]);
-                }
-                T *dst = myrow + ((pos + i) & 255);
-#pragma unroll
-                for (int k = 0; k < 8; k += 2) *reinterpret_cast<T2 *>(dst + k) = T2{y[k], y[k + 1]};
             }
             sample += nnew;
             pos = (pos + nnew) & 255; // = offset of the oldest of the 256 most recent samples = frame start
