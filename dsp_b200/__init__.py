@@ -54,6 +54,10 @@ def load_library():
     L.scrubjay_mfcc_stats_batch_dev.argtypes = [vp, vp, c_long, c_int, vp]
     L.scrubjay_predict_batch_dev.argtypes = [vp, vp, c_long, vp, vp, vp]
     L.scrubjay_infer_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_stream_windows.argtypes = [c_long, c_int, c_int]
+    L.scrubjay_stream_windows.restype = c_long
+    L.scrubjay_stream_infer_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
+    L.scrubjay_set_stream_chunk.argtypes = [vp, c_int]
     L.scrubjay_mfcc_stats.argtypes = [vp, vp, c_long, vp]
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
     L.scrubjay_infer_batch.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
@@ -148,6 +152,21 @@ class ScrubJay:
     def infer_batch_dev(self, d_clips, n_clips, n_samples, d_labels, d_conf=None, d_score=None, d_feats=None):
         self._check(self._L.scrubjay_infer_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_labels),
                                                      _ptr(d_conf), _ptr(d_score), _ptr(d_feats)))
+
+
+    def stream_windows(self, n_samples, win_frames=16, step_frames=16):
+        return self._L.scrubjay_stream_windows(n_samples, win_frames, step_frames)
+
+    def stream_infer_dev(self, streams, n_channels, n_samples, chan_stride, labels, conf=None, score=None, feats=None,
+                         win_frames=16, step_frames=16, prev_hop=None):
+        """scrubjay_stream_infer_dev: sliding-window cepstrum + SVM over continuous channels; outputs are
+        [channel][window] device arrays with stream_windows(n_samples, win, step) windows per channel."""
+        self._check(self._L.scrubjay_stream_infer_dev(self._h, _ptr(streams), n_channels, n_samples, chan_stride,
+                                                      _ptr(prev_hop), win_frames, step_frames, _ptr(labels),
+                                                      _ptr(conf), _ptr(score), _ptr(feats)))
+
+    def set_stream_chunk(self, windows_per_item):
+        self._check(self._L.scrubjay_set_stream_chunk(self._h, windows_per_item))
 
     def synth_clips_dev(self, d_out, first_clip, n_clips, n_samples, seed=0x5C2B):
         self._check(self._L.scrubjay_synth_clips_dev(self._h, _ptr(d_out), first_clip, n_clips, n_samples, seed))

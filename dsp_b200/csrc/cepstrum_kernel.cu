@@ -177,7 +177,10 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
 
 // FAST: the 16 kHz layout (28-bin lane chunks, static flush slots, <= 5 combine entries, mirror bins of
 // the first 4 untangling rows skipped); otherwise every mel parameter is read from the tables.
-template <int WARPS, bool TMA, bool FAST>
+// STREAM: the batch is a set of long channels cut into work items of `chunk_windows` analysis windows; the
+// pvoc state (previous hop) runs on across windows and a ring of the last win_frames MFCC vectors feeds the
+// per-window statistics.  Otherwise one work item = one clip = one window over all of its frames.
+template <int WARPS, bool TMA, bool FAST, bool STREAM>
 __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstrumArgs a, const int maxseg)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -186,10 +189,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     size_t off = (kHotBytes + 127) & ~size_t(127);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + off) + 2 * warp;
     off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
-    float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * warp_floats(maxseg);
+    constexpr int kRingFloats = STREAM ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0;
+    float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * (warp_floats(maxseg) + kRingFloats);
     float *tb = wbase + 2 * SJ_HOP;   // transpose plane, later |X|
     float *lg = tb + kTFloats;        // log energies / standardised features
     float *P = lg + kLogFloats;       // mel partial sums
+    float *mring = P + p_floats(maxseg); // STREAM: the last win_frames MFCC vectors, [frame % W][coef]
 
     {   // stage the tables
         const int4 *src = reinterpret_cast<const int4 *>(a.tables);
@@ -205,10 +210,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     __syncthreads();
 
     const int n_samples = a.n_samples;
-    const int F = (n_samples + SJ_HOP - 1) / SJ_HOP;
+    const int F = (n_samples + SJ_HOP - 1) / SJ_HOP; // hops of one clip / one channel
     const int last_valid = n_samples - (F - 1) * SJ_HOP;
     const long stride = long(gridDim.x) * WARPS;
-    long clip = long(blockIdx.x) * WARPS + warp;
+    const long n_items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
+    long item = long(blockIdx.x) * WARPS + warp;
+    const int W = a.win_frames, S = a.step_frames;
     // hann[64 m1 + 2 lane + d] = 0.5 - 0.5 cos(a + b), a = 2 pi m1/32, b = pi (2 lane + d)/1024
     float sb0, cb0, sb1, cb1;
     sincospif((float)(2 * lane) * (1.f / 1024.f), &sb0, &cb0);
@@ -221,9 +228,30 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const int partner = (32 - lane) & 31;
     constexpr int PSKIP = FAST ? 4 : 0;
 
-    // fetch hop `h` of clip `c` into ring slot `slot`
-    auto fetch = [&](long c, int h, int slot) {
-        const float *src = a.clips + c * (long)n_samples + (long)h * SJ_HOP;
+    // A work item walks `nh` consecutive hops of one clip / channel starting at hop `hop0` (-1 = the caller's
+    // carried-over hop); its first `warm` hops are only loaded (they are the previous hop of the first frame).
+    struct Seg { const float *base, *prev; long out0; int hop0, nh, warm, f0; };
+    auto seg_of = [&](long it) -> Seg {
+        Seg g;
+        if (!STREAM) {
+            g.base = a.clips + it * (long)n_samples; g.prev = nullptr; g.out0 = it; g.hop0 = 0; g.nh = F; g.warm = 0; g.f0 = 0;
+        } else {
+            const long c = it / a.chunks_per_chan;
+            const long j0 = (it - c * a.chunks_per_chan) * a.chunk_windows;
+            const long j1 = j0 + a.chunk_windows < a.n_windows ? j0 + a.chunk_windows : a.n_windows;
+            g.base = a.clips + c * a.chan_stride;
+            g.prev = a.prev_hop ? a.prev_hop + c * SJ_HOP : nullptr;
+            g.out0 = c * a.n_windows + j0;
+            g.f0 = (int)(j0 * S);
+            g.warm = (g.f0 > 0 || g.prev) ? 1 : 0;
+            g.hop0 = g.f0 - g.warm;
+            g.nh = (int)((j1 - 1) * S) + W - g.hop0;
+        }
+        return g;
+    };
+    // fetch hop `h` of the item into ring slot `slot`
+    auto fetch = [&](const Seg &g, int h, int slot) {
+        const float *src = h < 0 ? g.prev : g.base + (long)h * SJ_HOP;
         const int cnt = (h == F - 1) ? last_valid : SJ_HOP;
         float *dst = wbase + slot * SJ_HOP;
         if (TMA) {
@@ -237,19 +265,53 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             __syncwarp();
         }
     };
+    // window statistics (cepstrum/scrubjay_infer.c:61-67) -> Scaler -> SVM -> outputs at index `out`
+    auto emit = [&](long out, double sum, double sq, int nframes) {
+        __syncwarp();
+        if (lane < SJ_NCOEF) {
+            const double mean = sum / (double)nframes;
+            const double var = sq / (double)nframes - mean * mean;
+            const float fm = (float)mean;
+            const float fs = sqrtf((float)(var > 0 ? var : 0));
+            if (a.feats) {
+                a.feats[out * SJ_FEAT + lane] = fm;
+                a.feats[out * SJ_FEAT + SJ_NCOEF + lane] = fs;
+            }
+            const SjTables *G = a.tables;
+            lg[lane] = (fm - __ldg(&G->sv_off[lane])) * __ldg(&G->sv_scale[lane]);
+            lg[lane + SJ_NCOEF] = (fs - __ldg(&G->sv_off[lane + SJ_NCOEF])) * __ldg(&G->sv_scale[lane + SJ_NCOEF]);
+        }
+        __syncwarp();
+        if (a.do_svm) {
+            const SvmOut r = svm_eval(a.tables, lg, lane);
+            if (lane == 0) {
+                if (a.labels) a.labels[out] = r.label;
+                if (a.conf) a.conf[out] = r.conf;
+                if (a.score) a.score[out] = r.score;
+            }
+        }
+        __syncwarp();
+    };
 
     uint32_t q = 0; // running hop number of this warp: ring slot q&1, mbarrier parity (q>>1)&1
-    if (clip < a.n_clips) fetch(clip, 0, 0);
+    Seg sg = seg_of(item < n_items ? item : 0);
+    if (item < n_items) fetch(sg, sg.hop0, 0);
 
-    for (; clip < a.n_clips; clip += stride) {
+    for (; item < n_items; item += stride) {
         double sum = 0.0, sq = 0.0;
-        for (int t = 0; t < F; ++t, ++q) {
-            const int slot = q & 1;
+        const int nh = sg.nh;
+        Seg nxt = sg;
+        for (int hr = 0; hr < nh; ++hr, ++q) {
+            const int slot = q & 1, ha = sg.hop0 + hr;
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
             float *curf = wbase + slot * SJ_HOP;
-            if (t == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
+            if (ha == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
                 for (int i = last_valid + lane; i < SJ_HOP; i += 32) curf[i] = 0.f;
                 __syncwarp();
+            }
+            if (STREAM && hr < sg.warm) { // previous hop of the item's first frame: nothing to compute
+                fetch(sg, ha + 1, slot ^ 1);
+                continue;
             }
             const float2 *cur = reinterpret_cast<const float2 *>(curf) + lane;
             const float2 *prv = reinterpret_cast<const float2 *>(wbase + (slot ^ 1) * SJ_HOP) + lane;
@@ -259,7 +321,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             // The window is rebuilt from the angle sum 2 pi (64 m1 + 2 lane + d)/2048: 0.5 cos/sin of the m1 part
             // are immediates, cos/sin of the lane part sit in four registers -- two FMAs per pair of samples
             // instead of a table read (shared-memory bandwidth binds this kernel, not issue).
-            if (t == 0) {
+            if (hr == 0) { // no previous hop: aubio_pvoc starts from zeros
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
                     const float2 c = cur[32 * m1];
@@ -279,11 +341,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 }
             }
             __syncwarp();
-            {   // prefetch the next hop of the stream into the slot that just became free
-                int nt = t + 1;
-                long nc = clip;
-                if (nt == F) { nt = 0; nc = clip + stride; }
-                if (nc < a.n_clips) fetch(nc, nt, slot ^ 1);
+            // prefetch the next hop (of this item, else the first hop of the warp's next item) into the slot that
+            // just became free
+            if (hr + 1 < nh) fetch(sg, ha + 1, slot ^ 1);
+            else if (item + stride < n_items) {
+                nxt = seg_of(item + stride);
+                fetch(nxt, nxt.hop0, slot ^ 1);
             }
             // ---- 1024-point complex FFT, 32 x 32 split
             sj_fft32(v); // over m1: Y[k1] in v[SJ_BREV32(k1)]
@@ -419,36 +482,30 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 const float *eo = lg + (lane & 1) * SJ_NCOEF;
 #pragma unroll
                 for (int m = 0; m < SJ_NFILT / 2; ++m) acc = fmaf(T->dct[m][lane], eo[m], acc);
-                const double dv = (double)acc;
-                sum += dv;
-                sq += dv * dv;
+                if (!STREAM) {
+                    const double dv = (double)acc;
+                    sum += dv;
+                    sq += dv * dv;
+                } else {
+                    const int fr = ha - sg.f0; // frame index inside the item; window j ends at frame j*S + W-1
+                    if (lane < SJ_NCOEF) mring[(fr % W) * SJ_NCOEF + lane] = acc;
+                    __syncwarp();
+                    const int e = fr - (W - 1);
+                    if (e >= 0 && e % S == 0) {
+                        double ws = 0.0, wq = 0.0;
+                        if (lane < SJ_NCOEF)
+                            for (int i = 1; i <= W; ++i) { // oldest frame first, like the reference's running sums
+                                const double dv = (double)mring[((fr + i) % W) * SJ_NCOEF + lane];
+                                ws += dv;
+                                wq += dv * dv;
+                            }
+                        emit(sg.out0 + e / S, ws, wq, W);
+                    }
+                }
             }
         }
-        // ---- clip statistics (cepstrum/scrubjay_infer.c:61-67) and the SVM
-        __syncwarp();
-        if (lane < SJ_NCOEF) {
-            const double mean = sum / (double)F;
-            const double var = sq / (double)F - mean * mean;
-            const float fm = (float)mean;
-            const float fs = sqrtf((float)(var > 0 ? var : 0));
-            if (a.feats) {
-                a.feats[clip * SJ_FEAT + lane] = fm;
-                a.feats[clip * SJ_FEAT + SJ_NCOEF + lane] = fs;
-            }
-            const SjTables *G = a.tables;
-            lg[lane] = (fm - __ldg(&G->sv_off[lane])) * __ldg(&G->sv_scale[lane]);
-            lg[lane + SJ_NCOEF] = (fs - __ldg(&G->sv_off[lane + SJ_NCOEF])) * __ldg(&G->sv_scale[lane + SJ_NCOEF]);
-        }
-        __syncwarp();
-        if (a.do_svm) {
-            const SvmOut r = svm_eval(a.tables, lg, lane);
-            if (lane == 0) {
-                if (a.labels) a.labels[clip] = r.label;
-                if (a.conf) a.conf[clip] = r.conf;
-                if (a.score) a.score[clip] = r.score;
-            }
-        }
-        __syncwarp();
+        if (!STREAM) emit(sg.out0, sum, sq, F);
+        sg = nxt;
     }
 }
 
@@ -472,11 +529,11 @@ __global__ void __launch_bounds__(256) svm_kernel(const float *feats, long n, co
     }
 }
 
-template <int WARPS> size_t smem_bytes(int maxseg)
+template <int WARPS> size_t smem_bytes(int maxseg, bool stream)
 {
     size_t off = (kHotBytes + 127) & ~size_t(127);
     off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
-    return off + size_t(WARPS) * warp_floats(maxseg) * sizeof(float);
+    return off + size_t(WARPS) * (warp_floats(maxseg) + (stream ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0)) * sizeof(float);
 }
 
 #ifndef SJ_WARPS
@@ -484,44 +541,59 @@ template <int WARPS> size_t smem_bytes(int maxseg)
 #endif
 constexpr int kWarps = SJ_WARPS;
 
-template <bool TMA, bool FAST> cudaError_t setup_one(int maxseg)
+template <bool TMA, bool FAST, bool STREAM> cudaError_t setup_one(int maxseg)
 {
-    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem_bytes<kWarps>(maxseg));
+    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST, STREAM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem_bytes<kWarps>(maxseg, STREAM));
 }
 
-template <bool TMA, bool FAST>
+template <bool TMA, bool FAST, bool STREAM>
 cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
 {
-    long ctas = (a.n_clips + kWarps - 1) / kWarps;
+    const long items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
+    long ctas = (items + kWarps - 1) / kWarps;
     if (ctas > num_sms) ctas = num_sms;
-    cepstrum_kernel<kWarps, TMA, FAST><<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg), stream>>>(a, maxseg);
+    cepstrum_kernel<kWarps, TMA, FAST, STREAM>
+        <<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg, STREAM), stream>>>(a, maxseg);
     return cudaGetLastError();
+}
+
+template <bool STREAM> cudaError_t launch_any(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
+{
+    // the bulk-copy path needs 16-byte aligned hop addresses and sizes
+    bool tma = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
+    if (STREAM) tma = tma && (a.chan_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.prev_hop) & 15) == 0);
+    // the fast instantiation hard-codes the 16 kHz layout: 28-bin chunks, static flush slots, <= 5
+    // combine entries, the mirrors of the first 4 untangling rows above the bank
+    const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4;
+    const int maxseg = h->mel_maxseg;
+    if (fast) return tma ? launch_one<true, true, STREAM>(a, maxseg, num_sms, stream) : launch_one<false, true, STREAM>(a, maxseg, num_sms, stream);
+    return tma ? launch_one<true, false, STREAM>(a, maxseg, num_sms, stream) : launch_one<false, false, STREAM>(a, maxseg, num_sms, stream);
 }
 
 } // namespace
 
 cudaError_t sj_cepstrum_setup(int maxseg)
 {
-    cudaError_t e = setup_one<true, true>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, true>(maxseg);
-    if (e == cudaSuccess) e = setup_one<true, false>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, false>(maxseg);
+    cudaError_t e = setup_one<true, true, false>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, true, false>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, false, false>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, false, false>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, true, true>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, true, true>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, false, true>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, false, true>(maxseg);
     return e;
 }
 
 cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
 {
     if (a.n_clips <= 0) return cudaSuccess;
-    // the bulk-copy path needs 16-byte aligned hop addresses and sizes
-    const bool tma = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
-    // the fast instantiation hard-codes the 16 kHz layout: 28-bin chunks, static flush slots, <= 5
-    // combine entries, the mirrors of the first 4 untangling rows above the bank
-    const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4;
-    const int maxseg = h->mel_maxseg;
-    if (fast) return tma ? launch_one<true, true>(a, maxseg, num_sms, stream) : launch_one<false, true>(a, maxseg, num_sms, stream);
-    return tma ? launch_one<true, false>(a, maxseg, num_sms, stream) : launch_one<false, false>(a, maxseg, num_sms, stream);
+    if (a.n_windows > 0) return launch_any<true>(a, h, num_sms, stream);
+    return launch_any<false>(a, h, num_sms, stream);
 }
+
+int sj_cepstrum_resident_warps(int num_sms) { return num_sms * kWarps; }
 
 cudaError_t sj_launch_svm(const float *feats, long n, const SjTables *tables, int32_t *labels, float *conf,
                           float *score, cudaStream_t stream)

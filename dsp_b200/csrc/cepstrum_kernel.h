@@ -15,11 +15,24 @@ struct SjCepstrumArgs {
     float *score;         // [n_clips] or NULL
     float *feats;         // [n_clips][40] or NULL
     int do_svm;           // 0: features only
+    // stream mode (n_windows > 0): `clips` holds n_clips channels of n_samples samples, chan_stride apart; the
+    // pvoc runs on continuously; window j covers frames [j*step_frames, j*step_frames + win_frames) and the
+    // outputs are [channel][window].  prev_hop ([n_clips][1024] or NULL) is the hop before sample 0 (carried
+    // state of a chunked stream; NULL = stream start, zeros like a fresh aubio_pvoc).
+    long chan_stride;
+    const float *prev_hop;
+    long n_windows;       // windows per channel; 0 = clip mode
+    int win_frames, step_frames;
+    int chunk_windows;    // windows per work item
+    long chunks_per_chan;
 };
+#define SJ_STREAM_MAX_WIN 16 /* frames per stream-mode window (ring of MFCC vectors in shared memory) */
 
 // Enqueues the kernel on `stream`.  `host_tables` is the host copy of a.tables (selects the mel layout),
 // `num_sms` the SM count of the device.  Returns the cudaError_t of the launch.
 cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *host_tables, int num_sms, cudaStream_t stream);
+// warps the persistent grid keeps resident (work-item sizing of the stream mode)
+int sj_cepstrum_resident_warps(int num_sms);
 // one-time attribute set-up (max dynamic shared memory); returns cudaError_t
 cudaError_t sj_cepstrum_setup(int mel_maxseg);
 // batched standalone SVM: feats [n][40] -> labels/conf/score

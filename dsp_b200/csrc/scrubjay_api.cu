@@ -50,6 +50,7 @@ struct scrubjay_ctx {
     int chunk_n_samples = 0;
     // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
     float *d_small = nullptr;
+    int stream_chunk_windows = 0; // 0 = automatic work-item size of the stream mode
     // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
     void *d_donut_tables[2] = {nullptr, nullptr};
     int donut_grid[2] = {0, 0};
@@ -122,6 +123,8 @@ int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, 
     SjCepstrumArgs a;
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
     a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
+    a.chan_stride = 0; a.prev_hop = nullptr; a.n_windows = 0; a.win_frames = a.step_frames = 0;
+    a.chunk_windows = 0; a.chunks_per_chan = 0;
     if (timed) SJ_CUDA(c, cudaEventRecord(c->ev0, stream));
     SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables, c->num_sms, stream));
     if (timed) { SJ_CUDA(c, cudaEventRecord(c->ev1, stream)); c->have_timing = true; }
@@ -247,6 +250,58 @@ int scrubjay_infer_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips
     if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
     SJ_CUDA(c, cudaSetDevice(c->device));
     return launch_cepstrum(c, c->stream, d_clips, n_clips, n_samples, d_labels, d_conf, d_score, d_feats, 1, true);
+}
+
+long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames)
+{
+    if (n_samples <= 0 || win_frames < 1 || step_frames < 1) return 0;
+    const long hops = (n_samples + SJ_HOP - 1) / SJ_HOP;
+    return hops < win_frames ? 0 : (hops - win_frames) / step_frames + 1;
+}
+
+int scrubjay_stream_infer_dev(scrubjay_ctx *c, const float *d_streams, long n_channels, long n_samples, long chan_stride,
+                              const float *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
+                              float *d_conf, float *d_score, float *d_feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_streams || !d_labels || n_channels < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0 || n_samples > 0x7fffffffL) return set_err(c, SJ_EINVAL, "samples per channel must be in 1 .. 2^31-1");
+    if (chan_stride < n_samples) return set_err(c, SJ_EINVAL, "channel stride shorter than the channel");
+    if (win_frames < 1 || win_frames > SJ_STREAM_MAX_WIN || step_frames < 1 || step_frames > win_frames)
+        return set_err(c, SJ_EINVAL, "need 1 <= step_frames <= win_frames <= 16");
+    const long nw = scrubjay_stream_windows(n_samples, win_frames, step_frames);
+    if (nw == 0 || n_channels == 0) return SJ_OK;
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SjCepstrumArgs a;
+    a.clips = d_streams; a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
+    a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
+    a.chan_stride = chan_stride; a.prev_hop = d_prev_hop; a.n_windows = nw;
+    a.win_frames = win_frames; a.step_frames = step_frames;
+    // work items: enough of them to keep every resident warp busy (>= 4 per warp), but long enough that the
+    // win - step frames recomputed at the head of each item stay below ~20 % of its work
+    const long want = 4L * sj_cepstrum_resident_warps(c->num_sms);
+    long per_chan = (want + n_channels - 1) / n_channels;
+    long k = (nw + per_chan - 1) / per_chan;
+    const long k_min = 4L * (win_frames - step_frames) / step_frames;
+    if (k < k_min) k = k_min;
+    if (k < 1) k = 1;
+    if (c->stream_chunk_windows > 0) k = c->stream_chunk_windows;
+    if (k > nw) k = nw;
+    a.chunk_windows = (int)k;
+    a.chunks_per_chan = (nw + k - 1) / k;
+    SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables, c->num_sms, c->stream));
+    SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->have_timing = true;
+    c->launches += 1;
+    return SJ_OK;
+}
+
+int scrubjay_set_stream_chunk(scrubjay_ctx *c, int windows_per_item)
+{
+    if (!c || windows_per_item < 0) return SJ_EINVAL;
+    c->stream_chunk_windows = windows_per_item;
+    return SJ_OK;
 }
 
 } // extern "C"

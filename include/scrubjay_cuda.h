@@ -87,6 +87,24 @@ SJ_API int scrubjay_predict_batch_dev(scrubjay_ctx *ctx, const float *d_feats, l
 SJ_API int scrubjay_infer_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                              int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
 
+/* Stream mode (BASELINE config 5: long continuous channels, sliding-frame cepstrum + SVM).  The reference
+ * has no streaming entry point: main (cepstrum/scrubjay_infer.c:158-177) reduces a whole file to one
+ * feature vector.  Here the loop body of mfcc_stats (:39-53) runs on without restarting aubio_pvoc, and the
+ * statistics of :61-67 followed by ort_predict are taken over every window of `win_frames` consecutive
+ * frames, advancing by `step_frames` (1 <= step <= win <= 16): window j of a channel covers frames
+ * [j*step, j*step + win), frame f = [hop f-1 | hop f].  d_streams holds n_channels channels of n_samples
+ * float32 samples, chan_stride samples apart; outputs are [channel][window] with
+ * scrubjay_stream_windows(n_samples, win, step) windows per channel.  d_prev_hop ([n_channels][1024] or
+ * NULL) is the hop that precedes sample 0 of every channel: the state a caller carries between the time
+ * chunks of an endless stream (overlap consecutive chunks by win - step hops to keep every window);
+ * NULL = stream start (zeros, like a fresh aubio_pvoc).  d_conf / d_score / d_feats may be NULL. */
+SJ_API long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames);
+SJ_API int scrubjay_stream_infer_dev(scrubjay_ctx *ctx, const float *d_streams, long n_channels, long n_samples,
+                              long chan_stride, const float *d_prev_hop, int win_frames, int step_frames,
+                              int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+/* windows per work item of the stream mode (0 = automatic); a tuning / test knob */
+SJ_API int scrubjay_set_stream_chunk(scrubjay_ctx *ctx, int windows_per_item);
+
 /* Host-pointer forms.  scrubjay_mfcc_stats keeps the reference's contract: 0 on success, -1
  * (SJ_EINVAL) on an empty clip. */
 SJ_API int scrubjay_mfcc_stats(scrubjay_ctx *ctx, const float *samples, long n_samples, float out[SJ_FEAT_DIM]);

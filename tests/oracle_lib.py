@@ -69,3 +69,33 @@ class CepstrumOracle:
                                          conf.ctypes.data, score.ctypes.data, feats.ctypes.data)
         assert r == n
         return labels, conf, score, feats
+
+    def stream_infer(self, x, win_frames=16, step_frames=16, prev_hop=None):
+        """Stream mode restated on the oracle: one channel `x`, the pvoc running on without a restart
+        (per-frame MFCCs from sj_oracle_mfcc_stats over the whole channel), then for every window of
+        `win_frames` frames advancing by `step_frames` the statistics of cepstrum/scrubjay_infer.c:61-67
+        (double sums in frame order, float sqrt of the float-converted variance) and sj_oracle_predict.
+        prev_hop (1024 samples) is the hop before x[0]: it is prepended and its own frame dropped."""
+        x = np.ascontiguousarray(x, np.float32)
+        if prev_hop is not None:
+            x = np.concatenate([np.asarray(prev_hop, np.float32), x])
+        _, fr = self.mfcc_stats(x, want_frames=True)
+        if prev_hop is not None:
+            fr = fr[1:]
+        nw = 0 if len(fr) < win_frames else (len(fr) - win_frames) // step_frames + 1
+        labels = np.zeros(nw, np.int32)
+        conf = np.zeros(nw, np.float32)
+        score = np.zeros(nw, np.float32)
+        feats = np.zeros((nw, 40), np.float32)
+        for j in range(nw):
+            w = fr[j * step_frames:j * step_frames + win_frames].astype(np.float64)
+            s, q = np.zeros(20), np.zeros(20)
+            for v in w:  # running sums in frame order, like the reference's loop
+                s += v
+                q += v * v
+            mean = s / win_frames
+            var = np.maximum(q / win_frames - mean * mean, 0.0)
+            feats[j, :20] = mean.astype(np.float32)
+            feats[j, 20:] = np.sqrt(var.astype(np.float32))
+            labels[j], conf[j], score[j] = self.predict(feats[j])
+        return labels, conf, score, feats
