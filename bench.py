@@ -275,6 +275,39 @@ def run_ours(args, rank, local_rank, world):
     e2e_value = world * E * args.e2e_steps / float(t.item())
     assert np.array_equal(h_labels, labels[:E].cpu().numpy()), "host-path labels differ from device-path labels"
 
+    # ---- int16 PCM ingest (the reference's on-disk format; SURVEY 8(d): reported separately, 32 008 B/clip)
+    pcm = None
+    if args.pcm16:
+        Cp = min(C, args.pcm16_clips)
+        pcm_dev = torch.empty((Cp, N_SAMPLES), dtype=torch.int16, device=dev)
+        for i in range(0, Cp, 65536):
+            j = min(Cp, i + 65536)
+            pcm_dev[i:j] = torch.clamp(torch.round(clips[i:j] * 32768.0), -32768, 32767).to(torch.int16)
+        kp = []
+        for i in range(4):
+            sj.infer_batch_pcm16_dev(pcm_dev, Cp, N_SAMPLES, labels[:Cp], conf[:Cp], score[:Cp], None)
+            kp.append(sj.last_kernel_ms())
+        kp = min(kp[1:])
+        hpcm = torch.empty((E, N_SAMPLES), dtype=torch.int16, pin_memory=True)
+        hpcm.copy_(pcm_dev[:E])
+        torch.cuda.synchronize()
+        sj.infer_batch_pcm16(hpcm.data_ptr(), n_clips=E, n_samples=N_SAMPLES)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            sj.infer_batch_pcm16(hpcm.data_ptr(), n_clips=E, n_samples=N_SAMPLES)
+        torch.cuda.synchronize()
+        tp = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        pcm = {"clips_per_s_per_gpu_resident": Cp / (kp * 1e-3), "kernel_ms": kp, "clips": Cp,
+               "bytes_per_clip": N_SAMPLES * 2 + 8, "achieved_gbs": (N_SAMPLES * 2 + 8) * Cp / (kp * 1e-3) / 1e9,
+               "e2e": {"value": world * E * args.e2e_steps / float(tp.item()), "unit": "clips/s",
+                       "h2d_bytes_per_step": E * N_SAMPLES * 2, "d2h_bytes_per_step": E * 12,
+                       "api": "scrubjay_infer_batch_pcm16 (host int16 PCM, pinned)"},
+               "note": "outputs bit-identical to the float path on s/32768 (tests/test_pcm16_gpu.py)"}
+        del pcm_dev
+
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
@@ -299,6 +332,7 @@ def run_ours(args, rank, local_rank, world):
             "e2e": {"value": e2e_value, "unit": "clips/s", "h2d_bytes_per_step": E * N_SAMPLES * 4,
                     "d2h_bytes_per_step": E * 12, "clips_per_step": E, "steps": args.e2e_steps,
                     "api": "scrubjay_infer_batch (host pointers, pinned)"},
+            "pcm16": pcm,
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
@@ -320,6 +354,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--ref-clips-per-thread", type=int, default=1024)
+    ap.add_argument("--no-pcm16", dest="pcm16", action="store_false", help="skip the int16 PCM ingest measurement")
+    ap.add_argument("--pcm16-clips", type=int, default=500000)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

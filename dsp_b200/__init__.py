@@ -54,6 +54,10 @@ def load_library():
     L.scrubjay_mfcc_stats_batch_dev.argtypes = [vp, vp, c_long, c_int, vp]
     L.scrubjay_predict_batch_dev.argtypes = [vp, vp, c_long, vp, vp, vp]
     L.scrubjay_infer_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_infer_batch_pcm16_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_infer_batch_pcm16.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_wav_parse.argtypes = [vp, ctypes.c_size_t, vp]
+    L.scrubjay_decode_pcm16_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
     L.scrubjay_stream_windows.argtypes = [c_long, c_int, c_int]
     L.scrubjay_stream_windows.restype = c_long
     L.scrubjay_stream_infer_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
@@ -211,6 +215,45 @@ class ScrubJay:
         self._check(self._L.scrubjay_infer_batch(self._h, _ptr(clips), n_clips, n_samples, labels.ctypes.data,
                                                  conf.ctypes.data, score.ctypes.data, _ptr(feats)))
         return (labels, conf, score, feats) if want_feats else (labels, conf, score)
+
+    def infer_batch_pcm16(self, clips, want_feats=False, n_clips=None, n_samples=None):
+        """clips: numpy [n_clips][n_samples] int16 PCM, or a raw host address with n_clips/n_samples."""
+        if isinstance(clips, np.ndarray):
+            clips = np.ascontiguousarray(clips, dtype=np.int16)
+            n_clips, n_samples = clips.shape
+        labels = np.empty(n_clips, np.int32)
+        conf = np.empty(n_clips, np.float32)
+        score = np.empty(n_clips, np.float32)
+        feats = np.empty((n_clips, FEAT_DIM), np.float32) if want_feats else None
+        self._check(self._L.scrubjay_infer_batch_pcm16(self._h, _ptr(clips), n_clips, n_samples, labels.ctypes.data,
+                                                       conf.ctypes.data, score.ctypes.data, _ptr(feats)))
+        return (labels, conf, score, feats) if want_feats else (labels, conf, score)
+
+    def infer_batch_pcm16_dev(self, clips, n_clips, n_samples, labels, conf=None, score=None, feats=None):
+        self._check(self._L.scrubjay_infer_batch_pcm16_dev(self._h, _ptr(clips), n_clips, n_samples, _ptr(labels),
+                                                           _ptr(conf), _ptr(score), _ptr(feats)))
+
+    def decode_pcm16_dev(self, interleaved, frames, channels, policy, out):
+        """interleaved int16 frames -> mono float (policy MIX_FIRST / MIX_MEAN)"""
+        self._check(self._L.scrubjay_decode_pcm16_dev(self._h, _ptr(interleaved), frames, channels, policy, _ptr(out)))
+
+
+MIX_FIRST, MIX_MEAN = 0, 1
+
+
+class WavInfo(ctypes.Structure):
+    _fields_ = [("audio_format", ctypes.c_int32), ("channels", ctypes.c_int32), ("sample_rate", ctypes.c_int32),
+                ("bits_per_sample", ctypes.c_int32), ("data_offset", ctypes.c_int64), ("data_bytes", ctypes.c_int64),
+                ("frames", ctypes.c_int64)]
+
+
+def wav_parse(data):
+    """scrubjay_wav_parse over a bytes object (host only, no GPU): WavInfo, or None if the reference's
+    read_wav_file would reject the file"""
+    buf = bytes(data)
+    info = WavInfo()
+    rc = load_library().scrubjay_wav_parse(buf, len(buf), ctypes.byref(info))
+    return info if rc == 0 else None
 
 
 DONUT_DESKTOP_F64 = 0  # donut-classifier/classifier.c constants, double arithmetic

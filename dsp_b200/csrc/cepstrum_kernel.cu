@@ -180,7 +180,10 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
 // STREAM: the batch is a set of long channels cut into work items of `chunk_windows` analysis windows; the
 // pvoc state (previous hop) runs on across windows and a ring of the last win_frames MFCC vectors feeds the
 // per-window statistics.  Otherwise one work item = one clip = one window over all of its frames.
-template <int WARPS, bool TMA, bool FAST, bool STREAM>
+// PCM16: the clips are int16 PCM (the reference's on-disk format); a hop is 2 KB and the conversion
+// x = s / 32768 (aubio_source / classifier.c:56-60, exact in float) happens in the load phase, so the
+// results are bit-identical to the float path fed with the converted samples.
+template <int WARPS, bool TMA, bool FAST, bool STREAM, bool PCM16>
 __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstrumArgs a, const int maxseg)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -230,17 +233,19 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
 
     // A work item walks `nh` consecutive hops of one clip / channel starting at hop `hop0` (-1 = the caller's
     // carried-over hop); its first `warm` hops are only loaded (they are the previous hop of the first frame).
-    struct Seg { const float *base, *prev; long out0; int hop0, nh, warm, f0; };
+    constexpr int ES = PCM16 ? 2 : 4; // bytes per sample
+    struct Seg { const unsigned char *base, *prev; long out0; int hop0, nh, warm, f0; };
+    const unsigned char *clips_b = reinterpret_cast<const unsigned char *>(a.clips);
     auto seg_of = [&](long it) -> Seg {
         Seg g;
         if (!STREAM) {
-            g.base = a.clips + it * (long)n_samples; g.prev = nullptr; g.out0 = it; g.hop0 = 0; g.nh = F; g.warm = 0; g.f0 = 0;
+            g.base = clips_b + it * (long)n_samples * ES; g.prev = nullptr; g.out0 = it; g.hop0 = 0; g.nh = F; g.warm = 0; g.f0 = 0;
         } else {
             const long c = it / a.chunks_per_chan;
             const long j0 = (it - c * a.chunks_per_chan) * a.chunk_windows;
             const long j1 = j0 + a.chunk_windows < a.n_windows ? j0 + a.chunk_windows : a.n_windows;
-            g.base = a.clips + c * a.chan_stride;
-            g.prev = a.prev_hop ? a.prev_hop + c * SJ_HOP : nullptr;
+            g.base = clips_b + c * a.chan_stride * ES;
+            g.prev = a.prev_hop ? reinterpret_cast<const unsigned char *>(a.prev_hop) + c * SJ_HOP * ES : nullptr;
             g.out0 = c * a.n_windows + j0;
             g.f0 = (int)(j0 * S);
             g.warm = (g.f0 > 0 || g.prev) ? 1 : 0;
@@ -251,17 +256,21 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     };
     // fetch hop `h` of the item into ring slot `slot`
     auto fetch = [&](const Seg &g, int h, int slot) {
-        const float *src = h < 0 ? g.prev : g.base + (long)h * SJ_HOP;
+        const unsigned char *src = h < 0 ? g.prev : g.base + (long)h * SJ_HOP * ES;
         const int cnt = (h == F - 1) ? last_valid : SJ_HOP;
         float *dst = wbase + slot * SJ_HOP;
         if (TMA) {
             if (lane == 0) {
                 fence_proxy_async();
-                mbar_expect_tx(&bars[slot], (uint32_t)cnt * 4u);
-                bulk_g2s(dst, src, (uint32_t)cnt * 4u, &bars[slot]);
+                mbar_expect_tx(&bars[slot], (uint32_t)cnt * ES);
+                bulk_g2s(dst, src, (uint32_t)cnt * ES, &bars[slot]);
             }
         } else {
-            for (int i = lane; i < cnt; i += 32) dst[i] = __ldg(src + i);
+            if (PCM16)
+                for (int i = lane; i < cnt; i += 32)
+                    reinterpret_cast<int16_t *>(dst)[i] = __ldg(reinterpret_cast<const int16_t *>(src) + i);
+            else
+                for (int i = lane; i < cnt; i += 32) dst[i] = __ldg(reinterpret_cast<const float *>(src) + i);
             __syncwarp();
         }
     };
@@ -306,25 +315,33 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
             float *curf = wbase + slot * SJ_HOP;
             if (ha == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
-                for (int i = last_valid + lane; i < SJ_HOP; i += 32) curf[i] = 0.f;
+                if (PCM16)
+                    for (int i = last_valid + lane; i < SJ_HOP; i += 32) reinterpret_cast<int16_t *>(curf)[i] = 0;
+                else
+                    for (int i = last_valid + lane; i < SJ_HOP; i += 32) curf[i] = 0.f;
                 __syncwarp();
             }
             if (STREAM && hr < sg.warm) { // previous hop of the item's first frame: nothing to compute
                 fetch(sg, ha + 1, slot ^ 1);
                 continue;
             }
-            const float2 *cur = reinterpret_cast<const float2 *>(curf) + lane;
-            const float2 *prv = reinterpret_cast<const float2 *>(wbase + (slot ^ 1) * SJ_HOP) + lane;
+            // sample pair (2m, 2m+1), m = 32*m1 + lane, of the current / previous hop as floats
+            const float *prvf = wbase + (slot ^ 1) * SJ_HOP;
+            auto pair_at = [&](const float *hop, int m1) -> float2 {
+                if (PCM16) {
+                    const uint32_t w = reinterpret_cast<const uint32_t *>(hop)[32 * m1 + lane];
+                    return make_float2((float)(int16_t)(w & 0xffffu) * (1.f / 32768.f), (float)((int32_t)w >> 16) * (1.f / 32768.f));
+                }
+                return reinterpret_cast<const float2 *>(hop)[32 * m1 + lane];
+            };
             float2 v[32];
-            // ---- frame = [hop t-1 | hop t] * hann, packed z[m] = (y[2m], y[2m+1]), m = 32*m1 + lane;
-            // hann[i + 1024] = 1 - hann[i]
             // The window is rebuilt from the angle sum 2 pi (64 m1 + 2 lane + d)/2048: 0.5 cos/sin of the m1 part
             // are immediates, cos/sin of the lane part sit in four registers -- two FMAs per pair of samples
             // instead of a table read (shared-memory bandwidth binds this kernel, not issue).
             if (hr == 0) { // no previous hop: aubio_pvoc starts from zeros
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
-                    const float2 c = cur[32 * m1];
+                    const float2 c = pair_at(curf, m1);
                     const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
                     const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
                     v[m1] = make_float2(0.f, 0.f);
@@ -333,7 +350,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             } else {
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
-                    const float2 c = cur[32 * m1], s = prv[32 * m1];
+                    const float2 c = pair_at(curf, m1), s = pair_at(prvf, m1);
                     const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
                     const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
                     v[m1] = make_float2(s.x * wx, s.y * wy);
@@ -541,56 +558,65 @@ template <int WARPS> size_t smem_bytes(int maxseg, bool stream)
 #endif
 constexpr int kWarps = SJ_WARPS;
 
-template <bool TMA, bool FAST, bool STREAM> cudaError_t setup_one(int maxseg)
+template <bool TMA, bool FAST, bool STREAM, bool PCM16> cudaError_t setup_one(int maxseg)
 {
-    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST, STREAM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem_bytes<kWarps>(maxseg, STREAM));
+    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST, STREAM, PCM16>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<kWarps>(maxseg, STREAM));
 }
 
-template <bool TMA, bool FAST, bool STREAM>
+template <bool TMA, bool FAST, bool STREAM, bool PCM16>
 cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
 {
     const long items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
     long ctas = (items + kWarps - 1) / kWarps;
     if (ctas > num_sms) ctas = num_sms;
-    cepstrum_kernel<kWarps, TMA, FAST, STREAM>
+    cepstrum_kernel<kWarps, TMA, FAST, STREAM, PCM16>
         <<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg, STREAM), stream>>>(a, maxseg);
     return cudaGetLastError();
 }
 
-template <bool STREAM> cudaError_t launch_any(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
+template <bool STREAM, bool PCM16>
+cudaError_t launch_any(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
 {
     // the bulk-copy path needs 16-byte aligned hop addresses and sizes
-    bool tma = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
-    if (STREAM) tma = tma && (a.chan_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.prev_hop) & 15) == 0);
+    const int per16 = PCM16 ? 8 : 4; // samples per 16 bytes
+    bool tma = (a.n_samples % per16 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
+    if (STREAM) tma = tma && (a.chan_stride % per16 == 0) && ((reinterpret_cast<uintptr_t>(a.prev_hop) & 15) == 0);
     // the fast instantiation hard-codes the 16 kHz layout: 28-bin chunks, static flush slots, <= 5
     // combine entries, the mirrors of the first 4 untangling rows above the bank
     const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4;
     const int maxseg = h->mel_maxseg;
-    if (fast) return tma ? launch_one<true, true, STREAM>(a, maxseg, num_sms, stream) : launch_one<false, true, STREAM>(a, maxseg, num_sms, stream);
-    return tma ? launch_one<true, false, STREAM>(a, maxseg, num_sms, stream) : launch_one<false, false, STREAM>(a, maxseg, num_sms, stream);
+    if (fast) return tma ? launch_one<true, true, STREAM, PCM16>(a, maxseg, num_sms, stream)
+                         : launch_one<false, true, STREAM, PCM16>(a, maxseg, num_sms, stream);
+    return tma ? launch_one<true, false, STREAM, PCM16>(a, maxseg, num_sms, stream)
+               : launch_one<false, false, STREAM, PCM16>(a, maxseg, num_sms, stream);
+}
+
+template <bool STREAM, bool PCM16> cudaError_t setup_four(int maxseg)
+{
+    cudaError_t e = setup_one<true, true, STREAM, PCM16>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, true, STREAM, PCM16>(maxseg);
+    if (e == cudaSuccess) e = setup_one<true, false, STREAM, PCM16>(maxseg);
+    if (e == cudaSuccess) e = setup_one<false, false, STREAM, PCM16>(maxseg);
+    return e;
 }
 
 } // namespace
 
 cudaError_t sj_cepstrum_setup(int maxseg)
 {
-    cudaError_t e = setup_one<true, true, false>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, true, false>(maxseg);
-    if (e == cudaSuccess) e = setup_one<true, false, false>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, false, false>(maxseg);
-    if (e == cudaSuccess) e = setup_one<true, true, true>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, true, true>(maxseg);
-    if (e == cudaSuccess) e = setup_one<true, false, true>(maxseg);
-    if (e == cudaSuccess) e = setup_one<false, false, true>(maxseg);
+    cudaError_t e = setup_four<false, false>(maxseg);
+    if (e == cudaSuccess) e = setup_four<true, false>(maxseg);
+    if (e == cudaSuccess) e = setup_four<false, true>(maxseg);
     return e;
 }
 
 cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
 {
     if (a.n_clips <= 0) return cudaSuccess;
-    if (a.n_windows > 0) return launch_any<true>(a, h, num_sms, stream);
-    return launch_any<false>(a, h, num_sms, stream);
+    if (a.pcm16) return a.n_windows > 0 ? cudaErrorInvalidValue : launch_any<false, true>(a, h, num_sms, stream);
+    if (a.n_windows > 0) return launch_any<true, false>(a, h, num_sms, stream);
+    return launch_any<false, false>(a, h, num_sms, stream);
 }
 
 int sj_cepstrum_resident_warps(int num_sms) { return num_sms * kWarps; }

@@ -6,7 +6,8 @@
 #include "sj_tables.h"
 
 struct SjCepstrumArgs {
-    const float *clips;   // [n_clips][n_samples], device
+    const float *clips;   // [n_clips][n_samples], device (int16_t samples when pcm16 != 0)
+    int pcm16;            // clips are int16 PCM, converted as s / 32768 in the kernel (clip mode only)
     long n_clips;
     int n_samples;
     const SjTables *tables; // device copy

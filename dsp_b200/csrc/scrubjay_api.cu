@@ -11,6 +11,7 @@
 #include "../../include/scrubjay_cuda.h"
 #include "cepstrum_kernel.h"
 #include "donut_kernel.h"
+#include "ingest_kernel.h"
 #include "sj_tables.h"
 
 cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
@@ -118,9 +119,10 @@ int ensure_stages(scrubjay_ctx *c, int n_samples)
 }
 
 int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, long n_clips, int n_samples,
-                    int32_t *labels, float *conf, float *score, float *feats, int do_svm, bool timed)
+                    int32_t *labels, float *conf, float *score, float *feats, int do_svm, bool timed, int pcm16 = 0)
 {
     SjCepstrumArgs a;
+    a.pcm16 = pcm16;
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
     a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
     a.chan_stride = 0; a.prev_hop = nullptr; a.n_windows = 0; a.win_frames = a.step_frames = 0;
@@ -252,6 +254,56 @@ int scrubjay_infer_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips
     return launch_cepstrum(c, c->stream, d_clips, n_clips, n_samples, d_labels, d_conf, d_score, d_feats, 1, true);
 }
 
+int scrubjay_infer_batch_pcm16_dev(scrubjay_ctx *c, const int16_t *d_clips, long n_clips, int n_samples,
+                                   int32_t *d_labels, float *d_conf, float *d_score, float *d_feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    return launch_cepstrum(c, c->stream, reinterpret_cast<const float *>(d_clips), n_clips, n_samples, d_labels, d_conf,
+                           d_score, d_feats, 1, true, 1);
+}
+
+int scrubjay_wav_parse(const void *bytes, size_t n, scrubjay_wav_info *info)
+{
+    if (!bytes || !info) return SJ_EINVAL;
+    const unsigned char *p = static_cast<const unsigned char *>(bytes);
+    auto u16 = [&](size_t o) { return (uint32_t)p[o] | ((uint32_t)p[o + 1] << 8); };
+    auto u32 = [&](size_t o) { return u16(o) | (u16(o + 2) << 16); };
+    memset(info, 0, sizeof *info);
+    if (n < 36 || memcmp(p, "RIFF", 4) || memcmp(p + 8, "WAVE", 4) || memcmp(p + 12, "fmt ", 4)) return SJ_EINVAL;
+    const size_t fmt_size = u32(16);
+    info->audio_format = (int32_t)u16(20);
+    info->channels = (int32_t)u16(22);
+    info->sample_rate = (int32_t)u32(24);
+    info->bits_per_sample = (int32_t)u16(34);
+    if (info->audio_format != 1 || info->channels < 1 || info->bits_per_sample < 8) return SJ_EINVAL;
+    // the reference reads 16 bytes of fmt and expects the next chunk header right after them; a longer fmt
+    // chunk (fmt_size > 16) would make it misparse -- here the declared size is honoured
+    size_t o = 20 + (fmt_size < 16 ? 16 : fmt_size);
+    o += fmt_size & 1;
+    while (o + 8 <= n && memcmp(p + o, "data", 4)) o += 8 + (size_t)u32(o + 4) + (u32(o + 4) & 1);
+    if (o + 8 > n) return SJ_EINVAL;
+    size_t data_bytes = u32(o + 4);
+    if (data_bytes > n - (o + 8)) data_bytes = n - (o + 8); // truncated file: what is there
+    info->data_offset = (int64_t)(o + 8);
+    info->data_bytes = (int64_t)data_bytes;
+    info->frames = (int64_t)(data_bytes / (size_t)(info->bits_per_sample / 8) / (size_t)info->channels);
+    return SJ_OK;
+}
+
+int scrubjay_decode_pcm16_dev(scrubjay_ctx *c, const int16_t *d_in, long frames, int channels, int policy, float *d_out)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_in || !d_out || frames < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (channels < 1 || (policy != SJ_MIX_FIRST && policy != SJ_MIX_MEAN)) return set_err(c, SJ_EINVAL, "bad channel count or policy");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, sj_launch_decode_pcm16(d_in, frames, channels, policy, d_out, c->num_sms, c->stream));
+    if (frames > 0) c->launches += 1;
+    return SJ_OK;
+}
+
 long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames)
 {
     if (n_samples <= 0 || win_frames < 1 || step_frames < 1) return 0;
@@ -273,13 +325,15 @@ int scrubjay_stream_infer_dev(scrubjay_ctx *c, const float *d_streams, long n_ch
     if (nw == 0 || n_channels == 0) return SJ_OK;
     SJ_CUDA(c, cudaSetDevice(c->device));
     SjCepstrumArgs a;
+    a.pcm16 = 0;
     a.clips = d_streams; a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
     a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
     a.chan_stride = chan_stride; a.prev_hop = d_prev_hop; a.n_windows = nw;
     a.win_frames = win_frames; a.step_frames = step_frames;
-    // work items: enough of them to keep every resident warp busy (>= 4 per warp), but long enough that the
-    // win - step frames recomputed at the head of each item stay below ~20 % of its work
-    const long want = 4L * sj_cepstrum_resident_warps(c->num_sms);
+    // work items: enough of them that the static round-robin over the resident warps ends evenly (>= 16 per
+    // warp), but long enough that the win - step frames recomputed at the head of each item stay below ~20 %
+    // of its work
+    const long want = 16L * sj_cepstrum_resident_warps(c->num_sms);
     long per_chan = (want + n_channels - 1) / n_channels;
     long k = (nw + per_chan - 1) / per_chan;
     const long k_min = 4L * (win_frames - step_frames) / step_frames;
@@ -323,9 +377,11 @@ int drain(scrubjay_ctx *c, Stage &s, int32_t *labels, float *conf, float *score,
 }
 
 // host clips -> chunked 3-stage pipeline.  do_svm = 0 computes features only.
-int run_host_batch(scrubjay_ctx *c, const float *clips, long n_clips, int n_samples, int32_t *labels, float *conf,
-                   float *score, float *feats, int do_svm)
+int run_host_batch(scrubjay_ctx *c, const void *clips_v, long n_clips, int n_samples, int32_t *labels, float *conf,
+                   float *score, float *feats, int do_svm, int pcm16 = 0)
 {
+    const unsigned char *clips = static_cast<const unsigned char *>(clips_v);
+    const size_t es = pcm16 ? 2 : 4; // bytes per sample; the staging buffers are sized for float
     SJ_CUDA(c, cudaSetDevice(c->device));
     int rc = ensure_stages(c, n_samples);
     if (rc != SJ_OK) return rc;
@@ -335,10 +391,10 @@ int run_host_batch(scrubjay_ctx *c, const float *clips, long n_clips, int n_samp
         rc = drain(c, s, labels, conf, score, feats);
         if (rc != SJ_OK) return rc;
         const long n = (n_clips - done < c->chunk_clips) ? n_clips - done : c->chunk_clips;
-        SJ_CUDA(c, cudaMemcpyAsync(s.d_clips, clips + done * (long)n_samples, (size_t)n * n_samples * 4,
+        SJ_CUDA(c, cudaMemcpyAsync(s.d_clips, clips + (size_t)done * n_samples * es, (size_t)n * n_samples * es,
                                    cudaMemcpyHostToDevice, s.stream));
         rc = launch_cepstrum(c, s.stream, s.d_clips, n, n_samples, s.d_labels, s.d_conf, s.d_score,
-                             feats ? s.d_feats : nullptr, do_svm, false);
+                             feats ? s.d_feats : nullptr, do_svm, false, pcm16);
         if (rc != SJ_OK) return rc;
         if (do_svm) {
             SJ_CUDA(c, cudaMemcpyAsync(s.h_labels, s.d_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream));
@@ -370,6 +426,15 @@ int scrubjay_infer_batch(scrubjay_ctx *c, const float *clips, long n_clips, int 
     if (!clips || !labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
     if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
     return run_host_batch(c, clips, n_clips, n_samples, labels, conf, score, feats, 1);
+}
+
+int scrubjay_infer_batch_pcm16(scrubjay_ctx *c, const int16_t *clips, long n_clips, int n_samples, int32_t *labels,
+                               float *conf, float *score, float *feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!clips || !labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    return run_host_batch(c, clips, n_clips, n_samples, labels, conf, score, feats, 1, 1);
 }
 
 int scrubjay_mfcc_stats(scrubjay_ctx *c, const float *samples, long n_samples, float out[SJ_FEAT_DIM])

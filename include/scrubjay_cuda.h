@@ -87,6 +87,33 @@ SJ_API int scrubjay_predict_batch_dev(scrubjay_ctx *ctx, const float *d_feats, l
 SJ_API int scrubjay_infer_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                              int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
 
+/* int16 PCM input: the format the reference actually reads (WAV decoded by aubio_source_do,
+ * cepstrum/scrubjay_infer.c:21,41; `data[i] / 32768` at donut-classifier/classifier.c:56-60).  Clips are
+ * [n_clips][n_samples] int16 mono; the conversion x = s / 32768 is exact and done inside the kernel, so the
+ * outputs are bit-identical to scrubjay_infer_batch* on the converted floats, at half the bytes per clip
+ * (32 008 B algorithmic).  The host form pipelines H2D -> kernel -> D2H like scrubjay_infer_batch. */
+SJ_API int scrubjay_infer_batch_pcm16_dev(scrubjay_ctx *ctx, const int16_t *d_clips, long n_clips, int n_samples,
+                                   int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+SJ_API int scrubjay_infer_batch_pcm16(scrubjay_ctx *ctx, const int16_t *clips, long n_clips, int n_samples,
+                               int32_t *labels, float *conf, float *score, float *feats);
+
+/* WAV ingest.  scrubjay_wav_parse is host-only (no GPU): it walks a RIFF/WAVE image in memory with the
+ * acceptance rules of read_wav_file (donut-classifier/classifier.c:214-306): "RIFF"/"WAVE", the "fmt " chunk
+ * first, AudioFormat 1 (PCM), then any chunks are skipped up to "data".  frames = data_bytes /
+ * (bits_per_sample / 8) / channels.  Returns SJ_OK or SJ_EINVAL (the reference returns 0 and prints). */
+typedef struct scrubjay_wav_info {
+    int32_t audio_format, channels, sample_rate, bits_per_sample;
+    int64_t data_offset, data_bytes, frames;
+} scrubjay_wav_info;
+SJ_API int scrubjay_wav_parse(const void *bytes, size_t n_bytes, scrubjay_wav_info *info);
+/* Device decode of interleaved int16 frames to mono float: policy SJ_MIX_FIRST = channel 0 / 32768
+ * (classifier.c:293-297, 56-60), SJ_MIX_MEAN = mean over channels of s / 32768 (aubio_source_do's down-mix,
+ * the input of mfcc_stats).  d_out[frames]. */
+#define SJ_MIX_FIRST 0
+#define SJ_MIX_MEAN 1
+SJ_API int scrubjay_decode_pcm16_dev(scrubjay_ctx *ctx, const int16_t *d_interleaved, long frames, int channels,
+                              int policy, float *d_out);
+
 /* Stream mode (BASELINE config 5: long continuous channels, sliding-frame cepstrum + SVM).  The reference
  * has no streaming entry point: main (cepstrum/scrubjay_infer.c:158-177) reduces a whole file to one
  * feature vector.  Here the loop body of mfcc_stats (:39-53) runs on without restarting aubio_pvoc, and the
