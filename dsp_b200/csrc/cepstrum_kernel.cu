@@ -310,6 +310,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
         double sum = 0.0, sq = 0.0;
         const int nh = sg.nh;
         Seg nxt = sg;
+        int ring_at = 0, until_emit = W - 1, win_at = 0; // STREAM bookkeeping, see below
         for (int hr = 0; hr < nh; ++hr, ++q) {
             const int slot = q & 1, ha = sg.hop0 + hr;
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
@@ -504,20 +505,27 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                     sum += dv;
                     sq += dv * dv;
                 } else {
-                    const int fr = ha - sg.f0; // frame index inside the item; window j ends at frame j*S + W-1
-                    if (lane < SJ_NCOEF) mring[(fr % W) * SJ_NCOEF + lane] = acc;
+                    // frame `fr` of the item goes to ring row fr % W; window j ends at frame j*S + W-1 (both kept
+                    // as running counters: ring_at = row to write, until_emit = frames before the next window end)
+                    if (lane < SJ_NCOEF) mring[ring_at * SJ_NCOEF + lane] = acc;
+                    ring_at = ring_at + 1 == W ? 0 : ring_at + 1; // now the oldest row
                     __syncwarp();
-                    const int e = fr - (W - 1);
-                    if (e >= 0 && e % S == 0) {
+                    if (until_emit == 0) {
                         double ws = 0.0, wq = 0.0;
-                        if (lane < SJ_NCOEF)
-                            for (int i = 1; i <= W; ++i) { // oldest frame first, like the reference's running sums
-                                const double dv = (double)mring[((fr + i) % W) * SJ_NCOEF + lane];
+                        if (lane < SJ_NCOEF) {
+                            int row = ring_at;
+                            for (int i = 0; i < W; ++i) { // oldest frame first, like the reference's running sums
+                                const double dv = (double)mring[row * SJ_NCOEF + lane];
                                 ws += dv;
                                 wq += dv * dv;
+                                row = row + 1 == W ? 0 : row + 1;
                             }
-                        emit(sg.out0 + e / S, ws, wq, W);
+                        }
+                        emit(sg.out0 + win_at, ws, wq, W);
+                        ++win_at;
+                        until_emit = S;
                     }
+                    --until_emit;
                 }
             }
         }
