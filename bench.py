@@ -312,7 +312,7 @@ def run_ours(args, rank, local_rank, world):
         peak, peak_src = measured_peak_gbs()
         achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_clip()
-        cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if args.cpu_baseline else None
+        cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if (args.cpu_baseline and world == 1) else None  # N = 1 only
         line = {
             "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,

@@ -141,3 +141,58 @@ def test_round_trip_properties_large():
     assert torch.equal(outs[0][2], outs[1][2]) and torch.equal(outs[0][1], outs[1][1])
     assert torch.equal(outs[0][2][perm], outs[2][2]) and torch.equal(outs[0][0][perm], outs[2][0])
     assert torch.isfinite(outs[0][2]).all()
+
+
+def _balanced_blob(feats, n_sv=48, seed=3):
+    """An SJSV model blob fitted to the synthetic clips so that the fused path sees BOTH labels with many
+    clips close to the decision boundary (the shipped model puts every synthetic clip deep in class 0, which
+    makes "identical labels" trivial there): Scaler = the features' own mean/std, support vectors = random
+    clips' standardised features with alternating coefficient signs, rho = minus the median score."""
+    import struct
+    rng = np.random.default_rng(seed)
+    mean = feats.mean(axis=0).astype(np.float32)
+    std = feats.std(axis=0).astype(np.float32)
+    std[std < 1e-6] = 1.0
+    z = ((feats - mean) * (1.0 / std)).astype(np.float32)
+    pick = rng.choice(len(feats), n_sv, replace=False)
+    sv = z[pick]
+    coef = np.where(np.arange(n_sv) % 2 == 0, 1.0, -1.0).astype(np.float32) * rng.uniform(0.5, 1.5, n_sv).astype(np.float32)
+    gamma = np.float32(0.025)
+    d2 = ((z[:, None, :] - sv[None, :, :]) ** 2).sum(-1)
+    s = (np.exp(-gamma * d2) * coef).sum(-1)
+    rho = np.float32(-np.median(s))
+    hdr = struct.pack("<6I4f", 0x56534A53, 1, 40, n_sv, n_sv // 2, n_sv - n_sv // 2, float(gamma), float(rho), -2.2435925, 0.017861439)
+    body = np.concatenate([mean, (1.0 / std).astype(np.float32), coef, sv.reshape(-1)]).astype("<f4").tobytes()
+    return hdr + body
+
+
+def test_labels_identical_on_a_model_that_splits_the_synthetic_clips():
+    import torch
+    import dsp_b200
+    from oracle_lib import CepstrumOracle
+    sj = _ctx()
+    n, ns = 2048, 16000
+    d = torch.empty((n, ns), dtype=torch.float32, device="cuda")
+    sj.synth_clips_dev(d, 4000, n, ns)
+    torch.cuda.synchronize()
+    clips = d.cpu().numpy()
+    _, _, _, feats = _run_dev(sj, clips)
+    loud = np.abs(clips).max(axis=1) > 0
+    blob = _balanced_blob(feats[loud])
+    sj2 = dsp_b200.ScrubJay(device=0, samplerate=16000, model_blob=blob)
+    sj2.set_stream(torch.cuda.current_stream().cuda_stream)
+    gl, gc, gs, gf = _run_dev(sj2, clips)
+    ora = CepstrumOracle(16000)
+    of = np.stack([ora.mfcc_stats(c) for c in clips])
+    res = [ora.predict(f, blob) for f in of]
+    ol = np.array([r[0] for r in res]); oc = np.array([r[1] for r in res], np.float32); os_ = np.array([r[2] for r in res], np.float32)
+    frac = gl[loud].mean()
+    assert 0.25 < frac < 0.75, "the fitted model must split the clips (got %.2f positive)" % frac
+    assert (np.abs(os_) < 0.05).sum() > 50, "and put many of them near the boundary"
+    # the score inherits the feature error (1e-4 relative on standardised features); a label may only differ
+    # where |score| is inside that band
+    assert np.abs(gs - os_).max() <= 2e-4
+    decided = np.abs(os_) >= 2e-4
+    assert np.array_equal(gl[decided], ol[decided])
+    assert (~decided).sum() <= 0.02 * n
+    assert np.abs(gc - oc)[decided].max() <= 5e-3
