@@ -24,6 +24,7 @@ HOP_SIZE = 1024
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SCRUBJAY_LIB") or os.path.join(_HERE, "libscrubjay_cuda.so")  # override: A/B builds of the same ABI
 DEFAULT_MODEL = os.path.join(_HERE, "data", "scrubjay_svm.bin")
+KEYWORD_MODEL = os.path.join(_HERE, "data", "keyword_model.bin")
 
 _lib = None
 
@@ -58,6 +59,12 @@ def load_library():
     L.scrubjay_infer_batch_pcm16.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_wav_parse.argtypes = [vp, ctypes.c_size_t, vp]
     L.scrubjay_decode_pcm16_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
+    L.scrubjay_keyword_load.argtypes = [vp, vp, ctypes.c_size_t]
+    L.scrubjay_keyword_classify_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp]
+    L.scrubjay_keyword_classify_batch.argtypes = [vp, vp, c_long, c_int, vp]
+    L.classify_signal.argtypes = [vp, c_int]
+    L.classify_signal.restype = ctypes.c_float
+    L.classify_signal_binary.argtypes = [vp, c_int, ctypes.c_float]
     L.scrubjay_stream_windows.argtypes = [c_long, c_int, c_int]
     L.scrubjay_stream_windows.restype = c_long
     L.scrubjay_stream_infer_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
@@ -232,6 +239,26 @@ class ScrubJay:
     def infer_batch_pcm16_dev(self, clips, n_clips, n_samples, labels, conf=None, score=None, feats=None):
         self._check(self._L.scrubjay_infer_batch_pcm16_dev(self._h, _ptr(clips), n_clips, n_samples, _ptr(labels),
                                                            _ptr(conf), _ptr(score), _ptr(feats)))
+
+    # ---- keyword ("stop") detector, 2fa/audio/word/c
+    def keyword_load(self, blob=None):
+        """scrubjay_keyword_load; default = the shipped export of the reference's model (data/keyword_model.bin)"""
+        if blob is None:
+            blob = open(KEYWORD_MODEL, "rb").read()
+        blob = bytes(blob)
+        self._check(self._L.scrubjay_keyword_load(self._h, blob, len(blob)))
+
+    def keyword_classify_batch_dev(self, signals, n_clips, n_samples, prob, mfcc=None, n_frames=None):
+        self._check(self._L.scrubjay_keyword_classify_batch_dev(self._h, _ptr(signals), n_clips, n_samples, _ptr(prob),
+                                                                _ptr(mfcc), _ptr(n_frames)))
+
+    def keyword_classify_batch(self, signals):
+        """signals: numpy [n_clips][n_samples] float32 (host) -> probabilities"""
+        signals = np.ascontiguousarray(signals, dtype=np.float32)
+        prob = np.empty(signals.shape[0], np.float32)
+        self._check(self._L.scrubjay_keyword_classify_batch(self._h, signals.ctypes.data, signals.shape[0],
+                                                            signals.shape[1], prob.ctypes.data))
+        return prob
 
     def decode_pcm16_dev(self, interleaved, frames, channels, policy, out):
         """interleaved int16 frames -> mono float (policy MIX_FIRST / MIX_MEAN)"""

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 #include <new>
 
@@ -12,6 +13,7 @@
 #include "cepstrum_kernel.h"
 #include "donut_kernel.h"
 #include "ingest_kernel.h"
+#include "keyword_kernel.h"
 #include "sj_tables.h"
 
 cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
@@ -51,6 +53,12 @@ struct scrubjay_ctx {
     int chunk_n_samples = 0;
     // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
     float *d_small = nullptr;
+    // keyword path (scrubjay_keyword_load): tables on the device, staging for the host form
+    KwTables *d_kw_tables = nullptr;
+    int kw_maxseg = 0;
+    float *d_kw_signals = nullptr, *d_kw_prob = nullptr;
+    size_t kw_stage_bytes = 0;
+    long kw_stage_clips = 0;
     int stream_chunk_windows = 0; // 0 = automatic work-item size of the stream mode
     // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
     void *d_donut_tables[2] = {nullptr, nullptr};
@@ -197,6 +205,7 @@ void scrubjay_destroy(scrubjay_ctx *c)
     cudaFree(c->d_small);
     cudaFree(c->d_donut_tables[0]); cudaFree(c->d_donut_tables[1]); cudaFree(c->d_donut_scratch);
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
+    cudaFree(c->d_kw_tables); cudaFree(c->d_kw_signals); cudaFree(c->d_kw_prob);
     delete c->h_tables;
     delete c;
 }
@@ -635,6 +644,100 @@ int classify(float *data, int data_size)
     if (scrubjay_donut_classify_batch(g_default_ctx, data, 1, data_size, SJ_DONUT_SYNC_F32, &label, nullptr) != SJ_OK)
         return 0;
     return (int)label;
+}
+
+/* ---- keyword ("stop") detector: 2fa/audio/word/c ------------------------------------------------ */
+
+int scrubjay_keyword_load(scrubjay_ctx *c, const void *blob, size_t bytes)
+{
+    if (!c) return SJ_EINVAL;
+    KwTables *t = new (std::nothrow) KwTables;
+    if (!t) return set_err(c, SJ_ENOMEM, "out of memory");
+    char err[256];
+    if (kw_build_tables(t, blob, bytes, err)) { delete t; return set_err(c, SJ_EMODEL, err); }
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e == cudaSuccess && !c->d_kw_tables) e = cudaMalloc(&c->d_kw_tables, sizeof(KwTables));
+    if (e == cudaSuccess) e = cudaMemcpy(c->d_kw_tables, t, sizeof(KwTables), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = kw_setup();
+    c->kw_maxseg = t->mel_maxseg;
+    delete t;
+    if (e != cudaSuccess) return set_err(c, SJ_ECUDA, "scrubjay_keyword_load", e);
+    return SJ_OK;
+}
+
+int scrubjay_keyword_classify_batch_dev(scrubjay_ctx *c, const float *d_signals, long n_clips, int n_samples,
+                                        float *d_prob, float *d_mfcc, int32_t *d_n_frames)
+{
+    if (!c) return SJ_EINVAL;
+    if (!c->d_kw_tables) return set_err(c, SJ_EMODEL, "no keyword model loaded (scrubjay_keyword_load)");
+    if (!d_signals || !d_prob || n_clips < 0 || n_samples < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    KwArgs a;
+    a.signals = d_signals; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_kw_tables;
+    a.prob = d_prob; a.mfcc = d_mfcc; a.n_frames = d_n_frames;
+    SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    SJ_CUDA(c, kw_launch(a, c->kw_maxseg, c->num_sms, c->stream));
+    SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->have_timing = true;
+    if (n_clips > 0) c->launches += 1;
+    return SJ_OK;
+}
+
+int scrubjay_keyword_classify_batch(scrubjay_ctx *c, const float *signals, long n_clips, int n_samples, float *prob)
+{
+    if (!c) return SJ_EINVAL;
+    if (!c->d_kw_tables) return set_err(c, SJ_EMODEL, "no keyword model loaded (scrubjay_keyword_load)");
+    if (!signals || !prob || n_clips < 0 || n_samples < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    const size_t per = (size_t)(n_samples > 0 ? n_samples : 1) * 4;
+    long chunk = (long)((256u << 20) / per);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_clips) chunk = n_clips;
+    if (chunk * per > c->kw_stage_bytes || chunk > c->kw_stage_clips) {
+        cudaFree(c->d_kw_signals); cudaFree(c->d_kw_prob);
+        c->d_kw_signals = c->d_kw_prob = nullptr; c->kw_stage_bytes = 0; c->kw_stage_clips = 0;
+        SJ_CUDA(c, cudaMalloc(&c->d_kw_signals, chunk * per));
+        SJ_CUDA(c, cudaMalloc(&c->d_kw_prob, (size_t)chunk * 4));
+        c->kw_stage_bytes = chunk * per; c->kw_stage_clips = chunk;
+    }
+    for (long done = 0; done < n_clips; done += chunk) {
+        const long n = n_clips - done < chunk ? n_clips - done : chunk;
+        SJ_CUDA(c, cudaMemcpyAsync(c->d_kw_signals, signals + done * (long)n_samples, (size_t)n * n_samples * 4,
+                                   cudaMemcpyHostToDevice, c->stream));
+        int rc = scrubjay_keyword_classify_batch_dev(c, c->d_kw_signals, n, n_samples, c->d_kw_prob, nullptr, nullptr);
+        if (rc != SJ_OK) return rc;
+        SJ_CUDA(c, cudaMemcpyAsync(prob + done, c->d_kw_prob, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+        SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return SJ_OK;
+}
+
+/* The reference's own entry points, same names and signatures (2fa/audio/word/c/stop_detector.h:9-15).  They run
+ * on the process-wide context; the model blob is read once from $SCRUBJAY_KEYWORD_MODEL.  On any failure the
+ * probability is 0 (the reference has no failure path). */
+float classify_signal(const float *signal, int num_samples)
+{
+    if (!g_default_ctx) {
+        const char *env = getenv("SCRUBJAY_DEVICE");
+        if (scrubjay_create(&g_default_ctx, env ? atoi(env) : 0, nullptr, 0, 16000) != SJ_OK) return 0.f;
+    }
+    if (!g_default_ctx->d_kw_tables) {
+        const char *path = getenv("SCRUBJAY_KEYWORD_MODEL");
+        FILE *f = path ? fopen(path, "rb") : nullptr;
+        if (!f) return 0.f;
+        std::vector<char> buf(1 << 20);
+        const size_t n = fread(buf.data(), 1, buf.size(), f);
+        fclose(f);
+        if (scrubjay_keyword_load(g_default_ctx, buf.data(), n) != SJ_OK) return 0.f;
+    }
+    float p = 0.f;
+    if (scrubjay_keyword_classify_batch(g_default_ctx, signal, 1, num_samples, &p) != SJ_OK) return 0.f;
+    return p;
+}
+
+int classify_signal_binary(const float *signal, int num_samples, float threshold)
+{
+    return classify_signal(signal, num_samples) > threshold ? 1 : 0;
 }
 
 } // extern "C"

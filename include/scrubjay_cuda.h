@@ -162,6 +162,24 @@ SJ_API int scrubjay_donut_classify_batch_dev(scrubjay_ctx *ctx, const float *d_c
 SJ_API int scrubjay_donut_classify_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
                                          int variant, int32_t *labels, float *detail);
 
+/* ---- keyword ("stop") detector: 2fa/audio/word/c ------------------------------------------------ */
+
+/* Loads the detector's constants (mfcc_params.h + model_params.h as an "SJKW" blob, tools/export_keyword.py;
+ * shipped as dsp_b200/data/keyword_model.bin).  Replaces the compiled-in tables of the reference. */
+SJ_API int scrubjay_keyword_load(scrubjay_ctx *ctx, const void *blob, size_t bytes);
+/* Batched classify_signal (stop_detector.c:12-55 = compute_mfcc, mfcc.c:108-232, + audio_classifier_predict,
+ * audio_classifier_inference.c:38-90) for n_clips signals [n_clips][n_samples] of 16 kHz float audio:
+ * d_prob[n] = probability of "stop".  d_mfcc (may be NULL) [n][500][13] receives compute_mfcc's frame-major
+ * output, zero beyond the frames computed; d_n_frames (may be NULL) [n] its return value. */
+SJ_API int scrubjay_keyword_classify_batch_dev(scrubjay_ctx *ctx, const float *d_signals, long n_clips, int n_samples,
+                                        float *d_prob, float *d_mfcc, int32_t *d_n_frames);
+SJ_API int scrubjay_keyword_classify_batch(scrubjay_ctx *ctx, const float *signals, long n_clips, int n_samples,
+                                    float *prob);
+/* The reference's own entry points, same names and signatures (stop_detector.h:9-15); process-wide context,
+ * model blob from $SCRUBJAY_KEYWORD_MODEL. */
+SJ_API float classify_signal(const float *signal, int num_samples);
+SJ_API int classify_signal_binary(const float *signal, int num_samples, float threshold);
+
 /* Synthetic test/bench audio generated on the device: d_out[n_clips][n_samples], a pure function of
  * (seed, first_clip + clip, sample) -- white noise floor + up to three gated chirps, ~5 % of clips
  * silent or with a silent tail.  Not a reference function; the bench's "data": "synthetic". */
