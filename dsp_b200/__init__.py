@@ -285,6 +285,8 @@ def wav_parse(data):
 
 DONUT_DESKTOP_F64 = 0  # donut-classifier/classifier.c constants, double arithmetic
 DONUT_SYNC_F32 = 1     # sync/lib/classifier.cpp constants, float arithmetic
+DONUT_REVERT_F64 = 2   # donut-classifier/revert.c = microphone/src/classifier.c constants, double arithmetic
+DONUT_MIC_F32 = 3      # microphone/src/classifier.cpp constants, float arithmetic
 
 
 def classify(data):

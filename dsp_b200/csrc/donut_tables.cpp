@@ -8,9 +8,13 @@
 
 void sj_donut_default_params(SjDonutParams *p, int variant)
 {
-    p->gap_tol = 0.05; p->min_dur = 0.15;
-    if (variant == 0) { p->lo_norm = 0.70; p->hi_norm = 0.85; p->mid_thr_db = 45.0; p->thr_mid = 75; p->thr_above = 300; p->thr_below = 100; }
-    else              { p->lo_norm = 0.65; p->hi_norm = 0.80; p->mid_thr_db = 70.0; p->thr_mid = 100; p->thr_above = 200; p->thr_below = 80; }
+    // 0 donut-classifier/classifier.c, 1 sync/lib/classifier.cpp,
+    // 2 donut-classifier/revert.c = microphone/src/classifier.c (:713, :164/169), 3 microphone/src/classifier.cpp (:79-80, :123, :448, :535)
+    p->gap_tol = 0.05; p->min_dur = 0.15; p->lo_norm = 0.70; p->hi_norm = 0.85; p->mid_thr_db = 45.0;
+    if (variant == 0)      { p->thr_mid = 75; p->thr_above = 300; p->thr_below = 100; }
+    else if (variant == 1) { p->lo_norm = 0.65; p->hi_norm = 0.80; p->mid_thr_db = 70.0; p->thr_mid = 100; p->thr_above = 200; p->thr_below = 80; }
+    else if (variant == 2) { p->gap_tol = 0.15; p->thr_mid = 50; p->thr_above = 200; p->thr_below = 200; }
+    else                   { p->thr_mid = 100; p->thr_above = 200; p->thr_below = 150; }
 }
 
 namespace {

@@ -61,8 +61,8 @@ struct scrubjay_ctx {
     long kw_stage_clips = 0;
     int stream_chunk_windows = 0; // 0 = automatic work-item size of the stream mode
     // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
-    void *d_donut_tables[2] = {nullptr, nullptr};
-    int donut_grid[2] = {0, 0};
+    void *d_donut_tables[SJ_DONUT_N_VARIANTS] = {nullptr, nullptr, nullptr, nullptr};
+    int donut_grid[SJ_DONUT_N_VARIANTS] = {0, 0, 0, 0};
     void *d_donut_scratch = nullptr;
     size_t donut_scratch_bytes = 0;
     float *d_donut_clips = nullptr; // host-path staging
@@ -203,7 +203,8 @@ void scrubjay_destroy(scrubjay_ctx *c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
-    cudaFree(c->d_donut_tables[0]); cudaFree(c->d_donut_tables[1]); cudaFree(c->d_donut_scratch);
+    for (void *t : c->d_donut_tables) cudaFree(t);
+    cudaFree(c->d_donut_scratch);
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
     cudaFree(c->d_kw_tables); cudaFree(c->d_kw_signals); cudaFree(c->d_kw_prob);
     delete c->h_tables;
@@ -523,16 +524,17 @@ void scrubjay_host_free(void *p) { cudaFreeHost(p); }
 // ------------------------------------------------------------------------------------------------
 namespace {
 
+inline bool sj_donut_variant_is_f64(int variant) { return variant == SJ_DONUT_DESKTOP_F64 || variant == SJ_DONUT_REVERT_F64; }
+
 int donut_prepare(scrubjay_ctx *c, int variant, int n_samples, int *tb_out)
 {
-    if (variant != SJ_DONUT_DESKTOP_F64 && variant != SJ_DONUT_SYNC_F32)
-        return set_err(c, SJ_EINVAL, "unknown donut variant");
+    if (variant < 0 || variant >= SJ_DONUT_N_VARIANTS) return set_err(c, SJ_EINVAL, "unknown donut variant");
     if (c->samplerate != 16000)
         return set_err(c, SJ_EINVAL, "donut path: only 16 kHz has filter coefficients (classifier.c:403-407)");
     const int tb = n_samples >= DN_WIN ? (n_samples - DN_WIN) / DN_HOP + 1 : 0;
     if (tb < 1) return set_err(c, SJ_EINVAL, "donut path: clip shorter than one 256-sample frame");
     if (tb > DN_MAX_TB) return set_err(c, SJ_EINVAL, "donut path: clip longer than 21536 samples");
-    const bool f64 = variant == SJ_DONUT_DESKTOP_F64;
+    const bool f64 = sj_donut_variant_is_f64(variant);
     if (!c->d_donut_tables[variant]) {
         SJ_CUDA(c, sj_donut_setup());
         SjDonutParams p;
@@ -570,7 +572,7 @@ int donut_launch(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samp
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tb = tb;
     a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail;
     SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-    SJ_CUDA(c, sj_launch_donut(a, variant == SJ_DONUT_DESKTOP_F64, c->donut_grid[variant], c->stream));
+    SJ_CUDA(c, sj_launch_donut(a, sj_donut_variant_is_f64(variant), c->donut_grid[variant], c->stream));
     SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->have_timing = true;
     if (n_clips > 0) c->launches += 1;

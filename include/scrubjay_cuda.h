@@ -147,6 +147,9 @@ SJ_API int scrubjay_infer_batch(scrubjay_ctx *ctx, const float *clips, long n_cl
 /* variants: which reference binary's constants and precision to follow */
 #define SJ_DONUT_DESKTOP_F64 0 /* donut-classifier/classifier.c: double, band 0.70-0.85, 45 dB, mid<75 above>300 below>100 */
 #define SJ_DONUT_SYNC_F32 1    /* sync/lib/classifier.cpp: float, band 0.65-0.80, 70 dB, mid<100 above>200 below>80 */
+#define SJ_DONUT_REVERT_F64 2  /* donut-classifier/revert.c = microphone/src/classifier.c: double, 0.70-0.85, 45 dB, gap tolerance 0.15 s, mid<50 above>200 below>200 */
+#define SJ_DONUT_MIC_F32 3     /* microphone/src/classifier.cpp: float, 0.70-0.85, 45 dB, mid<100 above>200 below>150 */
+#define SJ_DONUT_N_VARIANTS 4
 
 /* The reference's own entry point, same name and signature: sync/lib/classifier.h:19, called as
  * classify(buffer, 16000) at sync/sync.cpp:202.  Host pointer in, 1/0 out (0 also on failure, as the

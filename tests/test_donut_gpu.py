@@ -46,7 +46,7 @@ def _gpu(sj, d, variant):
 
 
 def _compare(gl, gd, ol, od, variant, sum_tol):
-    thr = {0: (300, 75, 100), 1: (200, 100, 80)}[variant]
+    thr = {0: (300, 75, 100), 1: (200, 100, 80), 2: (200, 50, 200), 3: (200, 100, 150)}[variant]
     assert np.array_equal(gd[:, 0], od[:, 0]), "midpoint counts differ on %d clips" % (gd[:, 0] != od[:, 0]).sum()
     has = od[:, 0] > 0
     diff = np.abs(gd[:, 1:] - od[:, 1:])
@@ -149,3 +149,17 @@ def test_permutation_equivariance_large():
     b = _gpu(sj, d[perm].contiguous(), dsp_b200.DONUT_SYNC_F32)
     p = perm.cpu().numpy()
     assert np.array_equal(a[0][p], b[0]) and np.array_equal(a[1][p], b[1])
+
+
+@pytest.mark.parametrize("variant,prec,tol", [(2, "f64", 1e-3), (3, "f32", 2.0)])
+def test_other_reference_variants_match_port(variant, prec, tol):
+    """revert.c / microphone/src/classifier.c (double, gap tolerance 0.15 s) and microphone/src/classifier.cpp
+    (float): same kernels, the variant's own constants"""
+    from donut_lib import DonutPort
+    sj = _ctx()
+    d = _synth(sj, 9000, 768)
+    gl, gd = _gpu(sj, d, variant)
+    ol, od = DonutPort(prec).classify_batch(d.cpu().numpy(), variant=variant)
+    mism, near = _compare(gl, gd, ol, od, variant, sum_tol=tol)
+    assert mism <= near
+    assert (od[:, 0] > 0).mean() > 0.5
