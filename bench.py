@@ -201,6 +201,11 @@ def run_ours(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     dist = None
+    # libraries (NCCL's version banner) write to stdout; the contract is ONE JSON line there, so fd 1 points at
+    # stderr until the line is printed
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         import torch.distributed as dist_mod
         dist = dist_mod
@@ -336,7 +341,10 @@ def run_ours(args, rank, local_rank, world):
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     barrier()
     sj.close()
     if dist is not None:
