@@ -34,7 +34,7 @@ namespace {
 
 constexpr int kTStride = 36;                 // row stride of the transpose plane: 144 B => conflict-free 128-bit row reads
 constexpr int kTFloats = 32 * kTStride;      // 1152 floats: transpose plane, then |X| bins 0..1024
-constexpr int kLogFloats = 64;               // 40 log-energies (+pad)
+constexpr int kLogFloats = 96;               // folded log-energies of two frames (2 x 40, +pad)
 
 // mel partial sums: generic layout 32*maxseg, fast layout 32*SJ_MEL_FAST_SLOTS, + the zero slot
 __host__ __device__ constexpr int p_floats(int maxseg)
@@ -230,6 +230,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const float4 *X4 = reinterpret_cast<const float4 *>(tb + T->mel_lo + lane * mel_ch);
     const int partner = (32 - lane) & 31;
     constexpr int PSKIP = FAST ? 4 : 0;
+    uint32_t cmb[5]; // fast layout: this lane's combine entries live in registers
+#pragma unroll
+    for (int e = 0; e < 5; ++e) cmb[e] = T->comb2[e][lane];
 
     // A work item walks `nh` consecutive hops of one clip / channel starting at hop `hop0` (-1 = the caller's
     // carried-over hop); its first `warm` hops are only loaded (they are the previous hop of the first frame).
@@ -427,19 +430,24 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 float lo = 0.f, hi = 0.f;
                 if (FAST) {
                     float *Pl = P + lane;
+                    // a chunk has at most one step per aligned group of 8 bins: the flushed sum is kept in a
+                    // register and stored once per group (a predicated store per bin costs a shared-memory
+                    // wavefront whenever any lane steps there; stale values in groups without a step are never read)
+                    float fl = 0.f;
 #pragma unroll
                     for (int b = 0; b < SJ_MEL_FAST_CH / 4; ++b) {
                         const float4 x = X4[b], wa = mw4[64 * b], wb = mw4[64 * b + 32];
-                        auto bin = [&](int i, float av, float wx, float wy) {
+                        auto bin = [&](float av, float wx, float wy) {
                             const bool step = __float_as_int(wx) < 0;
-                            if (step) Pl[(i >> 3) * 32] = lo;
+                            fl = step ? lo : fl;
                             lo = fmaf(fabsf(wx), av, step ? hi : lo);
                             hi = fmaf(wy, av, step ? 0.f : hi);
                         };
-                        bin(4 * b + 0, x.x, wa.x, wa.y);
-                        bin(4 * b + 1, x.y, wa.z, wa.w);
-                        bin(4 * b + 2, x.z, wb.x, wb.y);
-                        bin(4 * b + 3, x.w, wb.z, wb.w);
+                        bin(x.x, wa.x, wa.y);
+                        bin(x.y, wa.z, wa.w);
+                        bin(x.z, wb.x, wb.y);
+                        bin(x.w, wb.z, wb.w);
+                        if ((b & 1) || b == SJ_MEL_FAST_CH / 4 - 1) Pl[(b >> 1) * 32] = fl;
                     }
                     Pl[(SJ_MEL_FAST_SLOTS - 2) * 32] = lo;
                     Pl[(SJ_MEL_FAST_SLOTS - 1) * 32] = hi;
@@ -469,9 +477,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 if (FAST) {
 #pragma unroll
                     for (int e = 0; e < 5; ++e) {
-                        const uint32_t c = T->comb2[e][lane];
-                        e0 += P[c & 0xffffu];
-                        e1 += P[c >> 16];
+                        e0 += P[cmb[e] & 0xffffu];
+                        e1 += P[cmb[e] >> 16];
                     }
                 } else {
                     for (int e = 0; e < ncomb; ++e) {
@@ -488,23 +495,40 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 const float far0 = __shfl_sync(kFull, e0, (39 - lane) & 31); // band 39-m for m = 8..19
                 const float far1 = __shfl_sync(kFull, e1, (7 - lane) & 31);  // band 39-m for m = 0..7
                 const float far = lane < 8 ? far1 : far0;
+                // clip mode runs the DCT on two frames at a time (one read of the matrix): odd frames use row 1
+                float *lgw = lg + ((!STREAM && (hr & 1)) ? SJ_NFILT : 0);
                 if (lane < SJ_NCOEF) {
-                    lg[lane] = e0 + far;
-                    lg[SJ_NCOEF + lane] = e0 - far;
+                    lgw[lane] = e0 + far;
+                    lgw[SJ_NCOEF + lane] = e0 - far;
                 }
             }
             __syncwarp();
             // ---- DCT-II (first 20 rows) and the reference's double accumulators
-            {
+            if (!STREAM) {
+                if ((hr & 1) || hr == nh - 1) {
+                    float acc0 = 0.f, acc1 = 0.f;
+                    const float *eo = lg + (lane & 1) * SJ_NCOEF;
+#pragma unroll
+                    for (int m = 0; m < SJ_NFILT / 2; ++m) {
+                        const float d = T->dct[m][lane];
+                        acc0 = fmaf(d, eo[m], acc0);
+                        acc1 = fmaf(d, eo[SJ_NFILT + m], acc1);
+                    }
+                    const double d0 = (double)acc0; // frame hr-1 (or the unpaired last frame), then frame hr
+                    sum += d0;
+                    sq += d0 * d0;
+                    if (hr & 1) {
+                        const double d1 = (double)acc1;
+                        sum += d1;
+                        sq += d1 * d1;
+                    }
+                }
+            } else {
                 float acc = 0.f;
                 const float *eo = lg + (lane & 1) * SJ_NCOEF;
 #pragma unroll
                 for (int m = 0; m < SJ_NFILT / 2; ++m) acc = fmaf(T->dct[m][lane], eo[m], acc);
-                if (!STREAM) {
-                    const double dv = (double)acc;
-                    sum += dv;
-                    sq += dv * dv;
-                } else {
+                {
                     // frame `fr` of the item goes to ring row fr % W; window j ends at frame j*S + W-1 (both kept
                     // as running counters: ring_at = row to write, until_emit = frames before the next window end)
                     if (lane < SJ_NCOEF) mring[ring_at * SJ_NCOEF + lane] = acc;
