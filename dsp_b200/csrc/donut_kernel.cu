@@ -2,7 +2,9 @@
 // `int classify(float *data, int data_size)` (sync/lib/classifier.cpp:9-136, float) and of main in
 // donut-classifier/classifier.c:84-198 (double), for a whole batch of clips in one launch.
 //
-// Mapping.  One warp per CTA; a warp owns 16 clips at a time, lane = 2*clip + filter:
+// Mapping.  A CTA of 3 (float) or 4 (double) warps owns 16 clips at a time, i.e. 32 (clip, filter) rows, row = 2*clip + filter.
+// Warp 0 runs phase 1 (one row per lane); all warps share phase 2 (the row passes are dealt round-robin) and the
+// band-sum epilogue (clips dealt round-robin), with CTA barriers between the phases:
 //   phase 1 (IIR, lane-parallel over clips): every lane advances ITS direct-form-II recurrence
 //     (butter_bandpass_filter, classifier.c:420-446) by one spectrogram hop, sequentially in time and
 //     with the reference's exact operation order (separate multiply and add, no FMA), so the filtered
@@ -30,6 +32,10 @@
 namespace {
 
 constexpr unsigned kFull = 0xffffffffu;
+// warps per CTA.  Measured (clips/s, float / double): 1 warp 3.17 M / 1.01 M, 2: 3.93 M / 1.59 M, 3: 4.58 M / 1.65 M,
+// 4: 4.44 M / 2.57 M -- the float variant deals 16 row passes (3 warps leave room for 4 CTAs per SM), the double
+// variant 4 passes (one per warp).
+template <typename T> struct DnWarps { static constexpr int value = sizeof(T) == 8 ? 4 : 3; };
 constexpr int kRow = 264; // row stride in elements: = 8 (mod 32) floats / = 8 (mod 16) doubles => conflict-free 64/128-bit reads
 
 template <typename T> struct V2;
@@ -96,12 +102,12 @@ __device__ __forceinline__ void iir8(const T (&x)[8], T (&w)[8], const T (&a)[9]
 template <typename T> struct RowState {
     T min_in[32], max_in[32];   // min / max of a = re^2 + im^2 over the cells with Sxx > 0: inner bins 1..127 (doubled)
     T min_ed[32], max_ed[32];   // ... and the edge bins 0 and 128
-    T queue[64];                // band-sum epilogue: a values of the cells that passed the level test
+    T queue[DnWarps<T>::value][64];      // band-sum epilogue: a values of the cells that passed the level test (per warp)
     uint32_t flags[32][3];
     int n_mid[DN_CLIPS_PER_WARP];
     T mids[DN_CLIPS_PER_WARP][DN_MAX_MID];
     T mean[32];                 // per-row frame mean, summed sequentially like the reference
-    float2 xbuf[2][16 * 17];    // 16x16 transpose buffers of the exact float FFT (two frames per pass)
+    float2 xbuf[DnWarps<T>::value][2][16 * 17]; // 16x16 transpose buffers of the exact float FFT (two frames per pass, per warp)
 };
 
 __host__ __device__ constexpr int brev4(int x) { return ((x & 1) << 3) | ((x & 2) << 1) | ((x & 4) >> 1) | ((x & 8) >> 3); }
@@ -125,12 +131,12 @@ __device__ __forceinline__ void bfly(float2 &lo, float2 &hi, float u1, float u2)
 // stages 4-7 act on h inside a lane (lane = r).
 __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, int pos, int t, int tb,
                                                              const SjDonutTables<float> *tab, RowState<float> *st,
-                                                             float *scratch, int lane)
+                                                             float *scratch, int lane, int warp)
 {
     const int half = lane >> 4, h = lane & 15;
-    float2 *xb = st->xbuf[half];
+    float2 *xb = st->xbuf[warp][half];
     const float a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
-    for (int p = 0; p < 16; ++p) {
+    for (int p = warp; p < 16; p += DnWarps<float>::value) {
         const int r = 2 * p + half;
         const float *rowp = rows + r * kRow;
         const float mean = st->mean[r];
@@ -224,7 +230,7 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
 }
 
 template <typename T, bool ALIGNED>
-__global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
+__global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjDonutArgs a)
 {
     typedef typename V2<T>::type T2;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -232,13 +238,14 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
     constexpr size_t kTabBytes = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
     T *rows = reinterpret_cast<T *>(smem + kTabBytes);
     RowState<T> *st = reinterpret_cast<RowState<T> *>(rows + 32 * kRow);
-    const int lane = threadIdx.x;
+    constexpr int kDnWarps = DnWarps<T>::value;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
-        for (int i = lane; i < int(sizeof(SjDonutTables<T>) / 4); i += 32) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kDnWarps * 32) dst[i] = __ldg(src + i);
     }
-    __syncwarp();
+    __syncthreads();
 
     const int f = lane & 1, ci = lane >> 1, tb = a.tb, n_samples = a.n_samples;
     T ca[9], cb[9];
@@ -257,9 +264,11 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         T w[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) w[j] = 0;
-        st->min_in[lane] = st->min_ed[lane] = (T)INFINITY;
-        st->max_in[lane] = st->max_ed[lane] = 0;
-        st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
+        if (warp == 0) {
+            st->min_in[lane] = st->min_ed[lane] = (T)INFINITY;
+            st->max_in[lane] = st->max_ed[lane] = 0;
+            st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
+        }
         int pos = 0, sample = 0;
         // software pipeline of the input: a register ring of kPre blocks of 8 samples, each block requested
         // kPre blocks (~1 us of recurrence) before it is filtered -- one warp per CTA and a serial
@@ -269,17 +278,18 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
 #pragma unroll
         for (int j = 0; j < kPre; ++j) {
             ring[j][0] = ring[j][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ALIGNED) { // tb >= 1 guarantees 256 samples
+            if (ALIGNED && warp == 0) { // tb >= 1 guarantees 256 samples
                 ring[j][0] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j));
                 ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j + 4));
             }
         }
         T acc_cur = 0, acc_next = 0; // running sums of the current frame and of the next one (32-sample overlap)
-        __syncwarp();
+        __syncthreads();
 
         for (int t = 0; t < tb; ++t) {
-            // ---- phase 1: advance this lane's IIR by one hop (256 samples for the first frame)
+            // ---- phase 1 (warp 0): advance each lane's IIR by one hop (256 samples for the first frame)
             const int nnew = t == 0 ? DN_WIN : DN_HOP;
+            if (warp == 0)
             for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) { // 224 and 256 are multiples of 32
 #pragma unroll
                 for (int j = 0; j < kPre; ++j) {
@@ -311,17 +321,17 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
             }
             sample += nnew;
             pos = (pos + nnew) & 255; // = offset of the oldest of the 256 most recent samples = frame start
-            st->mean[lane] = div_rn(acc_cur, (T)DN_WIN);
+            if (warp == 0) st->mean[lane] = div_rn(acc_cur, (T)DN_WIN);
             acc_cur = acc_next;
             acc_next = 0;
-            __syncwarp();
+            __syncthreads();
 
-            // ---- phase 2: spectrogram column t of all 32 rows
+            // ---- phase 2 (all warps): spectrogram column t of all 32 rows, the row passes dealt round-robin
             if constexpr (sizeof(T) == 4) {
-                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane);
+                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane, warp);
             } else
             // double: 8 rows per pass, 4 lanes per row (no bit-exact FFT to follow: FFTW's order is unknown)
-            for (int bq = 0; bq < 4; ++bq) {
+            for (int bq = warp; bq < 4; bq += kDnWarps) {
                 const int r = 8 * bq + q;
                 const T *rowp = rows + r * kRow;
                 T2 v[32];
@@ -416,12 +426,12 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                     } else if ((ballot >> (4 * q)) & 0xFu) st->flags[r][t >> 5] |= 1u << (t & 31);
                 }
             }
-            __syncwarp();
+            __syncthreads(); // the rows are overwritten by the next hop; cells and row state become visible to all warps
         }
 
         // ---- epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
         const T fs = tab->fs;
-        if (lane < DN_CLIPS_PER_WARP) {
+        if (warp == 0 && lane < DN_CLIPS_PER_WARP) {
             const uint32_t *fl = st->flags[2 * lane];
             const T tol = tab->gap_tol, mind = tab->min_dur;
             int count = 0, size = 0;
@@ -447,7 +457,7 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
             }
             st->n_mid[lane] = count;
         }
-        __syncwarp();
+        __syncthreads();
 
         // ---- epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip.
         // A cell counts when its normalised dB level nv lies strictly inside (lo_norm, hi_norm)
@@ -455,7 +465,7 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
         // a_lo <= a < a_hi with per-clip thresholds found by a 32-way search over bit patterns that evaluates
         // the reference's own expression (double log10 included); the logarithm is then only taken for the
         // cells that pass, compacted through a small queue so that all 32 lanes work on passing cells.
-        for (int c2 = 0; c2 < DN_CLIPS_PER_WARP; ++c2) {
+        for (int c2 = warp; c2 < DN_CLIPS_PER_WARP; c2 += kDnWarps) { // clips dealt round-robin to the warps
             if (base + c2 >= a.n_clips) break;
             const int nm = st->n_mid[c2];
             int label = 0;
@@ -498,6 +508,7 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                     a_hi = first_true([&](T av) { return !(level(av) < hi); });
                 }
                 const T *scr = scratch + size_t(c2) * tb * DN_BINS;
+                T *qu = st->queue[warp];
                 auto box = [&](int band, T half, T midpoint) -> T {
                     const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
                     // time index search exactly as sum_intense (classifier.c:619-640), evaluated lane-parallel:
@@ -525,18 +536,18 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                         }
                         const bool pass = c < ncell && av >= a_lo && av < a_hi;
                         const unsigned bal = __ballot_sync(kFull, pass);
-                        if (pass) st->queue[nq + __popc(bal & ((1u << lane) - 1u))] = av;
+                        if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
                         nq += __popc(bal);
                         __syncwarp();
                         if (nq >= 32) {
-                            acc += (double)level(st->queue[lane]);
+                            acc += (double)level(qu[lane]);
                             nq -= 32;
                             __syncwarp();
-                            if (lane < nq) st->queue[lane] = st->queue[32 + lane];
+                            if (lane < nq) qu[lane] = qu[32 + lane];
                             __syncwarp();
                         }
                     }
-                    if (lane < nq) acc += (double)level(st->queue[lane]);
+                    if (lane < nq) acc += (double)level(qu[lane]);
                     __syncwarp();
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
@@ -559,7 +570,7 @@ __global__ void __launch_bounds__(32) donut_kernel(const SjDonutArgs a)
                 }
             }
         }
-        __syncwarp();
+        __syncthreads();
     }
 }
 
@@ -585,8 +596,8 @@ cudaError_t sj_donut_setup()
 int sj_donut_grid(int num_sms, bool f64)
 {
     int per_sm = 0;
-    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true>, 32, smem_total<double>());
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true>, 32, smem_total<float>());
+    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true>, DnWarps<double>::value * 32, smem_total<double>());
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true>, DnWarps<float>::value * 32, smem_total<float>());
     if (per_sm < 1) per_sm = 1;
     return num_sms * per_sm;
 }
@@ -603,11 +614,11 @@ cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream
     if (groups < grid) grid = (int)groups;
     const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
     if (f64) {
-        if (aligned) donut_kernel<double, true><<<grid, 32, smem_total<double>(), stream>>>(a);
-        else donut_kernel<double, false><<<grid, 32, smem_total<double>(), stream>>>(a);
+        if (aligned) donut_kernel<double, true><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);
+        else donut_kernel<double, false><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);
     } else {
-        if (aligned) donut_kernel<float, true><<<grid, 32, smem_total<float>(), stream>>>(a);
-        else donut_kernel<float, false><<<grid, 32, smem_total<float>(), stream>>>(a);
+        if (aligned) donut_kernel<float, true><<<grid, DnWarps<float>::value * 32, smem_total<float>(), stream>>>(a);
+        else donut_kernel<float, false><<<grid, DnWarps<float>::value * 32, smem_total<float>(), stream>>>(a);
     }
     return cudaGetLastError();
 }
