@@ -26,6 +26,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#define SJ_PACKED_F32 1
+#include "sj_pk.h"
 #include "fft_gen.inc"
 #include "sj_tables.h"
 #include "cepstrum_kernel.h"
@@ -152,6 +154,15 @@ __device__ constexpr float kWinS[16] = {0.f, 0.09754516100806417f, 0.19134171618
 
 // Scaler + RBF SVM + Platt for one 40-d feature vector held as z[40] (already standardised) in
 // shared memory.  All 32 lanes participate; the result is valid on every lane.
+// W_64^j = (kUntC[j], -kUntS[j]), j < 16
+__device__ constexpr float kUntC[16] = {1.f, 0.99518472667219693f, 0.98078528040323043f, 0.95694033573220882f,
+                                        0.92387953251128674f, 0.88192126434835505f, 0.83146961230254524f, 0.77301045336273699f,
+                                        0.70710678118654757f, 0.63439328416364549f, 0.55557023301960229f, 0.47139673682599781f,
+                                        0.38268343236508984f, 0.29028467725446233f, 0.19509032201612833f, 0.09801714032956077f};
+__device__ constexpr float kUntS[16] = {0.f, 0.09801714032956060f, 0.19509032201612825f, 0.29028467725446233f,
+                                        0.38268343236508978f, 0.47139673682599764f, 0.55557023301960218f, 0.63439328416364549f,
+                                        0.70710678118654746f, 0.77301045336273699f, 0.83146961230254524f, 0.88192126434835494f,
+                                        0.92387953251128674f, 0.95694033573220894f, 0.98078528040323043f, 0.99518472667219682f};
 __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, int lane)
 {
     float d0 = 0.f, d1 = 0.f;
@@ -220,11 +231,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     long item = long(blockIdx.x) * WARPS + warp;
     const int W = a.win_frames, S = a.step_frames;
     // hann[64 m1 + 2 lane + d] = 0.5 - 0.5 cos(a + b), a = 2 pi m1/32, b = pi (2 lane + d)/1024
-    float sb0, cb0, sb1, cb1;
-    sincospif((float)(2 * lane) * (1.f / 1024.f), &sb0, &cb0);
-    sincospif((float)(2 * lane + 1) * (1.f / 1024.f), &sb1, &cb1);
+    float2 sb, cb;
+    sincospif((float)(2 * lane) * (1.f / 1024.f), &sb.x, &cb.x);
+    sincospif((float)(2 * lane + 1) * (1.f / 1024.f), &sb.y, &cb.y);
     const float4 *tw4 = reinterpret_cast<const float4 *>(T->tw4) + lane;
-    const float4 *tp4 = reinterpret_cast<const float4 *>(T->tp4) + lane;
+    // untangling base u = -i W_2048^lane with its quarter turn ur = i u: W_2048^(lane + 32 j) = W_2048^lane W_64^j, and the
+    // W_64^j are immediates (this replaced a 4 KB table: 32 shared-memory wavefronts per frame)
+    const float2 ut = make_float2(T->tp4[0][lane].y, -T->tp4[0][lane].x), ur = make_float2(-ut.y, ut.x);
     const float4 *mw4 = reinterpret_cast<const float4 *>(T->melw4) + lane;
     const int mel_ch = FAST ? SJ_MEL_FAST_CH : T->mel_ch, ncomb = FAST ? 5 : T->mel_ncomb;
     const float4 *X4 = reinterpret_cast<const float4 *>(tb + T->mel_lo + lane * mel_ch);
@@ -346,19 +359,17 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
                     const float2 c = pair_at(curf, m1);
-                    const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
-                    const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
+                    const float2 w = pk_fma(pk_bc(kWinS[m1]), sb, pk_fma(pk_bc(-kWinC[m1]), cb, pk_bc(0.5f)));
                     v[m1] = make_float2(0.f, 0.f);
-                    v[m1 + 16] = make_float2(fmaf(-c.x, wx, c.x), fmaf(-c.y, wy, c.y));
+                    v[m1 + 16] = pk_fma(pk_neg(c), w, c);
                 }
             } else {
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
                     const float2 c = pair_at(curf, m1), s = pair_at(prvf, m1);
-                    const float wx = fmaf(kWinS[m1], sb0, fmaf(-kWinC[m1], cb0, 0.5f));
-                    const float wy = fmaf(kWinS[m1], sb1, fmaf(-kWinC[m1], cb1, 0.5f));
-                    v[m1] = make_float2(s.x * wx, s.y * wy);
-                    v[m1 + 16] = make_float2(fmaf(-c.x, wx, c.x), fmaf(-c.y, wy, c.y));
+                    const float2 w = pk_fma(pk_bc(kWinS[m1]), sb, pk_fma(pk_bc(-kWinC[m1]), cb, pk_bc(0.5f)));
+                    v[m1] = pk_mul(s, w);
+                    v[m1 + 16] = pk_fma(pk_neg(c), w, c);
                 }
             }
             __syncwarp();
@@ -398,24 +409,26 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
 
             // ---- untangle the real FFT: bins k = lane + 32 j and 1024 - k, j < 16 (values are 2|X|)
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) {
-                const float4 w4 = tp4[32 * jj];
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int j = 2 * jj + h;
-                    const float wx = h ? w4.z : w4.x, wy = h ? w4.w : w4.y;
-                    const float2 A = v[SJ_BREV32(j)];
-                    const float2 S = v[SJ_BREV32(31 - j)];
-                    float bx = __shfl_sync(kFull, S.x, partner), by = __shfl_sync(kFull, S.y, partner);
-                    if (lane == 0) { bx = v[SJ_BREV32((32 - j) & 31)].x; by = v[SJ_BREV32((32 - j) & 31)].y; }
-                    const float ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
-                    const float tx = fmaf(wx, dy, wy * dx), ty = fmaf(wy, dy, -wx * dx);
-                    const float xa = ex + tx, ya = ey + ty;
-                    tb[lane + 32 * j] = fast_sqrt(fmaf(xa, xa, ya * ya));
-                    if (j >= PSKIP) { // the mirrors of the first rows lie above the filterbank
-                        const float xb = ex - tx, yb = ey - ty;
-                        tb[1024 - lane - 32 * j] = fast_sqrt(fmaf(xb, xb, yb * yb));
-                    }
+            for (int j = 0; j < 16; ++j) {
+                const float2 A = v[SJ_BREV32(j)];
+                const float2 S = v[SJ_BREV32(31 - j)];
+                float bx = __shfl_sync(kFull, S.x, partner), by = __shfl_sync(kFull, S.y, partner);
+                if (lane == 0) { bx = v[SJ_BREV32((32 - j) & 31)].x; by = v[SJ_BREV32((32 - j) & 31)].y; }
+                const float2 cbar = make_float2(bx, -by);
+                const float2 e = pk_add(A, cbar);
+                float2 d = pk_sub(A, cbar);
+                // t = -i W_2048^(lane + 32 j) d = u (W_64^j d)
+                if (j) d = pk_fma(pk_bc(kUntS[j]), make_float2(d.y, -d.x), pk_mul(pk_bc(kUntC[j]), d));
+                const float2 t = pk_fma(pk_bc(d.y), ur, pk_mul(pk_bc(d.x), ut));
+                if (j >= PSKIP) { // (bin k, mirror bin 1024 - k) side by side: e +- t
+                    const float2 X = pk_fma(pk_bc(t.x), make_float2(1.f, -1.f), pk_bc(e.x));
+                    const float2 Y = pk_fma(pk_bc(t.y), make_float2(1.f, -1.f), pk_bc(e.y));
+                    const float2 m = pk_fma(Y, Y, pk_mul(X, X));
+                    tb[lane + 32 * j] = fast_sqrt(m.x);
+                    tb[1024 - lane - 32 * j] = fast_sqrt(m.y);
+                } else { // the mirrors of the first rows lie above the filterbank
+                    const float2 xa = pk_add(e, t);
+                    tb[lane + 32 * j] = fast_sqrt(fmaf(xa.x, xa.x, xa.y * xa.y));
                 }
             }
             if (lane == 0) {

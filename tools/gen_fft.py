@@ -31,6 +31,111 @@ def lit(x, dbl):
     return s if dbl else s + "f"
 
 
+def gen_packed(n, tw=False):
+    """float flavour on Blackwell's packed fp32 pipe: every butterfly works on (re, im) register pairs with
+    add/sub/fma.rn.f32x2 (SASS FADD2 / FFMA2): 2 issue slots for w in {1, -i}, 3 for a general twiddle
+    (p = cs*b + a; a' = (sn,-sn)*(b.y,b.x) + p; b' = 2a - a'), same roundings as the scalar network."""
+    bits = n.bit_length() - 1
+    out = []
+    name = "sj_fft%d%s" % (n, "tw" if tw else "")
+    if tw:
+        out.append("__device__ __forceinline__ void %s(float2 (&v)[%d], const float4 *tw) {" % (name, n))
+        out.append("    float2 t, y;")
+        for j in range(n // 2):
+            a = "v[%d]" % j
+            c = "v[%d]" % (j + n // 2)
+            out.append("    { const float4 w = tw[%d];" % (32 * j))
+            if j == 0:
+                out.append("      y = %s;" % a)
+            else:
+                out.append("      y = pk_fma(pk_bc(%s.y), make_float2(-w.y, w.x), pk_mul(pk_bc(%s.x), make_float2(w.x, w.y)));"
+                           % (a, a))
+            out.append("      t = pk_fma(pk_bc(%s.y), make_float2(-w.w, w.z), pk_fma(pk_bc(%s.x), make_float2(w.z, w.w), y));"
+                       % (c, c))
+            out.append("      %s = pk_fma(pk_bc(2.0f), y, pk_neg(t)); %s = t; }" % (c, a))
+    else:
+        out.append("__device__ __forceinline__ void %s(float2 (&v)[%d]) {" % (name, n))
+        out.append("    float2 t;")
+    half = 2 if tw else 1
+    while half < n:
+        span = 2 * half
+        for b in range(0, n, span):
+            for j in range(half):
+                a = "v[%d]" % brev(b + j, bits)
+                c = "v[%d]" % brev(b + j + half, bits)
+                if j == 0:
+                    out.append("    t = %s; %s = pk_sub(%s, t); %s = pk_add(%s, t);" % (c, c, a, a, a))
+                elif 4 * j == span:  # w = -i : w*b = (b.y, -b.x)
+                    out.append("    t = make_float2(%s.y, -%s.x); %s = pk_sub(%s, t); %s = pk_add(%s, t);"
+                               % (c, c, c, a, a, a))
+                else:
+                    ang = 2.0 * math.pi * j / span
+                    cs, sn = math.cos(ang), math.sin(ang)
+                    out.append("    t = pk_fma(make_float2(%s, %s), make_float2(%s.y, %s.x), pk_fma(pk_bc(%s), %s, %s));"
+                               % (lit(sn, False), lit(-sn, False), c, c, lit(cs, False), c, a))
+                    out.append("    %s = pk_fma(pk_bc(2.0f), %s, pk_neg(t)); %s = t;" % (c, a, a))
+        half = span
+    out.append("}")
+    return "\n".join(out)
+
+
+def gen_packed_twr(n=32):
+    """Like gen_packed(tw=True) but the pending twiddles w_m = p^m (p = this lane's base twiddle) are built
+    in registers from pw = (p, p^2, p^4, p^8, p^16) instead of being read from a 32-entry table: shared-memory
+    bandwidth binds the cepstrum kernel, packed complex multiplies are 2 issue slots each."""
+    assert n == 32
+    bits = 5
+    out = ["__device__ __forceinline__ void sj_fft32twr(float2 (&v)[32], const float2 (&pw)[5]) {",
+           "    float2 t, y, w, wh;"]
+
+    def bfly(j, wj):
+        a = "v[%d]" % j
+        c = "v[%d]" % (j + 16)
+        if wj is None:
+            out.append("    y = %s; t = pk_cadd(y, pw[4], %s);" % (a, c))
+        else:
+            out.append("    wh = pk_cmul(pw[4], %s); y = pk_cmul(%s, %s); t = pk_cadd(y, wh, %s);" % (wj, wj, a, c))
+        out.append("    %s = pk_fma(pk_bc(2.0f), y, pk_neg(t)); %s = t;" % (c, a))
+
+    bfly(0, None)
+    bfly(8, "pw[3]")
+    # i = 1..7: w_i, then w_{i+8} = p^8 w_i
+    gens = {1: "pw[0]", 2: "pw[1]", 3: "pk_cmul(pw[1], pw[0])", 4: "pw[2]", 5: "pk_cmul(pw[2], pw[0])",
+            6: "pk_cmul(pw[2], pw[1])", 7: None}
+    out.append("    float2 w3;")
+    for i in range(1, 8):
+        if i == 3:
+            out.append("    w3 = %s; w = w3;" % gens[3])
+        elif i == 7:
+            out.append("    w = pk_cmul(pw[2], w3);")
+        else:
+            out.append("    w = %s;" % gens[i])
+        bfly(i, "w")
+        out.append("    w = pk_cmul(pw[3], w);")
+        bfly(i + 8, "w")
+    half = 2
+    while half < n:
+        span = 2 * half
+        for b in range(0, n, span):
+            for j in range(half):
+                a = "v[%d]" % brev(b + j, bits)
+                c = "v[%d]" % brev(b + j + half, bits)
+                if j == 0:
+                    out.append("    t = %s; %s = pk_sub(%s, t); %s = pk_add(%s, t);" % (c, c, a, a, a))
+                elif 4 * j == span:
+                    out.append("    t = make_float2(%s.y, -%s.x); %s = pk_sub(%s, t); %s = pk_add(%s, t);"
+                               % (c, c, c, a, a, a))
+                else:
+                    ang = 2.0 * math.pi * j / span
+                    cs, sn = math.cos(ang), math.sin(ang)
+                    out.append("    t = pk_fma(make_float2(%s, %s), make_float2(%s.y, %s.x), pk_fma(pk_bc(%s), %s, %s));"
+                               % (lit(sn, False), lit(-sn, False), c, c, lit(cs, False), c, a))
+                    out.append("    %s = pk_fma(pk_bc(2.0f), %s, pk_neg(t)); %s = t;" % (c, a, a))
+        half = span
+    out.append("}")
+    return "\n".join(out)
+
+
 def gen(n, dbl, tw=False):
     """tw=True: the inputs carry a pending per-element twiddle (step 2 of a two-pass split): element n
     still has to be multiplied by w_n, read as float4 (w_n, w_{n+n/2}) from tw[n * 32].  The multiply is
@@ -97,10 +202,19 @@ def main():
         parts.append("// X[k] of sj_fft%d is found in v[SJ_BREV%d(k)]" % (n, n))
         parts.append("__host__ __device__ constexpr int SJ_BREV%d(int k) { return %s; }" % (
             n, " | ".join("(((k >> %d) & 1) << %d)" % (b, bits - 1 - b) for b in range(bits))))
+        parts.append("#ifdef SJ_PACKED_F32")
+        parts.append(gen_packed(n))
+        parts.append("#else")
         parts.append(gen(n, False))
+        parts.append("#endif")
         parts.append(gen(n, True))
         if n == 32:
+            parts.append("#ifdef SJ_PACKED_F32")
+            parts.append(gen_packed(n, tw=True))
+            parts.append(gen_packed_twr())
+            parts.append("#else")
             parts.append(gen(n, False, tw=True))
+            parts.append("#endif")
     with open(os.path.join(root, "dsp_b200", "csrc", "fft_gen.inc"), "w") as f:
         f.write("\n".join(parts) + "\n")
 
