@@ -27,6 +27,7 @@
 #include <stdint.h>
 
 #include "donut_kernel.h"
+#include "sj_pk.h"
 #include "fft_gen.inc"
 
 namespace {
@@ -113,14 +114,16 @@ template <typename T> struct RowState {
 __host__ __device__ constexpr int brev4(int x) { return ((x & 1) << 3) | ((x & 2) << 1) | ((x & 4) >> 1) | ((x & 8) >> 3); }
 
 // one butterfly of the reference's float FFT, operation for operation (PlainFFT.cpp:64-71)
+// (packed fp32 pairs: mul.rn.f32x2 / add.rn.f32x2 round each half exactly like the scalar operations and are never
+// contracted, so the ten roundings of the reference's butterfly are reproduced in five issue slots)
 __device__ __forceinline__ void bfly(float2 &lo, float2 &hi, float u1, float u2)
 {
-    const float t1 = sub_rn(mul_rn(u1, hi.x), mul_rn(u2, hi.y));
-    const float t2 = add_rn(mul_rn(u1, hi.y), mul_rn(u2, hi.x));
-    hi.x = sub_rn(lo.x, t1);
-    hi.y = sub_rn(lo.y, t2);
-    lo.x = add_rn(lo.x, t1);
-    lo.y = add_rn(lo.y, t2);
+    const float2 m1 = pk_mul(pk_bc(u1), hi);                      // (u1 hi.x, u1 hi.y)
+    const float2 m2 = pk_mul(pk_bc(u2), make_float2(hi.y, hi.x)); // (u2 hi.y, u2 hi.x)
+    // (scalar here: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2, which would drop two roundings)
+    const float2 t = make_float2(sub_rn(m1.x, m2.x), add_rn(m1.y, m2.y));
+    hi = pk_sub(lo, t);
+    lo = pk_add(lo, t);
 }
 
 // Float variant: spectrogram column t of all 32 rows with the reference's exact arithmetic

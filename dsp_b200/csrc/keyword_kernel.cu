@@ -17,6 +17,8 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#define SJ_PACKED_F32 1
+#include "sj_pk.h"
 #include "fft_gen.inc"
 #include "keyword_kernel.h"
 

@@ -30,12 +30,3 @@ __device__ __forceinline__ float2 pk_fma(float2 a, float2 b, float2 c)
 }
 __device__ __forceinline__ float2 pk_bc(float x) { return make_float2(x, x); }
 __device__ __forceinline__ float2 pk_neg(float2 a) { return make_float2(-a.x, -a.y); }
-// complex product a*b and y + a*b on (re, im) pairs: two packed operations each
-__device__ __forceinline__ float2 pk_cmul(float2 a, float2 b)
-{
-    return pk_fma(pk_bc(a.y), make_float2(-b.y, b.x), pk_mul(pk_bc(a.x), b));
-}
-__device__ __forceinline__ float2 pk_cadd(float2 y, float2 a, float2 b)
-{
-    return pk_fma(pk_bc(a.y), make_float2(-b.y, b.x), pk_fma(pk_bc(a.x), b, y));
-}

@@ -79,63 +79,6 @@ def gen_packed(n, tw=False):
     return "\n".join(out)
 
 
-def gen_packed_twr(n=32):
-    """Like gen_packed(tw=True) but the pending twiddles w_m = p^m (p = this lane's base twiddle) are built
-    in registers from pw = (p, p^2, p^4, p^8, p^16) instead of being read from a 32-entry table: shared-memory
-    bandwidth binds the cepstrum kernel, packed complex multiplies are 2 issue slots each."""
-    assert n == 32
-    bits = 5
-    out = ["__device__ __forceinline__ void sj_fft32twr(float2 (&v)[32], const float2 (&pw)[5]) {",
-           "    float2 t, y, w, wh;"]
-
-    def bfly(j, wj):
-        a = "v[%d]" % j
-        c = "v[%d]" % (j + 16)
-        if wj is None:
-            out.append("    y = %s; t = pk_cadd(y, pw[4], %s);" % (a, c))
-        else:
-            out.append("    wh = pk_cmul(pw[4], %s); y = pk_cmul(%s, %s); t = pk_cadd(y, wh, %s);" % (wj, wj, a, c))
-        out.append("    %s = pk_fma(pk_bc(2.0f), y, pk_neg(t)); %s = t;" % (c, a))
-
-    bfly(0, None)
-    bfly(8, "pw[3]")
-    # i = 1..7: w_i, then w_{i+8} = p^8 w_i
-    gens = {1: "pw[0]", 2: "pw[1]", 3: "pk_cmul(pw[1], pw[0])", 4: "pw[2]", 5: "pk_cmul(pw[2], pw[0])",
-            6: "pk_cmul(pw[2], pw[1])", 7: None}
-    out.append("    float2 w3;")
-    for i in range(1, 8):
-        if i == 3:
-            out.append("    w3 = %s; w = w3;" % gens[3])
-        elif i == 7:
-            out.append("    w = pk_cmul(pw[2], w3);")
-        else:
-            out.append("    w = %s;" % gens[i])
-        bfly(i, "w")
-        out.append("    w = pk_cmul(pw[3], w);")
-        bfly(i + 8, "w")
-    half = 2
-    while half < n:
-        span = 2 * half
-        for b in range(0, n, span):
-            for j in range(half):
-                a = "v[%d]" % brev(b + j, bits)
-                c = "v[%d]" % brev(b + j + half, bits)
-                if j == 0:
-                    out.append("    t = %s; %s = pk_sub(%s, t); %s = pk_add(%s, t);" % (c, c, a, a, a))
-                elif 4 * j == span:
-                    out.append("    t = make_float2(%s.y, -%s.x); %s = pk_sub(%s, t); %s = pk_add(%s, t);"
-                               % (c, c, c, a, a, a))
-                else:
-                    ang = 2.0 * math.pi * j / span
-                    cs, sn = math.cos(ang), math.sin(ang)
-                    out.append("    t = pk_fma(make_float2(%s, %s), make_float2(%s.y, %s.x), pk_fma(pk_bc(%s), %s, %s));"
-                               % (lit(sn, False), lit(-sn, False), c, c, lit(cs, False), c, a))
-                    out.append("    %s = pk_fma(pk_bc(2.0f), %s, pk_neg(t)); %s = t;" % (c, a, a))
-        half = span
-    out.append("}")
-    return "\n".join(out)
-
-
 def gen(n, dbl, tw=False):
     """tw=True: the inputs carry a pending per-element twiddle (step 2 of a two-pass split): element n
     still has to be multiplied by w_n, read as float4 (w_n, w_{n+n/2}) from tw[n * 32].  The multiply is
@@ -211,7 +154,6 @@ def main():
         if n == 32:
             parts.append("#ifdef SJ_PACKED_F32")
             parts.append(gen_packed(n, tw=True))
-            parts.append(gen_packed_twr())
             parts.append("#else")
             parts.append(gen(n, False, tw=True))
             parts.append("#endif")
