@@ -29,6 +29,12 @@ KEYWORD_MODEL = os.path.join(_HERE, "data", "keyword_model.bin")
 _lib = None
 
 
+F32, F64 = 0, 1                  # element type of the donut stage functions
+IIR_EXACT, IIR_SCAN = 0, 1       # one recurrence per lane (bit-identical) / block-wise state-space scan over time
+BUTTER_16K, BUTTER_48K_DESIGN = 0, 1
+DONUT_MAX_MID = 8
+
+
 class ScrubJayError(RuntimeError):
     pass
 
@@ -76,6 +82,25 @@ def load_library():
     L.scrubjay_donut_classify_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.scrubjay_donut_classify_batch.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.classify.argtypes = [vp, c_int]
+    L.scrubjay_donut_midpoints_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp, vp]
+    L.butter_bandpass.argtypes = [ctypes.c_float, ctypes.c_float, vp, vp]
+    L.butter_bandpass.restype = ctypes.c_bool
+    L.scrubjay_butter_bandpass_f64.argtypes = [ctypes.c_double, ctypes.c_double, c_int, vp, vp]
+    L.scrubjay_butter_filter_batch_dev.argtypes = [vp, vp, vp, c_long, c_long, c_long, c_int, vp, vp, vp, c_int]
+    L.scrubjay_butter_filter_batch.argtypes = [vp, vp, vp, c_long, c_long, c_int, vp, vp, c_int]
+    L.butter_bandpass_filter.argtypes = [vp, c_int, vp, vp, vp]
+    L.butter_bandpass_filter.restype = None
+    L.scrubjay_spectrogram_frames.argtypes = [c_long, c_int]
+    L.scrubjay_spectrogram_frames.restype = c_long
+    L.scrubjay_spectrogram_batch_dev.argtypes = [vp, vp, c_long, c_long, c_long, c_int, c_int, c_int, vp]
+    L.scrubjay_spectrogram_batch.argtypes = [vp, vp, c_long, c_long, c_int, c_int, c_int, vp]
+    fpp = ctypes.POINTER(ctypes.POINTER(ctypes.c_float))
+    L.compute_spectrogram.argtypes = [vp, c_int, c_int, fpp, fpp, ctypes.POINTER(fpp), ctypes.POINTER(c_int), ctypes.POINTER(c_int)]
+    L.compute_spectrogram.restype = None
+    L.find_midpoints.argtypes = [vp, c_int, c_int, ctypes.POINTER(c_int)]
+    L.find_midpoints.restype = ctypes.POINTER(ctypes.c_float)
+    L.sum_intense.argtypes = [ctypes.c_float, ctypes.c_float, ctypes.c_float, vp, c_int, vp, c_int, vp, ctypes.c_float]
+    L.sum_intense.restype = ctypes.c_float
     L.scrubjay_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
     L.scrubjay_host_free.argtypes = [vp]
     L.scrubjay_host_free.restype = None
@@ -196,6 +221,51 @@ class ScrubJay:
                                                           labels.ctypes.data, detail.ctypes.data))
         return labels, detail
 
+    def donut_midpoints_batch_dev(self, d_clips, n_clips, n_samples, variant, d_labels, d_detail, d_mids):
+        self._check(self._L.scrubjay_donut_midpoints_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, variant,
+                                                               _ptr(d_labels), _ptr(d_detail), _ptr(d_mids)))
+
+    # ---- donut stage functions (sync/lib/classifier.h:14-18)
+    def butter_filter_batch_dev(self, d_in, d_out, n_signals, n_samples, stride, precision, b, a, d_state=None,
+                                mode=IIR_EXACT):
+        dt = np.float64 if precision == F64 else np.float32
+        b = np.ascontiguousarray(b, dtype=dt)
+        a = np.ascontiguousarray(a, dtype=dt)
+        self._check(self._L.scrubjay_butter_filter_batch_dev(self._h, _ptr(d_in), _ptr(d_out), n_signals, n_samples,
+                                                             stride, precision, b.ctypes.data, a.ctypes.data,
+                                                             _ptr(d_state), mode))
+
+    def butter_filter_batch(self, signals, b, a, mode=IIR_EXACT):
+        """host signals [n][n_samples] float32 or float64 -> filtered array of the same shape and type"""
+        signals = np.ascontiguousarray(signals)
+        if signals.dtype not in (np.float32, np.float64):
+            signals = signals.astype(np.float32)
+        precision = F64 if signals.dtype == np.float64 else F32
+        b = np.ascontiguousarray(b, dtype=signals.dtype)
+        a = np.ascontiguousarray(a, dtype=signals.dtype)
+        n, ns = signals.shape
+        out = np.empty_like(signals)
+        self._check(self._L.scrubjay_butter_filter_batch(self._h, signals.ctypes.data, out.ctypes.data, n, ns, precision,
+                                                         b.ctypes.data, a.ctypes.data, mode))
+        return out
+
+    def spectrogram_batch_dev(self, d_signals, n_signals, n_samples, stride, precision, nperseg, fs, d_sxx):
+        self._check(self._L.scrubjay_spectrogram_batch_dev(self._h, _ptr(d_signals), n_signals, n_samples, stride,
+                                                           precision, nperseg, fs, _ptr(d_sxx)))
+
+    def spectrogram_batch(self, signals, nperseg=256, fs=16000):
+        """host signals [n][n_samples] float32/float64 -> Sxx [n][nperseg/2+1][frames] (the reference's Sxx[f][t])"""
+        signals = np.ascontiguousarray(signals)
+        if signals.dtype not in (np.float32, np.float64):
+            signals = signals.astype(np.float32)
+        precision = F64 if signals.dtype == np.float64 else F32
+        n, ns = signals.shape
+        frames = spectrogram_frames(ns, nperseg)
+        out = np.empty((n, nperseg // 2 + 1, frames), signals.dtype)
+        self._check(self._L.scrubjay_spectrogram_batch(self._h, signals.ctypes.data, n, ns, precision, nperseg, fs,
+                                                       out.ctypes.data))
+        return out
+
     # ---- host-pointer entry points (numpy in, numpy out)
     def mfcc_stats(self, samples):
         x = np.ascontiguousarray(samples, dtype=np.float32)
@@ -293,6 +363,82 @@ def classify(data):
     """int classify(float *data, int data_size) -- sync/lib/classifier.h:19, same symbol name"""
     x = np.ascontiguousarray(data, dtype=np.float32)
     return int(load_library().classify(x.ctypes.data, x.size))
+
+
+def butter_bandpass(lowcut, highcut, design=BUTTER_16K, dtype=np.float32):
+    """butter_bandpass (classifier.h:14 / classifier.c:319-409): (b, a) or None for an unknown band"""
+    L = load_library()
+    if dtype == np.float32 and design == BUTTER_16K:
+        b, a = np.zeros(9, np.float32), np.zeros(9, np.float32)
+        return (b, a) if L.butter_bandpass(lowcut, highcut, b.ctypes.data, a.ctypes.data) else None
+    b, a = np.zeros(9, np.float64), np.zeros(9, np.float64)
+    if L.scrubjay_butter_bandpass_f64(lowcut, highcut, design, b.ctypes.data, a.ctypes.data) != 0:
+        return None
+    return b.astype(dtype), a.astype(dtype)
+
+
+def butter_bandpass_filter(data, b, a):
+    """void butter_bandpass_filter(float*, int, float*, float*, float*) -- classifier.h:15, same symbol name"""
+    x = np.ascontiguousarray(data, dtype=np.float32)
+    b = np.ascontiguousarray(b, dtype=np.float32)
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    out = np.zeros_like(x)
+    load_library().butter_bandpass_filter(x.ctypes.data, x.size, b.ctypes.data, a.ctypes.data, out.ctypes.data)
+    return out
+
+
+def spectrogram_frames(n_samples, nperseg=256):
+    return int(load_library().scrubjay_spectrogram_frames(n_samples, nperseg))
+
+
+def compute_spectrogram(signal, fs=16000):
+    """compute_spectrogram (classifier.h:16) through the reference's own pointer-to-pointer interface:
+    returns (frequencies, times, Sxx[f][t]) and frees the malloc'd arrays like the reference's caller does."""
+    L = load_library()
+    x = np.ascontiguousarray(signal, dtype=np.float32)
+    fp = ctypes.POINTER(ctypes.c_float)
+    fr, tm, S = fp(), fp(), ctypes.POINTER(fp)()
+    nb, nt = ctypes.c_int(0), ctypes.c_int(0)
+    L.compute_spectrogram(x.ctypes.data, x.size, fs, ctypes.byref(fr), ctypes.byref(tm), ctypes.byref(S),
+                          ctypes.byref(nb), ctypes.byref(nt))
+    if nb.value == 0:
+        return None
+    libc = ctypes.CDLL(None)
+    libc.free.argtypes = [ctypes.c_void_p]
+    freqs = np.ctypeslib.as_array(fr, (nb.value,)).copy()
+    times = np.ctypeslib.as_array(tm, (nt.value,)).copy()
+    sxx = np.stack([np.ctypeslib.as_array(S[i], (nt.value,)).copy() for i in range(nb.value)])
+    for i in range(nb.value):
+        libc.free(ctypes.cast(S[i], ctypes.c_void_p))
+    for p in (fr, tm, S):
+        libc.free(ctypes.cast(p, ctypes.c_void_p))
+    return freqs, times, sxx
+
+
+def find_midpoints(data, fs=16000):
+    """float *find_midpoints(float*, int, int, int*) -- classifier.h:18; returns a float32 array or None"""
+    L = load_library()
+    x = np.ascontiguousarray(data, dtype=np.float32)
+    n = ctypes.c_int(0)
+    p = L.find_midpoints(x.ctypes.data, x.size, fs, ctypes.byref(n))
+    if not p:
+        return None
+    out = np.ctypeslib.as_array(p, (max(n.value, 1),))[:n.value].copy()
+    libc = ctypes.CDLL(None)
+    libc.free.argtypes = [ctypes.c_void_p]
+    libc.free(ctypes.cast(p, ctypes.c_void_p))
+    return out
+
+
+def sum_intense(lower, upper, half_range, frequencies, times, plane, midpoint):
+    """float sum_intense(...) -- classifier.h:17; plane is [freq_bins][time_bins] float32 (NaN = filtered out)"""
+    L = load_library()
+    fr = np.ascontiguousarray(frequencies, dtype=np.float32)
+    tm = np.ascontiguousarray(times, dtype=np.float32)
+    pl = np.ascontiguousarray(plane, dtype=np.float32)
+    rows = (ctypes.c_void_p * pl.shape[0])(*[pl[i].ctypes.data for i in range(pl.shape[0])])
+    return float(L.sum_intense(lower, upper, half_range, fr.ctypes.data, fr.size, tm.ctypes.data, tm.size,
+                               ctypes.cast(rows, ctypes.c_void_p), midpoint))
 
 
 def shard_range(n_items, rank, world_size):

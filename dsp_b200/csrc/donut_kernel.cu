@@ -572,6 +572,8 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
                 }
             }
+            if (a.mids && lane < DN_MAX_MID) // find_midpoints' return array (classifier.cpp:433-598), NaN-padded
+                a.mids[(base + c2) * DN_MAX_MID + lane] = lane < nm ? (float)st->mids[c2][lane] : __int_as_float(0x7fc00000);
         }
         __syncthreads();
     }

@@ -49,6 +49,7 @@ struct SjDonutArgs {
     void *scratch;        // [grid][16][tb][129] of T: the 3000-7500 Hz PSD of the clips in flight
     int32_t *labels;      // [n_clips]
     float *detail;        // [n_clips][4] = n_midpoints, above, middle, below (last midpoint evaluated) or NULL
+    float *mids;          // [n_clips][DN_MAX_MID] midpoint times in seconds (NaN-padded) or NULL
 };
 
 // builds the tables for precision T on the host (window/twiddles/threshold exactly as the reference computes them)

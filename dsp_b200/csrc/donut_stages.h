@@ -1,0 +1,54 @@
+// donut_stages.h -- the donut classifier's stage functions as stand-alone batched kernels:
+// butter_bandpass_filter (classifier.c:420-446 / sync/lib/classifier.cpp:193-219) and compute_spectrogram
+// (classifier.c:448-592 / classifier.cpp:221-368; classifier.ino:245-395 for the 64-sample window).
+// The fused kernel (donut_kernel.cu) is the hot path; these serve the reference's public helper symbols
+// (sync/lib/classifier.h:14-18), arbitrary coefficient sets and signals of any length.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SJ_STAGE_MAX_WIN 256
+#define SJ_SCAN_BLOCK 256 /* samples per block of the state-space scan */
+
+template <typename T> struct SjStageTab {
+    T window[SJ_STAGE_MAX_WIN]; // first nperseg points of the (nperseg + 1)-point symmetric Tukey(0.25)
+    T tw[SJ_STAGE_MAX_WIN][2];  // radix-2 DIT twiddles: stage l, butterfly offset m at index (2^l - 1) + m
+    T U;                        // fs * sum(window^2)
+    int32_t nperseg, hop, bins, pad;
+};
+
+// float: the twiddle sequence of PlainFFT::Compute (bit-exact replay); double: cos/sin evaluated in double
+void sj_stage_build_tab_f32(SjStageTab<float> *t, int nperseg, int fs);
+void sj_stage_build_tab_f64(SjStageTab<double> *t, int nperseg, int fs);
+
+// 8 x 8 transition matrix of the zero-input recurrence over `steps` samples (state k = w0 at time n-1-k), row-major
+void sj_stage_transition(const double a[9], int steps, double M[64]);
+
+struct SjIirArgs {
+    const void *in;   // [n_signals] rows of T, `in_stride` elements apart
+    void *out;        // same shape, `out_stride`
+    long n_signals, n_samples, in_stride, out_stride;
+    const void *coef; // device: T a[9], T b[9]
+    void *state;      // device [n_signals][8] of T, read at entry and written at exit; NULL = zero state, not returned
+    // scan mode only
+    void *blk_final;  // [n_signals][n_blocks][8] of T
+    const void *M;    // device: T M[64]
+    long n_blocks;
+};
+
+cudaError_t sj_launch_iir_exact(const SjIirArgs &a, bool f64, cudaStream_t stream);
+cudaError_t sj_launch_iir_scan(const SjIirArgs &a, bool f64, cudaStream_t stream); // 3 launches
+
+struct SjSpecArgs {
+    const void *signals; // [n_signals] rows of T, `stride` elements apart
+    long n_signals, n_samples, stride;
+    int frames;          // (n_samples - nperseg) / hop + 1
+    const void *tab;     // SjStageTab<T> on the device
+    void *sxx;           // [n_signals][bins][frames] of T (the reference's Sxx[f][t] per signal)
+};
+cudaError_t sj_stage_setup();
+cudaError_t sj_launch_spectrogram(const SjSpecArgs &a, bool f64, int nperseg, cudaStream_t stream);
+
+// sum_intense (classifier.cpp:370-431) on a dense [bins][frames] float plane, one thread, the reference's order
+cudaError_t sj_launch_sum_intense(const float *d_plane, int bins, int frames, int f0, int f1, int t0, int t1,
+                                  float *d_out, cudaStream_t stream);

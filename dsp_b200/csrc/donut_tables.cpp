@@ -140,3 +140,84 @@ template <typename T, typename U> void build(SjDonutTables<T> *t, const SjDonutP
 
 void sj_donut_build_tables_f32(SjDonutTables<float> *t, const SjDonutParams &p, int fs) { build<float, uint32_t>(t, p, fs); }
 void sj_donut_build_tables_f64(SjDonutTables<double> *t, const SjDonutParams &p, int fs) { build<double, uint64_t>(t, p, fs); }
+
+// ---- stage tables (donut_stages.h)
+#include "donut_stages.h"
+
+namespace {
+
+template <typename T> T tukey_cos(T x);
+template <> float tukey_cos<float>(float x) { return cosf(x); }
+template <> double tukey_cos<double>(double x) { return cos(x); }
+
+// the reference's window code (classifier.cpp:263-297 / classifier.c:484-521 / classifier.ino:286-320) for any
+// window_size, alpha = 0.25; the write to window[window_size] (out of bounds in the reference) is not made
+template <typename T> void build_stage(SjStageTab<T> *t, int nperseg, int fs)
+{
+    memset(t, 0, sizeof *t);
+    t->nperseg = nperseg;
+    t->hop = nperseg - nperseg / 8;
+    t->bins = nperseg / 2 + 1;
+    const T alpha = (T)0.25, M = (T)(nperseg + 1), pi = (T)kPi;
+    const int width = (int)floor((double)(alpha * (M - (T)1) / (T)2));
+    for (int n = 0; n <= width && n < nperseg; n++)
+        t->window[n] = (T)0.5 * ((T)1 + tukey_cos<T>(pi * ((T)-1 + (T)2 * (T)n / (alpha * (M - (T)1)))));
+    for (int n = width + 1; n <= (int)(M - width - 2) && n < nperseg; n++) t->window[n] = 1;
+    for (int n = (int)(M - width - 1); n < nperseg; n++)
+        t->window[n] = (T)0.5 * ((T)1 + tukey_cos<T>(pi * ((T)-2 / alpha + (T)1 + (T)2 * (T)n / (alpha * (M - (T)1)))));
+    T u = 0;
+    for (int i = 0; i < nperseg; i++) u += t->window[i] * t->window[i];
+    t->U = u * (T)fs;
+    if (sizeof(T) == 4) {
+        // PlainFFT::Compute's run-time twiddle recurrence (sync/lib/PlainFFT.cpp:48-80), float arithmetic
+        float c1 = -1.0f, c2 = 0.0f;
+        for (int l1 = 1; l1 < nperseg; l1 <<= 1) {
+            float u1 = 1.0f, u2 = 0.0f;
+            for (int m = 0; m < l1; ++m) {
+                t->tw[l1 - 1 + m][0] = (T)u1;
+                t->tw[l1 - 1 + m][1] = (T)u2;
+                const float z = (u1 * c1) - (u2 * c2);
+                u2 = (u1 * c2) + (u2 * c1);
+                u1 = z;
+            }
+            c2 = -(float)sqrt((1.0 - c1) / 2.0);
+            c1 = (float)sqrt((1.0 + c1) / 2.0);
+        }
+    } else {
+        for (int l1 = 1; l1 < nperseg; l1 <<= 1)
+            for (int m = 0; m < l1; ++m) {
+                const double ang = kPi * m / l1;
+                t->tw[l1 - 1 + m][0] = (T)cos(ang);
+                t->tw[l1 - 1 + m][1] = (T)(-sin(ang));
+            }
+    }
+}
+
+} // namespace
+
+void sj_stage_build_tab_f32(SjStageTab<float> *t, int nperseg, int fs) { build_stage<float>(t, nperseg, fs); }
+void sj_stage_build_tab_f64(SjStageTab<double> *t, int nperseg, int fs) { build_stage<double>(t, nperseg, fs); }
+
+void sj_stage_transition(const double a[9], int steps, double M[64])
+{
+    // zero-input step: s'[0] = -sum_j a[j] s[j-1], s'[k] = s[k-1]; M = A^steps by binary powering (long double)
+    long double A[64], R[64], Tm[64];
+    for (int i = 0; i < 64; i++) { A[i] = 0; R[i] = 0; }
+    for (int j = 1; j < 9; j++) A[j - 1] = -(long double)a[j];
+    for (int k = 1; k < 8; k++) A[k * 8 + k - 1] = 1;
+    for (int i = 0; i < 8; i++) R[i * 8 + i] = 1;
+    auto mul = [&](const long double *X, const long double *Y, long double *Z) {
+        for (int i = 0; i < 8; i++)
+            for (int j = 0; j < 8; j++) {
+                long double acc = 0;
+                for (int k = 0; k < 8; k++) acc += X[i * 8 + k] * Y[k * 8 + j];
+                Z[i * 8 + j] = acc;
+            }
+    };
+    for (int e = steps; e > 0; e >>= 1) {
+        if (e & 1) { mul(R, A, Tm); memcpy(R, Tm, sizeof R); }
+        mul(A, A, Tm);
+        memcpy(A, Tm, sizeof A);
+    }
+    for (int i = 0; i < 64; i++) M[i] = (double)R[i];
+}

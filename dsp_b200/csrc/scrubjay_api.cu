@@ -12,6 +12,7 @@
 #include "../../include/scrubjay_cuda.h"
 #include "cepstrum_kernel.h"
 #include "donut_kernel.h"
+#include "donut_stages.h"
 #include "ingest_kernel.h"
 #include "keyword_kernel.h"
 #include "sj_tables.h"
@@ -70,6 +71,13 @@ struct scrubjay_ctx {
     float *d_donut_detail = nullptr;
     long donut_stage_clips = 0;
     int donut_stage_samples = 0;
+    // donut stage functions (donut_stage_api.inc)
+    bool stage_setup_done = false;
+    void *d_stage_coef = nullptr, *d_stage_M = nullptr;
+    void *d_stage_tab[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; // [precision][nperseg == 64]
+    int stage_tab_fs[2][2] = {{0, 0}, {0, 0}};
+    void *d_stage_blk = nullptr, *d_stage_in = nullptr, *d_stage_out = nullptr;
+    size_t stage_blk_bytes = 0, stage_in_bytes = 0, stage_out_bytes = 0;
 };
 
 namespace {
@@ -206,6 +214,8 @@ void scrubjay_destroy(scrubjay_ctx *c)
     for (void *t : c->d_donut_tables) cudaFree(t);
     cudaFree(c->d_donut_scratch);
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
+    cudaFree(c->d_stage_coef); cudaFree(c->d_stage_M); cudaFree(c->d_stage_blk); cudaFree(c->d_stage_in); cudaFree(c->d_stage_out);
+    for (auto &r : c->d_stage_tab) for (void *t : r) cudaFree(t);
     cudaFree(c->d_kw_tables); cudaFree(c->d_kw_signals); cudaFree(c->d_kw_prob);
     delete c->h_tables;
     delete c;
@@ -566,11 +576,11 @@ int donut_prepare(scrubjay_ctx *c, int variant, int n_samples, int *tb_out)
 }
 
 int donut_launch(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant, int tb,
-                 int32_t *d_labels, float *d_detail)
+                 int32_t *d_labels, float *d_detail, float *d_mids = nullptr)
 {
     SjDonutArgs a;
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tb = tb;
-    a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail;
+    a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail; a.mids = d_mids;
     SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     SJ_CUDA(c, sj_launch_donut(a, sj_donut_variant_is_f64(variant), c->donut_grid[variant], c->stream));
     SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
@@ -743,3 +753,5 @@ int classify_signal_binary(const float *signal, int num_samples, float threshold
 }
 
 } // extern "C"
+
+#include "donut_stage_api.inc"

@@ -22,6 +22,7 @@
 #define SCRUBJAY_CUDA_H
 
 #include <stddef.h>
+#include <stdbool.h>
 #include <stdint.h>
 
 #if defined(__GNUC__)
@@ -164,6 +165,63 @@ SJ_API int scrubjay_donut_classify_batch_dev(scrubjay_ctx *ctx, const float *d_c
                                              int n_samples, int variant, int32_t *d_labels, float *d_detail);
 SJ_API int scrubjay_donut_classify_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
                                          int variant, int32_t *labels, float *detail);
+
+/* As above, also returning find_midpoints' array (classifier.cpp:433-598 / classifier.c:657-825): d_mids
+ * [n][SJ_DONUT_MAX_MID] midpoint times in seconds, NaN-padded (d_detail[n][0] holds the count). */
+#define SJ_DONUT_MAX_MID 8
+SJ_API int scrubjay_donut_midpoints_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
+                                              int variant, int32_t *d_labels, float *d_detail, float *d_mids);
+
+/* ---- donut stage functions: the reference's public helpers (sync/lib/classifier.h:14-18; the double forms
+ * donut-classifier/classifier.c:22-28) as batched calls, plus the helpers themselves under their own names.
+ * The reference's C++ symbols are exported here with C linkage, like classify. ---------------------------- */
+#define SJ_F32 0
+#define SJ_F64 1
+#define SJ_IIR_EXACT 0 /* one recurrence per lane in the reference's operation order: bit-identical outputs */
+#define SJ_IIR_SCAN 1  /* block-wise state-space scan over time, for few long signals: rounding differs (~1e-15 rel, f64) */
+#define SJ_BUTTER_16K 0        /* the active coefficient sets, classifier.c:342-360 and :383-401 (= classifier.cpp:142-182) */
+#define SJ_BUTTER_48K_DESIGN 1 /* the commented-out sets, classifier.c:323-341 and :364-382 (they produced _postbutter.txt) */
+
+/* butter_bandpass (classifier.h:14 / classifier.cpp:138-191): table lookup for (1000,3000) and (3000,7500),
+ * false otherwise (the reference also prints "invalid bandpass range"). */
+SJ_API bool butter_bandpass(float lowcut, float highcut, float *b, float *a);
+/* double form (classifier.c:319-409) with the choice of coefficient set; SJ_OK or SJ_EINVAL */
+SJ_API int scrubjay_butter_bandpass_f64(double lowcut, double highcut, int design, double *b, double *a);
+
+/* butter_bandpass_filter (classifier.h:15 / classifier.cpp:193-219 / classifier.c:420-446) for n_signals rows of
+ * n_samples elements (rows `stride` elements apart in both arrays; element type float or double by `precision`),
+ * coefficients b[9], a[9] of the same type (host pointers).  d_state (may be NULL = zero initial state as in the
+ * reference) is [n_signals][8] elements: the delay line w[0..7] (classifier.c:422) read at entry and written back
+ * at exit, so a stream can be filtered in pieces with results identical to one call.  In place (d_out == d_in)
+ * is allowed in SJ_IIR_EXACT mode. */
+SJ_API int scrubjay_butter_filter_batch_dev(scrubjay_ctx *ctx, const void *d_in, void *d_out, long n_signals,
+                                            long n_samples, long stride, int precision, const void *b, const void *a,
+                                            void *d_state, int mode);
+SJ_API int scrubjay_butter_filter_batch(scrubjay_ctx *ctx, const void *in, void *out, long n_signals, long n_samples,
+                                        int precision, const void *b, const void *a, int mode);
+/* the reference's symbol (host pointers, one signal, zero state), run on the process-wide context */
+SJ_API void butter_bandpass_filter(float *data, int n, float *b, float *a, float *output);
+
+/* compute_spectrogram (classifier.h:16 / classifier.cpp:221-368 / classifier.c:448-592; classifier.ino:245-395 with
+ * nperseg 64): frames of nperseg samples every nperseg - nperseg/8, mean removed, periodic Tukey(0.25), PSD.
+ * d_sxx is dense [n_signals][nperseg/2 + 1][frames] (the reference's Sxx[f][t] per signal), frames =
+ * scrubjay_spectrogram_frames(n_samples, nperseg).  nperseg 256 or 64.  float: bit-identical to the reference
+ * (PlainFFT replayed operation for operation); double: ~1e-15 relative (FFTW's order is not reproducible). */
+SJ_API long scrubjay_spectrogram_frames(long n_samples, int nperseg);
+SJ_API int scrubjay_spectrogram_batch_dev(scrubjay_ctx *ctx, const void *d_signals, long n_signals, long n_samples,
+                                          long stride, int precision, int nperseg, int fs, void *d_sxx);
+SJ_API int scrubjay_spectrogram_batch(scrubjay_ctx *ctx, const void *signals, long n_signals, long n_samples,
+                                      int precision, int nperseg, int fs, void *sxx);
+/* the reference's symbol: allocates *frequencies, *times, *Sxx and each (*Sxx)[f] with malloc; the caller frees
+ * them (classifier.cpp:239-245 vs :127-133).  On failure *freq_bins = *time_bins = 0 and nothing is allocated. */
+SJ_API void compute_spectrogram(float *signal, int signal_length, int fs, float **frequencies, float **times,
+                                float ***Sxx, int *freq_bins, int *time_bins);
+/* find_midpoints (classifier.h:18 / classifier.cpp:433-598): malloc'd array of *num_midpoints times, NULL on failure */
+SJ_API float *find_midpoints(float *data, int num_frames, int samplingFreq, int *num_midpoints);
+/* sum_intense (classifier.h:17 / classifier.cpp:370-431): the index searches run on the host, the NaN-skipping
+ * sum over the box on the device in the reference's order */
+SJ_API float sum_intense(float lower, float upper, float half_range, float *frequencies, int freq_bins, float *times,
+                         int time_bins, float **intensity_dB_filtered, float midpoint);
 
 /* ---- keyword ("stop") detector: 2fa/audio/word/c ------------------------------------------------ */
 

@@ -9,6 +9,7 @@ from oracle_lib import ORACLE_DIR, build_oracle
 
 REF32 = os.path.join(ORACLE_DIR, "_ref", "libdonut_ref_f32.so")
 REF64 = os.path.join(ORACLE_DIR, "_ref", "libdonut_ref_f64.so")
+REFINO = os.path.join(ORACLE_DIR, "_ref", "libdonut_ref_ino.so")
 vp, c_int, c_long = ctypes.c_void_p, ctypes.c_int, ctypes.c_long
 
 
@@ -87,9 +88,38 @@ class DonutRef32:
         self.spec_fn = getattr(self.L, "_Z19compute_spectrogramPfiiPS_S0_PS0_PiS2_")
         self.spec_fn.argtypes = [vp, c_int, c_int, vp, vp, vp, vp, vp]
 
+        self.mid_fn = getattr(self.L, "_Z14find_midpointsPfiiPi")
+        self.mid_fn.argtypes = [vp, c_int, c_int, vp]
+        self.mid_fn.restype = ctypes.POINTER(ctypes.c_float)
+        self.sum_fn = getattr(self.L, "_Z11sum_intensefffPfiS_iPS_f")
+        self.sum_fn.argtypes = [ctypes.c_float, ctypes.c_float, ctypes.c_float, vp, c_int, vp, c_int, vp, ctypes.c_float]
+        self.sum_fn.restype = ctypes.c_float
+
     def classify(self, clip):
         x = np.ascontiguousarray(clip, np.float32).copy()
         return int(_silence_stdout(self.classify_fn, x.ctypes.data, x.size))
+
+    def filter_coef(self, x, b, a):
+        x = np.ascontiguousarray(x, np.float32).copy()
+        b = np.ascontiguousarray(b, np.float32).copy()
+        a = np.ascontiguousarray(a, np.float32).copy()
+        out = np.empty_like(x)
+        self.filter_fn(x.ctypes.data, x.size, b.ctypes.data, a.ctypes.data, out.ctypes.data)
+        return out
+
+    def midpoints(self, clip):
+        x = np.ascontiguousarray(clip, np.float32).copy()
+        n = c_int()
+        p = _silence_stdout(self.mid_fn, x.ctypes.data, x.size, 16000, ctypes.byref(n))
+        return np.array([p[i] for i in range(n.value)], np.float32)
+
+    def sum_intense(self, lower, upper, half_range, freqs, times, plane, midpoint):
+        fr = np.ascontiguousarray(freqs, np.float32)
+        tm = np.ascontiguousarray(times, np.float32)
+        pl = np.ascontiguousarray(plane, np.float32)
+        rows = (vp * pl.shape[0])(*[pl[i].ctypes.data for i in range(pl.shape[0])])
+        return float(self.sum_fn(lower, upper, half_range, fr.ctypes.data, fr.size, tm.ctypes.data, tm.size,
+                                 ctypes.cast(rows, vp), midpoint))
 
     def filter(self, x, lo, hi):
         x = np.ascontiguousarray(x, np.float32).copy()
@@ -154,6 +184,28 @@ class DonutRef64:
         n = c_int()
         p = _silence_stdout(self.L.find_midpoints, x.ctypes.data, x.size, 16000, ctypes.byref(n))
         return np.array([p[i] for i in range(n.value)])
+
+
+class DonutRefIno:
+    """donut-classifier/classifier.ino (64-sample windows) compiled as C++ against oracle/shim/ino"""
+
+    def __init__(self):
+        self.L = ctypes.CDLL(REFINO)
+        self.spec_fn = getattr(self.L, "_Z19compute_spectrogramPfiiPS_S0_PS0_PiS2_")
+        self.spec_fn.argtypes = [vp, c_int, c_int, vp, vp, vp, vp, vp]
+
+    def spectrogram(self, sig, fs=16000):
+        sig = np.ascontiguousarray(sig, np.float32).copy()
+        fr, tm, S = vp(), vp(), vp()
+        fb, tb = c_int(), c_int()
+        self.spec_fn(sig.ctypes.data, sig.size, fs, ctypes.byref(fr), ctypes.byref(tm), ctypes.byref(S),
+                     ctypes.byref(fb), ctypes.byref(tb))
+        rows = ctypes.cast(S, ctypes.POINTER(ctypes.POINTER(ctypes.c_float)))
+        return np.array([np.ctypeslib.as_array(rows[i], shape=(tb.value,)).copy() for i in range(fb.value)])
+
+
+def have_ref_ino():
+    return os.path.exists(REFINO)
 
 
 def have_ref():
