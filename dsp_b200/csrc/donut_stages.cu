@@ -206,6 +206,33 @@ __device__ __forceinline__ void bfly(double2 &lo, double2 &hi, double u1, double
     lo.y = add_rn(lo.y, t2);
 }
 
+// stages L0 .. L0+K-1 of the radix-2 DIT network on the column col[i * 32]
+template <typename T, int N, int L0, int K>
+__device__ __forceinline__ void fft_pass(typename V2<T>::type *col, const SjStageTab<T> *tab)
+{
+    typedef typename V2<T>::type T2;
+    constexpr int G = 1 << K, l1 = 1 << L0;
+#pragma unroll 2
+    for (int grp = 0; grp < N / G; ++grp) {
+        const int lo = grp & (l1 - 1), i = ((grp >> L0) << (L0 + K)) | lo; // bits [L0, L0+K) of i are zero
+        T2 e[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) e[j] = col[(i + j * l1) * 32];
+#pragma unroll
+        for (int s = 0; s < K; ++s) {
+#pragma unroll
+            for (int j = 0; j < G; ++j)
+                if (!(j & (1 << s))) {
+                    // stage L0+s pairs elements 2^(L0+s) apart; twiddle offset = (element index) mod 2^(L0+s)
+                    const int m = lo + (j & ((1 << s) - 1)) * l1, ls = l1 << s;
+                    bfly(e[j], e[j | (1 << s)], tab->tw[ls - 1 + m][0], tab->tw[ls - 1 + m][1]);
+                }
+        }
+#pragma unroll
+        for (int j = 0; j < G; ++j) col[(i + j * l1) * 32] = e[j];
+    }
+}
+
 template <int N> __host__ __device__ constexpr int log2c() { return N == 1 ? 0 : 1 + log2c<N / 2>(); }
 template <> __host__ __device__ constexpr int log2c<1>() { return 0; }
 
@@ -235,9 +262,11 @@ template <typename T, int N> __global__ void __launch_bounds__(32) spectrogram_k
         const long left = p.n_samples - (long)t * hop;
         const int valid = left < N ? (int)left : N;
         T sum = 0;
+#pragma unroll 8
         for (int i = 0; i < N; ++i) sum = add_rn(sum, i < valid ? __ldg(x + i) : (T)0);
         const T mean = div_rn(sum, (T)N);
         // detrend, window, bit-reversed placement (PlainFFT::Compute starts with the reversal)
+#pragma unroll 8
         for (int i = 0; i < N; ++i) {
             const int r = (int)(__brev((unsigned)i) >> (32 - LOG));
             T2 v;
@@ -245,19 +274,11 @@ template <typename T, int N> __global__ void __launch_bounds__(32) spectrogram_k
             v.y = 0;
             col[r * 32] = v;
         }
-        for (int l = 0; l < LOG; ++l) {
-            const int l1 = 1 << l;
-            for (int m = 0; m < l1; ++m) {
-                const T u1 = tab->tw[l1 - 1 + m][0], u2 = tab->tw[l1 - 1 + m][1];
-#pragma unroll 4
-                for (int i = m; i < N; i += 2 * l1) {
-                    T2 lo = col[i * 32], hi = col[(i + l1) * 32];
-                    bfly(lo, hi, u1, u2);
-                    col[i * 32] = lo;
-                    col[(i + l1) * 32] = hi;
-                }
-            }
-        }
+        // the butterfly network, K stages at a time on 2^K elements held in registers (3 + 3 + 2 stages for N = 256):
+        // every butterfly sees the operands and the twiddle it has in PlainFFT::Compute, only the visiting order differs
+        fft_pass<T, N, 0, 3>(col, tab);
+        fft_pass<T, N, 3, 3>(col, tab);
+        if constexpr (LOG > 6) fft_pass<T, N, 6, LOG - 6>(col, tab);
         // PSD (classifier.cpp:349-364): mag^2 / U, inner bins doubled
         T *out = reinterpret_cast<T *>(p.sxx) + s * (long)BINS * p.frames + t;
         for (int f = 0; f < BINS; ++f) {
