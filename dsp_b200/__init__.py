@@ -65,6 +65,8 @@ def load_library():
     L.scrubjay_infer_batch_pcm16.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_wav_parse.argtypes = [vp, ctypes.c_size_t, vp]
     L.scrubjay_decode_pcm16_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
+    L.scrubjay_decode_adc12_dev.argtypes = [vp, vp, c_long, vp]
+    L.scrubjay_upsample_linear_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
     L.scrubjay_keyword_load.argtypes = [vp, vp, ctypes.c_size_t]
     L.scrubjay_keyword_classify_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp]
     L.scrubjay_keyword_classify_batch.argtypes = [vp, vp, c_long, c_int, vp]
@@ -329,6 +331,14 @@ class ScrubJay:
         self._check(self._L.scrubjay_keyword_classify_batch(self._h, signals.ctypes.data, signals.shape[0],
                                                             signals.shape[1], prob.ctypes.data))
         return prob
+
+    def decode_adc12_dev(self, adc, n, out):
+        """12-bit ADC counts (uint16, device) -> float (sync/sync.cpp:236-241)"""
+        self._check(self._L.scrubjay_decode_adc12_dev(self._h, _ptr(adc), n, _ptr(out)))
+
+    def upsample_linear_dev(self, d_in, n_signals, old_size, new_size, d_out):
+        """upsampleLinear (microphone/src/microphone.cpp:55-70), batched"""
+        self._check(self._L.scrubjay_upsample_linear_dev(self._h, _ptr(d_in), n_signals, old_size, new_size, _ptr(d_out)))
 
     def decode_pcm16_dev(self, interleaved, frames, channels, policy, out):
         """interleaved int16 frames -> mono float (policy MIX_FIRST / MIX_MEAN)"""

@@ -324,6 +324,27 @@ int scrubjay_decode_pcm16_dev(scrubjay_ctx *c, const int16_t *d_in, long frames,
     return SJ_OK;
 }
 
+int scrubjay_decode_adc12_dev(scrubjay_ctx *c, const uint16_t *d_adc, long n, float *d_out)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_adc || !d_out || n < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, sj_launch_decode_adc12(d_adc, n, d_out, c->num_sms, c->stream));
+    if (n > 0) c->launches += 1;
+    return SJ_OK;
+}
+
+int scrubjay_upsample_linear_dev(scrubjay_ctx *c, const float *d_in, long n_signals, int old_size, int new_size, float *d_out)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_in || !d_out || n_signals < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (old_size < 1 || new_size < 2) return set_err(c, SJ_EINVAL, "upsample: old_size >= 1 and new_size >= 2 (the reference divides by new_size - 1)");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, sj_launch_upsample_linear(d_in, n_signals, old_size, new_size, d_out, c->num_sms, c->stream));
+    if (n_signals > 0) c->launches += 1;
+    return SJ_OK;
+}
+
 long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames)
 {
     if (n_samples <= 0 || win_frames < 1 || step_frames < 1) return 0;

@@ -114,6 +114,13 @@ SJ_API int scrubjay_wav_parse(const void *bytes, size_t n_bytes, scrubjay_wav_in
 #define SJ_MIX_MEAN 1
 SJ_API int scrubjay_decode_pcm16_dev(scrubjay_ctx *ctx, const int16_t *d_interleaved, long frames, int channels,
                               int policy, float *d_out);
+/* The firmware's ADC path in front of classify() (sync/sync.cpp:236-241): 12-bit counts -> int16 pcm = (adc - 2048) * 16
+ * -> pcm / 32768.0 as float.  d_adc[n] uint16, d_out[n] float. */
+SJ_API int scrubjay_decode_adc12_dev(scrubjay_ctx *ctx, const uint16_t *d_adc, long n, float *d_out);
+/* upsampleLinear (microphone/src/microphone.cpp:55-70) for n_signals buffers [n_signals][old_size] ->
+ * [n_signals][new_size], float arithmetic in the reference's order (no fused multiply-add). */
+SJ_API int scrubjay_upsample_linear_dev(scrubjay_ctx *ctx, const float *d_in, long n_signals, int old_size, int new_size,
+                                        float *d_out);
 
 /* Stream mode (BASELINE config 5: long continuous channels, sliding-frame cepstrum + SVM).  The reference
  * has no streaming entry point: main (cepstrum/scrubjay_infer.c:158-177) reduces a whole file to one

@@ -1,6 +1,8 @@
 """GPU tests of the int16 PCM ingest: the pcm16 entry points must be BIT-identical to the float entry points
 fed with s / 32768 (the conversion is exact), and the decode kernel must follow the two reference channel
 policies (classifier.c:293-297 channel 0; aubio's mean of channels)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -98,3 +100,49 @@ def test_decode_policies():
         for c in range(ch):
             acc = acc + x[:, c].astype(np.float32) / np.float32(32768)
         assert np.array_equal(out.cpu().numpy(), acc / np.float32(ch))
+
+
+def _ingest_oracle():
+    import ctypes
+    from oracle_lib import ORACLE_DIR, build_oracle
+    path = os.path.join(ORACLE_DIR, "libsj_oracle_f32.so")
+    if not os.path.exists(path):
+        build_oracle()
+    L = ctypes.CDLL(path)
+    L.sj_oracle_adc12.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p]
+    L.sj_oracle_upsample_linear.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    return L
+
+
+def test_adc12_decode_matches_firmware_arithmetic():
+    """sync/sync.cpp:236-241: every one of the 4096 ADC codes (and out-of-range counts, which wrap like the int16 cast)"""
+    import torch
+    sj = _ctx()
+    L = _ingest_oracle()
+    adc = np.concatenate([np.arange(4096), [4096, 5000, 65535]]).astype(np.uint16)
+    want = np.empty(adc.size, np.float32)
+    L.sj_oracle_adc12(adc.ctypes.data, adc.size, want.ctypes.data)
+    d = torch.from_numpy(adc.view(np.int16)).cuda()
+    out = torch.empty(adc.size, dtype=torch.float32, device="cuda")
+    sj.decode_adc12_dev(d, adc.size, out)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), want)
+    assert want[0] == -1.0 and want[2048] == 0.0 and want[4095] == np.float32(2047 * 16 / 32768.0)
+
+
+@pytest.mark.parametrize("old,new", [(9000, 16000), (16000, 16000), (1, 5), (7, 2), (12345, 48000)])
+def test_upsample_linear_bit_identical(old, new):
+    """microphone/src/microphone.cpp:55-70"""
+    import torch
+    sj = _ctx()
+    L = _ingest_oracle()
+    rng = np.random.default_rng(old + new)
+    x = rng.uniform(-1, 1, (6, old)).astype(np.float32)
+    want = np.empty((6, new), np.float32)
+    for i in range(6):
+        L.sj_oracle_upsample_linear(x[i].ctypes.data, old, want[i].ctypes.data, new)
+    d = torch.from_numpy(x).cuda()
+    out = torch.empty((6, new), dtype=torch.float32, device="cuda")
+    sj.upsample_linear_dev(d, 6, old, new, out)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), want)
