@@ -85,6 +85,9 @@ def load_library():
     L.scrubjay_donut_classify_batch.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.classify.argtypes = [vp, c_int]
     L.scrubjay_donut_midpoints_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp, vp]
+    L.scrubjay_donut_stream_seconds.argtypes = [c_long, c_int]
+    L.scrubjay_donut_stream_seconds.restype = c_long
+    L.scrubjay_donut_classify_streams_dev.argtypes = [vp, vp, c_long, c_long, c_long, c_int, c_int, vp, vp]
     L.butter_bandpass.argtypes = [ctypes.c_float, ctypes.c_float, vp, vp]
     L.butter_bandpass.restype = ctypes.c_bool
     L.scrubjay_butter_bandpass_f64.argtypes = [ctypes.c_double, ctypes.c_double, c_int, vp, vp]
@@ -226,6 +229,12 @@ class ScrubJay:
     def donut_midpoints_batch_dev(self, d_clips, n_clips, n_samples, variant, d_labels, d_detail, d_mids):
         self._check(self._L.scrubjay_donut_midpoints_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, variant,
                                                                _ptr(d_labels), _ptr(d_detail), _ptr(d_mids)))
+
+    def donut_classify_streams_dev(self, d_streams, n_channels, n_samples, chan_stride, variant, d_track, d_detail=None,
+                                   clip_samples=16000):
+        """per-second decision track (int8: 1 = no bird, 2 = scrub jay; sync/sync.cpp:202-203) of continuous streams"""
+        self._check(self._L.scrubjay_donut_classify_streams_dev(self._h, _ptr(d_streams), n_channels, n_samples, chan_stride,
+                                                                clip_samples, variant, _ptr(d_track), _ptr(d_detail)))
 
     # ---- donut stage functions (sync/lib/classifier.h:14-18)
     def butter_filter_batch_dev(self, d_in, d_out, n_signals, n_samples, stride, precision, b, a, d_state=None,

@@ -263,7 +263,11 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
     for (long base = long(blockIdx.x) * DN_CLIPS_PER_WARP; base < a.n_clips; base += long(gridDim.x) * DN_CLIPS_PER_WARP) {
         long clip = base + ci;
         if (clip >= a.n_clips) clip = a.n_clips - 1; // idle lanes shadow the last clip; nothing is written for them
-        const float *src = a.clips + clip * (long)n_samples;
+        // clip -> samples: contiguous clips, or second k of channel r of a stream array (sync/sync.cpp:190-203
+        // classifies every full second of the microphone stream from zero state)
+        const float *src = a.clips_per_row > 0
+                               ? a.clips + (clip / a.clips_per_row) * a.row_stride + (clip % a.clips_per_row) * (long)n_samples
+                               : a.clips + clip * (long)n_samples;
         T w[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) w[j] = 0;
@@ -566,7 +570,8 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                 }
             }
             if (lane == 0) {
-                a.labels[base + c2] = label;
+                if (a.labels) a.labels[base + c2] = label;
+                if (a.track) a.track[base + c2] = (int8_t)(label + 1); // imu_window[].classification, sync/sync.cpp:202-203
                 if (a.detail) {
                     float *d = a.detail + (base + c2) * 4;
                     d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
@@ -617,7 +622,8 @@ cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream
     if (a.n_clips <= 0) return cudaSuccess;
     long groups = (a.n_clips + DN_CLIPS_PER_WARP - 1) / DN_CLIPS_PER_WARP;
     if (groups < grid) grid = (int)groups;
-    const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0);
+    const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
+                         (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
     if (f64) {
         if (aligned) donut_kernel<double, true><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);
         else donut_kernel<double, false><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);

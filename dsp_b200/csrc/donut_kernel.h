@@ -50,6 +50,9 @@ struct SjDonutArgs {
     int32_t *labels;      // [n_clips]
     float *detail;        // [n_clips][4] = n_midpoints, above, middle, below (last midpoint evaluated) or NULL
     float *mids;          // [n_clips][DN_MAX_MID] midpoint times in seconds (NaN-padded) or NULL
+    int8_t *track;        // [n_clips] label + 1 (the firmware's per-second classification byte) or NULL
+    long row_stride;      // stream form: clip c = second (c % clips_per_row) of channel (c / clips_per_row),
+    int clips_per_row;    // channels row_stride samples apart; 0 = plain contiguous clips
 };
 
 // builds the tables for precision T on the host (window/twiddles/threshold exactly as the reference computes them)

@@ -597,11 +597,13 @@ int donut_prepare(scrubjay_ctx *c, int variant, int n_samples, int *tb_out)
 }
 
 int donut_launch(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant, int tb,
-                 int32_t *d_labels, float *d_detail, float *d_mids = nullptr)
+                 int32_t *d_labels, float *d_detail, float *d_mids = nullptr, int8_t *d_track = nullptr,
+                 long row_stride = 0, int clips_per_row = 0)
 {
     SjDonutArgs a;
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tb = tb;
     a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail; a.mids = d_mids;
+    a.track = d_track; a.row_stride = row_stride; a.clips_per_row = clips_per_row;
     SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     SJ_CUDA(c, sj_launch_donut(a, sj_donut_variant_is_f64(variant), c->donut_grid[variant], c->stream));
     SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));

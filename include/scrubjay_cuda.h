@@ -179,6 +179,17 @@ SJ_API int scrubjay_donut_classify_batch(scrubjay_ctx *ctx, const float *clips, 
 SJ_API int scrubjay_donut_midpoints_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                                               int variant, int32_t *d_labels, float *d_detail, float *d_mids);
 
+/* Decision tracks of continuous streams, the firmware's loop (sync/sync.cpp:190-212): every full block of
+ * clip_samples samples (16000 there) of every channel is classified from zero state and the result stored as the
+ * classification byte of IMUClassificationFrame (sync.cpp:49-63, :202-203): 1 = no bird, 2 = scrub jay.
+ * d_streams [n_channels] rows chan_stride samples apart; d_track [n_channels][seconds] int8, seconds =
+ * scrubjay_donut_stream_seconds(n_samples, clip_samples) (a trailing partial block is not classified, as in the
+ * firmware, which waits for a full buffer); d_detail (may be NULL) [n_channels][seconds][4] as in classify_batch. */
+SJ_API long scrubjay_donut_stream_seconds(long n_samples, int clip_samples);
+SJ_API int scrubjay_donut_classify_streams_dev(scrubjay_ctx *ctx, const float *d_streams, long n_channels, long n_samples,
+                                               long chan_stride, int clip_samples, int variant, int8_t *d_track,
+                                               float *d_detail);
+
 /* ---- donut stage functions: the reference's public helpers (sync/lib/classifier.h:14-18; the double forms
  * donut-classifier/classifier.c:22-28) as batched calls, plus the helpers themselves under their own names.
  * The reference's C++ symbols are exported here with C linkage, like classify. ---------------------------- */

@@ -163,3 +163,31 @@ def test_other_reference_variants_match_port(variant, prec, tol):
     mism, near = _compare(gl, gd, ol, od, variant, sum_tol=tol)
     assert mism <= near
     assert (od[:, 0] > 0).mean() > 0.5
+
+
+def test_stream_decision_track_equals_clip_path():
+    """sync/sync.cpp:190-212: every full second of a stream is classified from zero state; track byte = label + 1"""
+    import torch
+    import dsp_b200
+    sj = _ctx()
+    ch, secs, tail, stride = 5, 7, 4321, 7 * 16000 + 4321 + 3  # odd stride: the unaligned-load instantiation
+    clips = _synth(sj, 700, ch * secs)
+    streams = torch.zeros((ch, stride), dtype=torch.float32, device="cuda")
+    streams[:, :secs * 16000] = clips.view(ch, secs * 16000)
+    streams[:, secs * 16000:] = 0.25
+    for variant in (dsp_b200.DONUT_SYNC_F32, dsp_b200.DONUT_DESKTOP_F64):
+        labels, detail = _gpu(sj, clips, variant)
+        track = torch.zeros((ch, secs), dtype=torch.int8, device="cuda")
+        det2 = torch.empty((ch, secs, 4), dtype=torch.float32, device="cuda")
+        sj.donut_classify_streams_dev(streams, ch, secs * 16000 + tail, stride, variant, track, det2)
+        torch.cuda.synchronize()
+        assert np.array_equal(track.cpu().numpy().reshape(-1), labels.astype(np.int8) + 1)
+        assert np.array_equal(det2.cpu().numpy().reshape(-1, 4), detail)
+    # aligned stride takes the vector-load instantiation: same bits
+    s2 = torch.zeros((ch, secs * 16000 + 16), dtype=torch.float32, device="cuda")
+    s2[:, :secs * 16000] = clips.view(ch, secs * 16000)
+    track2 = torch.zeros((ch, secs), dtype=torch.int8, device="cuda")
+    sj.donut_classify_streams_dev(s2, ch, secs * 16000, secs * 16000 + 16, dsp_b200.DONUT_SYNC_F32, track2)
+    torch.cuda.synchronize()
+    labels, _ = _gpu(sj, clips, dsp_b200.DONUT_SYNC_F32)
+    assert np.array_equal(track2.cpu().numpy().reshape(-1), labels.astype(np.int8) + 1)
