@@ -43,9 +43,10 @@ __host__ __device__ constexpr int p_floats(int maxseg)
 {
     return (32 * (maxseg > SJ_MEL_FAST_SLOTS ? maxseg : SJ_MEL_FAST_SLOTS) + 4) & ~3;
 }
-__host__ __device__ constexpr int warp_floats(int maxseg)
+// per-warp shared memory in floats: the 2-slot hop ring (int16 hops need half a slot), the transpose plane, logs, partials
+__host__ __device__ constexpr int warp_floats(int maxseg, bool pcm16)
 {
-    return 2 * SJ_HOP + kTFloats + kLogFloats + p_floats(maxseg);
+    return (pcm16 ? SJ_HOP : 2 * SJ_HOP) + kTFloats + kLogFloats + p_floats(maxseg);
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -204,8 +205,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + off) + 2 * warp;
     off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
     constexpr int kRingFloats = STREAM ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0;
-    float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * (warp_floats(maxseg) + kRingFloats);
-    float *tb = wbase + 2 * SJ_HOP;   // transpose plane, later |X|
+    float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * (warp_floats(maxseg, PCM16) + kRingFloats);
+    constexpr int kSlot = PCM16 ? SJ_HOP / 2 : SJ_HOP; // floats per ring slot
+    float *tb = wbase + 2 * kSlot;    // transpose plane, later |X|
     float *lg = tb + kTFloats;        // log energies / standardised features
     float *P = lg + kLogFloats;       // mel partial sums
     float *mring = P + p_floats(maxseg); // STREAM: the last win_frames MFCC vectors, [frame % W][coef]
@@ -237,7 +239,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const float4 *tw4 = reinterpret_cast<const float4 *>(T->tw4) + lane;
     // untangling base u = -i W_2048^lane with its quarter turn ur = i u: W_2048^(lane + 32 j) = W_2048^lane W_64^j, and the
     // W_64^j are immediates (this replaced a 4 KB table: 32 shared-memory wavefronts per frame)
-    const float2 ut = make_float2(T->tp4[0][lane].y, -T->tp4[0][lane].x), ur = make_float2(-ut.y, ut.x);
+    const float2 ut = make_float2(__ldg(&a.tables->tp4[0][lane].y), -__ldg(&a.tables->tp4[0][lane].x)), ur = make_float2(-ut.y, ut.x);
     const float4 *mw4 = reinterpret_cast<const float4 *>(T->melw4) + lane;
     const int mel_ch = FAST ? SJ_MEL_FAST_CH : T->mel_ch, ncomb = FAST ? 5 : T->mel_ncomb;
     const float4 *X4 = reinterpret_cast<const float4 *>(tb + T->mel_lo + lane * mel_ch);
@@ -274,7 +276,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     auto fetch = [&](const Seg &g, int h, int slot) {
         const unsigned char *src = h < 0 ? g.prev : g.base + (long)h * SJ_HOP * ES;
         const int cnt = (h == F - 1) ? last_valid : SJ_HOP;
-        float *dst = wbase + slot * SJ_HOP;
+        float *dst = wbase + slot * kSlot;
         if (TMA) {
             if (lane == 0) {
                 fence_proxy_async();
@@ -330,7 +332,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
         for (int hr = 0; hr < nh; ++hr, ++q) {
             const int slot = q & 1, ha = sg.hop0 + hr;
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
-            float *curf = wbase + slot * SJ_HOP;
+            float *curf = wbase + slot * kSlot;
             if (ha == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
                 if (PCM16)
                     for (int i = last_valid + lane; i < SJ_HOP; i += 32) reinterpret_cast<int16_t *>(curf)[i] = 0;
@@ -343,7 +345,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 continue;
             }
             // sample pair (2m, 2m+1), m = 32*m1 + lane, of the current / previous hop as floats
-            const float *prvf = wbase + (slot ^ 1) * SJ_HOP;
+            const float *prvf = wbase + (slot ^ 1) * kSlot;
             auto pair_at = [&](const float *hop, int m1) -> float2 {
                 if (PCM16) {
                     const uint32_t w = reinterpret_cast<const uint32_t *>(hop)[32 * m1 + lane];
@@ -591,32 +593,41 @@ __global__ void __launch_bounds__(256) svm_kernel(const float *feats, long n, co
     }
 }
 
-template <int WARPS> size_t smem_bytes(int maxseg, bool stream)
+template <int WARPS> size_t smem_bytes(int maxseg, bool stream, bool pcm16)
 {
     size_t off = (kHotBytes + 127) & ~size_t(127);
     off += (size_t(WARPS) * 2 * 8 + 127) & ~size_t(127);
-    return off + size_t(WARPS) * (warp_floats(maxseg) + (stream ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0)) * sizeof(float);
+    return off + size_t(WARPS) * (warp_floats(maxseg, pcm16) + (stream ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0)) * sizeof(float);
 }
 
+// warps per CTA (one CTA per SM): what 227 KB of shared memory and 64 K registers admit per variant
 #ifndef SJ_WARPS
 #define SJ_WARPS 12
 #endif
-constexpr int kWarps = SJ_WARPS;
+#ifndef SJ_WARPS_PCM16
+#define SJ_WARPS_PCM16 SJ_WARPS
+#endif
+#ifndef SJ_WARPS_STREAM
+#define SJ_WARPS_STREAM 12
+#endif
+template <bool STREAM, bool PCM16> constexpr int warps_of() { return STREAM ? SJ_WARPS_STREAM : PCM16 ? SJ_WARPS_PCM16 : SJ_WARPS; }
 
 template <bool TMA, bool FAST, bool STREAM, bool PCM16> cudaError_t setup_one(int maxseg)
 {
-    return cudaFuncSetAttribute(cepstrum_kernel<kWarps, TMA, FAST, STREAM, PCM16>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<kWarps>(maxseg, STREAM));
+    constexpr int W = warps_of<STREAM, PCM16>();
+    return cudaFuncSetAttribute(cepstrum_kernel<W, TMA, FAST, STREAM, PCM16>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<W>(maxseg, STREAM, PCM16));
 }
 
 template <bool TMA, bool FAST, bool STREAM, bool PCM16>
 cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStream_t stream)
 {
+    constexpr int W = warps_of<STREAM, PCM16>();
     const long items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
-    long ctas = (items + kWarps - 1) / kWarps;
+    long ctas = (items + W - 1) / W;
     if (ctas > num_sms) ctas = num_sms;
-    cepstrum_kernel<kWarps, TMA, FAST, STREAM, PCM16>
-        <<<(unsigned)ctas, kWarps * 32, smem_bytes<kWarps>(maxseg, STREAM), stream>>>(a, maxseg);
+    cepstrum_kernel<W, TMA, FAST, STREAM, PCM16>
+        <<<(unsigned)ctas, W * 32, smem_bytes<W>(maxseg, STREAM, PCM16), stream>>>(a, maxseg);
     return cudaGetLastError();
 }
 
@@ -664,7 +675,7 @@ cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int n
     return launch_any<false, false>(a, h, num_sms, stream);
 }
 
-int sj_cepstrum_resident_warps(int num_sms) { return num_sms * kWarps; }
+int sj_cepstrum_resident_warps(int num_sms) { return num_sms * warps_of<true, false>(); }
 
 cudaError_t sj_launch_svm(const float *feats, long n, const SjTables *tables, int32_t *labels, float *conf,
                           float *score, cudaStream_t stream)

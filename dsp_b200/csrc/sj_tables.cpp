@@ -238,14 +238,13 @@ int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned s
             t->tw4[a][b].z = (float)cos(a1);
             t->tw4[a][b].w = (float)(-sin(a1));
         }
-    for (int jj = 0; jj < 8; ++jj)
-        for (int b = 0; b < 32; ++b) {
-            double a0 = two_pi * (b + 64 * jj) / 2048.0, a1 = two_pi * (b + 64 * jj + 32) / 2048.0;
-            t->tp4[jj][b].x = (float)cos(a0);
-            t->tp4[jj][b].y = (float)(-sin(a0));
-            t->tp4[jj][b].z = (float)cos(a1);
-            t->tp4[jj][b].w = (float)(-sin(a1));
-        }
+    for (int b = 0; b < 32; ++b) {
+        const double a0 = two_pi * b / 2048.0;
+        t->tp4[0][b].x = (float)cos(a0);
+        t->tp4[0][b].y = (float)(-sin(a0));
+        t->tp4[0][b].z = 0.f;
+        t->tp4[0][b].w = 0.f;
+    }
     if (build_mel(t, samplerate, err)) return -1;
     // aubio mfcc.c: orthonormal DCT-II over the 40 log energies, first 20 rows kept
     const double pi = two_pi / 2;

@@ -26,8 +26,6 @@ struct SjTables {
     // step-2 twiddles of the 32x32 split of the 1024-point complex FFT, paired for the merged first
     // butterfly stage: tw4[n][lane] = (W^(n*lane), W^((n+16)*lane)), W = exp(-2 pi i/1024)
     SjQuad tw4[16][32];
-    // real-FFT untangling twiddles W_2048^k for k = lane + 64 jj and k + 32
-    SjQuad tp4[8][32];
     // sparse Slaney bank, chunked: lane L owns bins mel_lo + L*mel_ch + i, i < mel_ch (mel_lo and
     // mel_ch are multiples of 4).  melw4[g][L] = (w_lo, w_hi) of bins 2g and 2g+1 of the chunk: weights
     // for filters f and f+1 where f is the lowest filter touching the bin; they carry the 0.5 that the
@@ -51,6 +49,8 @@ struct SjTables {
     float sv_coef[SJ_MAX_SV];     // zero beyond n_sv
     float gamma, rho, prob_a, prob_b;
     int32_t n_sv, pad0, pad1, pad2;
+    // real-FFT untangling base twiddles W_2048^lane = (x, y) (the kernel reads its own entry once, from global memory)
+    SjQuad tp4[1][32];
 };
 
 // Builds the tables.  Returns 0, or a negative value and a message in `err` (size >= 256).
