@@ -522,12 +522,17 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             if (!STREAM) {
                 if ((hr & 1) || hr == nh - 1) {
                     float acc0 = 0.f, acc1 = 0.f;
-                    const float *eo = lg + (lane & 1) * SJ_NCOEF;
+                    // folded log energies as 128-bit loads (two addresses per warp: even / odd coefficient lanes)
+                    const float4 *eo = reinterpret_cast<const float4 *>(lg + (lane & 1) * SJ_NCOEF);
 #pragma unroll
-                    for (int m = 0; m < SJ_NFILT / 2; ++m) {
-                        const float d = T->dct[m][lane];
-                        acc0 = fmaf(d, eo[m], acc0);
-                        acc1 = fmaf(d, eo[SJ_NFILT + m], acc1);
+                    for (int q = 0; q < SJ_NFILT / 8; ++q) {
+                        const float4 ea = eo[q], eb = eo[SJ_NFILT / 4 + q];
+                        const float d0 = T->dct[4 * q][lane], d1 = T->dct[4 * q + 1][lane];
+                        const float d2 = T->dct[4 * q + 2][lane], d3 = T->dct[4 * q + 3][lane];
+                        acc0 = fmaf(d0, ea.x, acc0); acc1 = fmaf(d0, eb.x, acc1);
+                        acc0 = fmaf(d1, ea.y, acc0); acc1 = fmaf(d1, eb.y, acc1);
+                        acc0 = fmaf(d2, ea.z, acc0); acc1 = fmaf(d2, eb.z, acc1);
+                        acc0 = fmaf(d3, ea.w, acc0); acc1 = fmaf(d3, eb.w, acc1);
                     }
                     const double d0 = (double)acc0; // frame hr-1 (or the unpaired last frame), then frame hr
                     sum += d0;
@@ -540,9 +545,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 }
             } else {
                 float acc = 0.f;
-                const float *eo = lg + (lane & 1) * SJ_NCOEF;
+                const float4 *eo = reinterpret_cast<const float4 *>(lg + (lane & 1) * SJ_NCOEF);
 #pragma unroll
-                for (int m = 0; m < SJ_NFILT / 2; ++m) acc = fmaf(T->dct[m][lane], eo[m], acc);
+                for (int q = 0; q < SJ_NFILT / 8; ++q) {
+                    const float4 ea = eo[q];
+                    acc = fmaf(T->dct[4 * q][lane], ea.x, acc);
+                    acc = fmaf(T->dct[4 * q + 1][lane], ea.y, acc);
+                    acc = fmaf(T->dct[4 * q + 2][lane], ea.z, acc);
+                    acc = fmaf(T->dct[4 * q + 3][lane], ea.w, acc);
+                }
                 {
                     // frame `fr` of the item goes to ring row fr % W; window j ends at frame j*S + W-1 (both kept
                     // as running counters: ring_at = row to write, until_emit = frames before the next window end)
