@@ -85,6 +85,7 @@ def load_library():
     L.scrubjay_donut_classify_batch.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.classify.argtypes = [vp, c_int]
     L.scrubjay_donut_midpoints_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp, vp]
+    L.scrubjay_donut_classify_long_dev.argtypes = [vp, vp, c_long, c_long, c_int, vp, vp, vp, c_int]
     L.scrubjay_donut_stream_seconds.argtypes = [c_long, c_int]
     L.scrubjay_donut_stream_seconds.restype = c_long
     L.scrubjay_donut_classify_streams_dev.argtypes = [vp, vp, c_long, c_long, c_long, c_int, c_int, vp, vp]
@@ -229,6 +230,12 @@ class ScrubJay:
     def donut_midpoints_batch_dev(self, d_clips, n_clips, n_samples, variant, d_labels, d_detail, d_mids):
         self._check(self._L.scrubjay_donut_midpoints_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, variant,
                                                                _ptr(d_labels), _ptr(d_detail), _ptr(d_mids)))
+
+    def donut_classify_long_dev(self, d_signals, n_signals, n_samples, variant, d_labels, d_detail=None, d_mids=None,
+                                max_mid=64):
+        """staged classifier: signals of any length, and DONUT_INO_F32 (64-sample windows)"""
+        self._check(self._L.scrubjay_donut_classify_long_dev(self._h, _ptr(d_signals), n_signals, n_samples, variant,
+                                                             _ptr(d_labels), _ptr(d_detail), _ptr(d_mids), max_mid))
 
     def donut_classify_streams_dev(self, d_streams, n_channels, n_samples, chan_stride, variant, d_track, d_detail=None,
                                    clip_samples=16000):
@@ -376,6 +383,7 @@ DONUT_DESKTOP_F64 = 0  # donut-classifier/classifier.c constants, double arithme
 DONUT_SYNC_F32 = 1     # sync/lib/classifier.cpp constants, float arithmetic
 DONUT_REVERT_F64 = 2   # donut-classifier/revert.c = microphone/src/classifier.c constants, double arithmetic
 DONUT_MIC_F32 = 3      # microphone/src/classifier.cpp constants, float arithmetic
+DONUT_INO_F32 = 4      # donut-classifier/classifier.ino constants, float arithmetic, 64-sample windows (staged path)
 
 
 def classify(data):

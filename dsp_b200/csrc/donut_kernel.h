@@ -17,6 +17,8 @@ struct SjDonutParams {
     double mid_thr_db;         // classifier.c:660 / classifier.cpp:436
     double gap_tol, min_dur;   // classifier.c:749-750 / classifier.cpp:523-524
     double thr_mid, thr_above, thr_below; // classifier.c:184 / classifier.cpp:109
+    double band[3][2], half[3];           // sum_intense boxes: above, middle, below (classifier.c:175-177 / classifier.ino:123-125)
+    int nperseg;                          // 256, or 64 for classifier.ino:249
 };
 
 template <typename T> struct SjDonutTables {
@@ -58,7 +60,7 @@ struct SjDonutArgs {
 // builds the tables for precision T on the host (window/twiddles/threshold exactly as the reference computes them)
 void sj_donut_build_tables_f32(SjDonutTables<float> *t, const SjDonutParams &p, int fs);
 void sj_donut_build_tables_f64(SjDonutTables<double> *t, const SjDonutParams &p, int fs);
-void sj_donut_default_params(SjDonutParams *p, int variant); // 0: classifier.c (f64 row), 1: sync/lib (f32 row)
+void sj_donut_default_params(SjDonutParams *p, int variant); // 0: classifier.c (f64 row), 1: sync/lib (f32 row), 2, 3, 4: classifier.ino
 
 // number of CTAs (1 warp each) the kernel wants for `num_sms` SMs, and scratch bytes per CTA
 int sj_donut_grid(int num_sms, bool f64);

@@ -65,8 +65,8 @@ __device__ __forceinline__ void iir_block8(const T (&x)[8], T (&r)[8], const T (
 }
 
 // run `n` samples of one signal from state w (shifted form); out may be NULL (state only)
-template <typename T, bool WRITE>
-__device__ __forceinline__ void iir_run(const T *__restrict__ in, T *__restrict__ out, long n, T (&w)[8],
+template <typename T, bool WRITE, typename IN = T>
+__device__ __forceinline__ void iir_run(const IN *__restrict__ in, T *__restrict__ out, long n, T (&w)[8],
                                         const T (&a)[9], const T (&b)[9])
 {
     T r[8];
@@ -76,7 +76,7 @@ __device__ __forceinline__ void iir_run(const T *__restrict__ in, T *__restrict_
     for (; i + 8 <= n; i += 8) {
         T x[8], y[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) x[k] = __ldg(in + i + k);
+        for (int k = 0; k < 8; ++k) x[k] = (T)__ldg(in + i + k);
         iir_block8<T>(x, r, a, b, y);
         if (WRITE) {
 #pragma unroll
@@ -86,7 +86,7 @@ __device__ __forceinline__ void iir_run(const T *__restrict__ in, T *__restrict_
 #pragma unroll
     for (int k = 0; k < 8; ++k) w[k] = r[7 - k];
     for (; i < n; ++i) {
-        const T y = iir_step<T>(__ldg(in + i), w, a, b);
+        const T y = iir_step<T>((T)__ldg(in + i), w, a, b);
         if (WRITE) out[i] = y;
     }
 }
@@ -107,8 +107,12 @@ template <typename T> __global__ void __launch_bounds__(128) iir_exact_kernel(co
     T *st = p.state ? reinterpret_cast<T *>(p.state) + s * 8 : nullptr;
 #pragma unroll
     for (int k = 0; k < 8; ++k) w[k] = st ? st[k] : (T)0;
-    iir_run<T, true>(reinterpret_cast<const T *>(p.in) + s * p.in_stride, reinterpret_cast<T *>(p.out) + s * p.out_stride,
-                     p.n_samples, w, a, b);
+    if (sizeof(T) == 8 && p.in_f32)
+        iir_run<T, true, float>(reinterpret_cast<const float *>(p.in) + s * p.in_stride,
+                                reinterpret_cast<T *>(p.out) + s * p.out_stride, p.n_samples, w, a, b);
+    else
+        iir_run<T, true>(reinterpret_cast<const T *>(p.in) + s * p.in_stride, reinterpret_cast<T *>(p.out) + s * p.out_stride,
+                         p.n_samples, w, a, b);
     if (st) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) st[k] = w[k];
@@ -306,7 +310,171 @@ __global__ void sum_intense_kernel(const float *plane, int frames, int f0, int f
     *out = total;
 }
 
+// dB value exactly as the reference forms it: (T)(10 * log10((double)s / 1e-12))
+template <typename T> __device__ __forceinline__ T to_db(T s) { return (T)(10.0 * log10((double)s / 1e-12)); }
+
+constexpr int kEpThreads = 256;
+
+template <typename T> __device__ T block_min(T v, T *red)
+{
+    for (int o = 16; o > 0; o >>= 1) { const T u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    T r = red[0];
+    for (int i = 1; i < kEpThreads / 32; ++i) r = red[i] < r ? red[i] : r;
+    return r;
+}
+template <typename T> __device__ T block_max(T v, T *red)
+{
+    for (int o = 16; o > 0; o >>= 1) { const T u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    T r = red[0];
+    for (int i = 1; i < kEpThreads / 32; ++i) r = red[i] > r ? red[i] : r;
+    return r;
+}
+__device__ double block_sum(double v, double *red)
+{
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double r = 0;
+    for (int i = 0; i < kEpThreads / 32; ++i) r += red[i];
+    return r;
+}
+
+// one CTA per signal
+template <typename T> __global__ void __launch_bounds__(kEpThreads) donut_epilogue_kernel(const SjEpilogueArgs a)
+{
+    __shared__ SjEpilogueParams<T> P;
+    __shared__ double red[kEpThreads / 32];
+    __shared__ int sh_count, sh_label;
+    __shared__ T sh_sums[3];
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.params);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(&P);
+        for (int i = threadIdx.x; i < int(sizeof(P) / 4); i += kEpThreads) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const int frames = a.frames, bins = P.bins;
+    const long cells = (long)bins * frames;
+    for (long s = blockIdx.x; s < a.n_signals; s += gridDim.x) {
+        const T *band = reinterpret_cast<const T *>(a.sxx_band) + s * cells;
+        const T *mid = reinterpret_cast<const T *>(a.sxx_mid) + s * cells;
+        unsigned char *flags = a.flags + s * (long)frames;
+        T *mids = reinterpret_cast<T *>(a.mids_t) + s * (long)P.max_mid;
+        float *fmids = a.mids ? a.mids + s * (long)P.max_mid : nullptr;
+        // find_midpoints, part 1: frames with any cell above the dB threshold (threshold moved to the PSD domain)
+        for (int t = threadIdx.x; t < frames; t += kEpThreads) {
+            bool any = false;
+            for (int f = 0; f < bins; ++f) any = any || (mid[(long)f * frames + t] >= P.s_thr);
+            flags[t] = any;
+        }
+        // global minimum / maximum of the positive cells of the band spectrogram (dB is monotone)
+        T mn = (T)INFINITY, mx = 0;
+        for (long i = threadIdx.x; i < cells; i += kEpThreads) {
+            const T v = band[i];
+            if (v > 0) { mn = v < mn ? v : mn; mx = v > mx ? v : mx; }
+        }
+        mn = block_min<T>(mn, reinterpret_cast<T *>(red));
+        mx = block_max<T>(mx, reinterpret_cast<T *>(red));
+        __syncthreads();
+        // find_midpoints, part 2: clusters of flagged frames (gap <= gap_tol, duration >= min_dur), sequentially
+        if (threadIdx.x == 0) {
+            int count = 0, size = 0;
+            T first = 0, last = 0, tsum = 0;
+            for (int j = 0; j <= frames; ++j) {
+                const bool on = j < frames && flags[j];
+                const T tj = div_rn((T)(j * P.hop + P.nperseg / 2), P.fs);
+                const bool joins = on && size > 0 && sub_rn(tj, last) <= P.gap_tol;
+                if (size > 0 && (!on ? j == frames : !joins)) {
+                    if (sub_rn(last, first) >= P.min_dur) {
+                        if (count < P.max_mid) mids[count] = div_rn(tsum, (T)size);
+                        ++count;
+                    }
+                    size = 0;
+                }
+                if (on) {
+                    if (size == 0) { first = tj; tsum = 0; }
+                    tsum = add_rn(tsum, tj);
+                    last = tj;
+                    ++size;
+                }
+            }
+            if (fmids)
+                for (int k = 0; k < P.max_mid; ++k) fmids[k] = k < count ? (float)mids[k] : __int_as_float(0x7fc00000);
+            sh_count = count;
+            sh_label = 0;
+            sh_sums[0] = sh_sums[1] = sh_sums[2] = 0;
+        }
+        __syncthreads();
+        const int count = sh_count, cap = count < P.max_mid ? count : P.max_mid;
+        const T dmn = to_db<T>(mn), dmx = to_db<T>(mx), range = sub_rn(dmx, dmn);
+        for (int m = 0; m < cap; ++m) {
+            const T mp = mids[m];
+            T sums[3];
+            for (int b = 0; b < 3; ++b) {
+                const int f0 = P.box_f[b][0], f1 = P.box_f[b][1];
+                const T tlo = sub_rn(mp, P.half[b]), thi = add_rn(mp, P.half[b]);
+                // sum_intense's time searches: frames before the window / after it (times are increasing)
+                int nb = 0, na = 0;
+                for (int j = threadIdx.x; j < frames; j += kEpThreads) {
+                    const T tj = div_rn((T)(j * P.hop + P.nperseg / 2), P.fs);
+                    nb += tj < tlo;
+                    na += tj > thi;
+                }
+                nb = (int)block_sum((double)nb, red);
+                __syncthreads();
+                na = (int)block_sum((double)na, red);
+                __syncthreads();
+                int t0 = nb, t1 = frames - 1 - na;
+                if (t0 >= frames) t0 = frames - 1;
+                if (t1 < 0) t1 = 0;
+                if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
+                const int nt = t1 - t0 + 1;
+                const long ncell = (long)(f1 - f0 + 1) * nt;
+                double acc = 0.0;
+                if (range > 0)
+                    for (long c = threadIdx.x; c < ncell; c += kEpThreads) {
+                        const int i = (int)(c / nt), j = (int)(c - (long)i * nt);
+                        const T v = band[(long)(f0 + i) * frames + t0 + j];
+                        if (v > 0) {
+                            const T nv = div_rn(sub_rn(to_db<T>(v), dmn), range);
+                            if (nv > P.lo_norm && nv < P.hi_norm) acc += (double)nv;
+                        }
+                    }
+                sums[b] = (T)block_sum(acc, red);
+                __syncthreads();
+            }
+            const bool hit = sums[1] < P.thr_mid && sums[0] > P.thr_above && sums[2] > P.thr_below;
+            if (threadIdx.x == 0) { sh_sums[0] = sums[0]; sh_sums[1] = sums[1]; sh_sums[2] = sums[2]; if (hit) sh_label = 1; }
+            if (hit) break;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            a.labels[s] = sh_label;
+            if (a.detail) {
+                float *d = a.detail + s * 4;
+                d[0] = (float)count; d[1] = (float)sh_sums[0]; d[2] = (float)sh_sums[1]; d[3] = (float)sh_sums[2];
+            }
+        }
+        __syncthreads();
+    }
+}
+
 } // namespace
+
+cudaError_t sj_launch_donut_epilogue(const SjEpilogueArgs &a, bool f64, cudaStream_t stream)
+{
+    if (a.n_signals <= 0) return cudaSuccess;
+    const unsigned grid = (unsigned)(a.n_signals < 148L * 8 ? a.n_signals : 148L * 8);
+    if (f64) donut_epilogue_kernel<double><<<grid, kEpThreads, 0, stream>>>(a);
+    else donut_epilogue_kernel<float><<<grid, kEpThreads, 0, stream>>>(a);
+    return cudaGetLastError();
+}
 
 cudaError_t sj_launch_iir_exact(const SjIirArgs &a, bool f64, cudaStream_t stream)
 {

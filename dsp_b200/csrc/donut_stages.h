@@ -30,6 +30,7 @@ struct SjIirArgs {
     long n_signals, n_samples, in_stride, out_stride;
     const void *coef; // device: T a[9], T b[9]
     void *state;      // device [n_signals][8] of T, read at entry and written at exit; NULL = zero state, not returned
+    int in_f32;       // exact mode: the input rows are float even when T is double (converted on load)
     // scan mode only
     void *blk_final;  // [n_signals][n_blocks][8] of T
     const void *M;    // device: T M[64]
@@ -52,3 +53,34 @@ cudaError_t sj_launch_spectrogram(const SjSpecArgs &a, bool f64, int nperseg, cu
 // sum_intense (classifier.cpp:370-431) on a dense [bins][frames] float plane, one thread, the reference's order
 cudaError_t sj_launch_sum_intense(const float *d_plane, int bins, int frames, int f0, int f1, int t0, int t1,
                                   float *d_out, cudaStream_t stream);
+
+// ---- generic epilogue of the classifier on dense spectrograms (any length, any window): dB, global min/max,
+// level band, find_midpoints' clustering, sum_intense boxes, verdict (classifier.c:104-198 / classifier.cpp:34-135 /
+// classifier.ino:52-139)
+template <typename T> struct SjEpilogueParams {
+    T fs;
+    int32_t nperseg, hop, bins, max_mid;
+    T s_thr;              // smallest Sxx whose dB value exceeds the midpoint threshold (exact, by bisection on the host)
+    T lo_norm, hi_norm, gap_tol, min_dur, thr_mid, thr_above, thr_below;
+    T half[3];            // sum_intense half ranges: above, middle, below
+    int32_t box_f[3][2];  // sum_intense's inclusive frequency-bin ranges (index searches done on the host)
+    int32_t pad[2];
+};
+struct SjEpilogueArgs {
+    const void *sxx_band; // [n][bins][frames] of T: spectrogram of the 3000-7500 Hz filtered signal
+    const void *sxx_mid;  // [n][bins][frames] of T: spectrogram of the 1000-3000 Hz filtered signal
+    long n_signals;
+    int frames;
+    const void *params;   // SjEpilogueParams<T> on the device
+    unsigned char *flags; // scratch [n][frames]
+    void *mids_t;         // scratch [n][max_mid] of T: the midpoints in working precision
+    float *mids;          // [n][max_mid] midpoint times as float (NaN-padded) or NULL
+    int32_t *labels;      // [n]
+    float *detail;        // [n][4] or NULL
+};
+cudaError_t sj_launch_donut_epilogue(const SjEpilogueArgs &a, bool f64, cudaStream_t stream);
+// constants of reference variant `variant` (0-3: the 256-sample programs, 4: classifier.ino) for sampling rate fs
+bool sj_epilogue_variant_f64(int variant);
+int sj_epilogue_variant_nperseg(int variant);
+void sj_epilogue_build_params_f32(SjEpilogueParams<float> *p, int variant, int fs, int max_mid);
+void sj_epilogue_build_params_f64(SjEpilogueParams<double> *p, int variant, int fs, int max_mid);

@@ -14,7 +14,13 @@ void sj_donut_default_params(SjDonutParams *p, int variant)
     if (variant == 0)      { p->thr_mid = 75; p->thr_above = 300; p->thr_below = 100; }
     else if (variant == 1) { p->lo_norm = 0.65; p->hi_norm = 0.80; p->mid_thr_db = 70.0; p->thr_mid = 100; p->thr_above = 200; p->thr_below = 80; }
     else if (variant == 2) { p->gap_tol = 0.15; p->thr_mid = 50; p->thr_above = 200; p->thr_below = 200; }
-    else                   { p->thr_mid = 100; p->thr_above = 200; p->thr_below = 150; }
+    else if (variant == 3) { p->thr_mid = 100; p->thr_above = 200; p->thr_below = 150; }
+    else                   { p->thr_mid = 75; p->thr_above = 300; p->thr_below = 100; } // 4: classifier.ino:88-89, :460, :549-550, :134
+    const double b256[3][2] = {{5000, 7000}, {2500, 5000}, {500, 2500}}, bino[3][2] = {{4500, 7500}, {3500, 4000}, {500, 3000}};
+    for (int b = 0; b < 3; ++b)
+        for (int k = 0; k < 2; ++k) p->band[b][k] = variant == 4 ? bino[b][k] : b256[b][k];
+    p->half[0] = 0.18; p->half[1] = 0.05; p->half[2] = 0.18;
+    p->nperseg = variant == 4 ? 64 : 256;
 }
 
 namespace {
@@ -221,3 +227,39 @@ void sj_stage_transition(const double a[9], int steps, double M[64])
     }
     for (int i = 0; i < 64; i++) M[i] = (double)R[i];
 }
+
+// ---- generic epilogue constants (donut_stages.h)
+namespace {
+template <typename T, typename U> void build_epilogue(SjEpilogueParams<T> *e, int variant, int fs, int max_mid)
+{
+    SjDonutParams p;
+    sj_donut_default_params(&p, variant);
+    memset(e, 0, sizeof *e);
+    e->fs = (T)fs;
+    e->nperseg = p.nperseg;
+    e->hop = p.nperseg - p.nperseg / 8;
+    e->bins = p.nperseg / 2 + 1;
+    e->max_mid = max_mid;
+    e->s_thr = smallest_exceeding<T, U>((T)p.mid_thr_db);
+    e->lo_norm = (T)p.lo_norm; e->hi_norm = (T)p.hi_norm; e->gap_tol = (T)p.gap_tol; e->min_dur = (T)p.min_dur;
+    e->thr_mid = (T)p.thr_mid; e->thr_above = (T)p.thr_above; e->thr_below = (T)p.thr_below;
+    for (int b = 0; b < 3; ++b) {
+        e->half[b] = (T)p.half[b];
+        // sum_intense's index search (classifier.c:596-617 / classifier.cpp:372-393) on frequencies[i] = i * fs / nfft
+        const int bins = e->bins;
+        int f0 = 0, f1 = bins - 1;
+        while (f0 < bins && (T)f0 * e->fs / (T)p.nperseg < (T)p.band[b][0]) f0++;
+        while (f1 >= 0 && (T)f1 * e->fs / (T)p.nperseg > (T)p.band[b][1]) f1--;
+        if (f0 >= bins) f0 = bins - 1;
+        if (f1 < 0) f1 = 0;
+        if (f0 > f1) { const int x = f0; f0 = f1; f1 = x; }
+        e->box_f[b][0] = f0;
+        e->box_f[b][1] = f1;
+    }
+}
+} // namespace
+
+bool sj_epilogue_variant_f64(int variant) { return variant == 0 || variant == 2; }
+int sj_epilogue_variant_nperseg(int variant) { return variant == 4 ? 64 : 256; }
+void sj_epilogue_build_params_f32(SjEpilogueParams<float> *p, int variant, int fs, int max_mid) { build_epilogue<float, uint32_t>(p, variant, fs, max_mid); }
+void sj_epilogue_build_params_f64(SjEpilogueParams<double> *p, int variant, int fs, int max_mid) { build_epilogue<double, uint64_t>(p, variant, fs, max_mid); }

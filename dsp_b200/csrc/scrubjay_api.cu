@@ -78,6 +78,10 @@ struct scrubjay_ctx {
     int stage_tab_fs[2][2] = {{0, 0}, {0, 0}};
     void *d_stage_blk = nullptr, *d_stage_in = nullptr, *d_stage_out = nullptr;
     size_t stage_blk_bytes = 0, stage_in_bytes = 0, stage_out_bytes = 0;
+    void *d_ep_params[SJ_DONUT_INO_F32 + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ep_max_mid[SJ_DONUT_INO_F32 + 1] = {0, 0, 0, 0, 0};
+    void *d_long_ws = nullptr;
+    size_t long_ws_bytes = 0;
 };
 
 namespace {
@@ -216,6 +220,8 @@ void scrubjay_destroy(scrubjay_ctx *c)
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
     cudaFree(c->d_stage_coef); cudaFree(c->d_stage_M); cudaFree(c->d_stage_blk); cudaFree(c->d_stage_in); cudaFree(c->d_stage_out);
     for (auto &r : c->d_stage_tab) for (void *t : r) cudaFree(t);
+    for (void *t : c->d_ep_params) cudaFree(t);
+    cudaFree(c->d_long_ws);
     cudaFree(c->d_kw_tables); cudaFree(c->d_kw_signals); cudaFree(c->d_kw_prob);
     delete c->h_tables;
     delete c;
@@ -618,12 +624,18 @@ scrubjay_ctx *g_default_ctx = nullptr;
 
 extern "C" {
 
+// signals longer than the fused kernel's 96 frames, and the 64-sample-window variant, take the staged pipeline
+static bool donut_needs_staged(int variant, long n_samples) { return variant == SJ_DONUT_INO_F32 || n_samples > DN_WIN + (long)DN_HOP * (DN_MAX_TB - 1); }
+constexpr int kStagedMaxMid = 64;
+
 int scrubjay_donut_classify_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant,
                                       int32_t *d_labels, float *d_detail)
 {
     if (!c) return SJ_EINVAL;
     if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
     SJ_CUDA(c, cudaSetDevice(c->device));
+    if (donut_needs_staged(variant, n_samples))
+        return scrubjay_donut_classify_long_dev(c, d_clips, n_clips, n_samples, variant, d_labels, d_detail, nullptr, kStagedMaxMid);
     int tb = 0, rc = donut_prepare(c, variant, n_samples, &tb);
     if (rc != SJ_OK) return rc;
     return donut_launch(c, d_clips, n_clips, n_samples, variant, tb, d_labels, d_detail);
@@ -635,8 +647,10 @@ int scrubjay_donut_classify_batch(scrubjay_ctx *c, const float *clips, long n_cl
     if (!c) return SJ_EINVAL;
     if (!clips || !labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
     SJ_CUDA(c, cudaSetDevice(c->device));
-    int tb = 0, rc = donut_prepare(c, variant, n_samples, &tb);
+    const bool staged = donut_needs_staged(variant, n_samples);
+    int tb = 0, rc = staged ? SJ_OK : donut_prepare(c, variant, n_samples, &tb);
     if (rc != SJ_OK) return rc;
+    if (n_samples < 1) return set_err(c, SJ_EINVAL, "donut path: empty clip");
     long chunk = kChunkBytes / ((long)n_samples * 4);
     if (chunk < 1) chunk = 1;
     if (chunk > n_clips && n_clips > 0) chunk = n_clips;
@@ -655,7 +669,9 @@ int scrubjay_donut_classify_batch(scrubjay_ctx *c, const float *clips, long n_cl
         const long n = n_clips - done < chunk ? n_clips - done : chunk;
         SJ_CUDA(c, cudaMemcpyAsync(c->d_donut_clips, clips + done * (long)n_samples, (size_t)n * n_samples * 4,
                                    cudaMemcpyHostToDevice, c->stream));
-        rc = donut_launch(c, c->d_donut_clips, n, n_samples, variant, tb, c->d_donut_labels, c->d_donut_detail);
+        rc = staged ? scrubjay_donut_classify_long_dev(c, c->d_donut_clips, n, n_samples, variant, c->d_donut_labels,
+                                                       c->d_donut_detail, nullptr, kStagedMaxMid)
+                    : donut_launch(c, c->d_donut_clips, n, n_samples, variant, tb, c->d_donut_labels, c->d_donut_detail);
         if (rc != SJ_OK) return rc;
         SJ_CUDA(c, cudaMemcpyAsync(labels + done, c->d_donut_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
         if (detail)

@@ -157,7 +157,9 @@ SJ_API int scrubjay_infer_batch(scrubjay_ctx *ctx, const float *clips, long n_cl
 #define SJ_DONUT_SYNC_F32 1    /* sync/lib/classifier.cpp: float, band 0.65-0.80, 70 dB, mid<100 above>200 below>80 */
 #define SJ_DONUT_REVERT_F64 2  /* donut-classifier/revert.c = microphone/src/classifier.c: double, 0.70-0.85, 45 dB, gap tolerance 0.15 s, mid<50 above>200 below>200 */
 #define SJ_DONUT_MIC_F32 3     /* microphone/src/classifier.cpp: float, 0.70-0.85, 45 dB, mid<100 above>200 below>150 */
-#define SJ_DONUT_N_VARIANTS 4
+#define SJ_DONUT_N_VARIANTS 4  /* variants of the fused 256-sample-window kernel */
+#define SJ_DONUT_INO_F32 4     /* donut-classifier/classifier.ino: float, 64-sample windows, 0.70-0.85, 45 dB, boxes 4500-7500 /
+                                  3500-4000 / 500-3000 Hz, mid<75 above>300 below>100 (staged path only) */
 
 /* The reference's own entry point, same name and signature: sync/lib/classifier.h:19, called as
  * classify(buffer, 16000) at sync/sync.cpp:202.  Host pointer in, 1/0 out (0 also on failure, as the
@@ -178,6 +180,14 @@ SJ_API int scrubjay_donut_classify_batch(scrubjay_ctx *ctx, const float *clips, 
 #define SJ_DONUT_MAX_MID 8
 SJ_API int scrubjay_donut_midpoints_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                                               int variant, int32_t *d_labels, float *d_detail, float *d_mids);
+
+/* Signals of ANY length (the desktop program classifies whole recordings, classifier.c:37-210) and the
+ * 64-sample-window variant: the same classifier as a staged pipeline (filter -> spectrogram, twice, -> epilogue)
+ * instead of the fused kernel; scrubjay_donut_classify_batch(_dev) switches to it by itself for n_samples > 21536
+ * or variant SJ_DONUT_INO_F32.  d_mids (may be NULL) [n][max_mid] float midpoints, NaN-padded; at most max_mid
+ * (1..4096) midpoints are evaluated per signal.  d_detail as above. */
+SJ_API int scrubjay_donut_classify_long_dev(scrubjay_ctx *ctx, const float *d_signals, long n_signals, long n_samples,
+                                            int variant, int32_t *d_labels, float *d_detail, float *d_mids, int max_mid);
 
 /* Decision tracks of continuous streams, the firmware's loop (sync/sync.cpp:190-212): every full block of
  * clip_samples samples (16000 there) of every channel is classified from zero state and the result stored as the

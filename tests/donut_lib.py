@@ -204,6 +204,24 @@ class DonutRefIno:
         return np.array([np.ctypeslib.as_array(rows[i], shape=(tb.value,)).copy() for i in range(fb.value)])
 
 
+    def classify(self, clip):
+        """the sketch's setup() on a one-second clip -> (label, number of midpoints, [(above, middle, below), ...])"""
+        x = np.ascontiguousarray(clip, np.float32)
+        assert x.size == 16000
+        buf = (ctypes.c_float * 16000).in_dll(self.L, "data")
+        ctypes.memmove(buf, x.ctypes.data, 16000 * 4)
+        cnt = ctypes.c_int.in_dll(self.L, "sj_shim_serial_count")
+        scrub = ctypes.c_int.in_dll(self.L, "sj_shim_serial_scrub")
+        nums = (ctypes.c_double * 4096).in_dll(self.L, "sj_shim_serial_numbers")
+        cnt.value = 0
+        scrub.value = -1
+        getattr(self.L, "_Z5setupv")()
+        vals = [nums[i] for i in range(cnt.value)]
+        n_mid = int(vals[0]) if vals else 0
+        sums = [tuple(vals[1 + 3 * k:4 + 3 * k]) for k in range((len(vals) - 1) // 3)]
+        return (1 if scrub.value == 1 else 0), n_mid, sums
+
+
 def have_ref_ino():
     return os.path.exists(REFINO)
 

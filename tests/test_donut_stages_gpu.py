@@ -235,3 +235,97 @@ def test_stage_argument_errors():
     with pytest.raises(dsp_b200.ScrubJayError):
         sj.spectrogram_batch(np.zeros((1, 10), np.float32), nperseg=256)  # (10 - 256) / 224 + 1 = 0 frames
     assert sj.butter_filter_batch(np.zeros((0, 100), np.float32), np.zeros(9), np.ones(9)).shape == (0, 100)
+
+
+def _synth_dev(sj, first, n, ns=16000):
+    import torch
+    d = torch.empty((n, ns), dtype=torch.float32, device="cuda")
+    sj.set_stream(torch.cuda.current_stream().cuda_stream)
+    sj.synth_clips_dev(d, first, n, ns)
+    torch.cuda.synchronize()
+    return d
+
+
+def _long(sj, d, variant, max_mid=64):
+    import torch
+    n, ns = d.shape
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    detail = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    mids = torch.empty((n, max_mid), dtype=torch.float32, device="cuda")
+    sj.donut_classify_long_dev(d, n, ns, variant, labels, detail, mids, max_mid)
+    torch.cuda.synchronize()
+    return labels.cpu().numpy(), detail.cpu().numpy(), mids.cpu().numpy()
+
+
+@pytest.mark.parametrize("variant,tol", [(0, 1e-6), (1, 2e-3), (2, 1e-6), (3, 2e-3)])
+def test_staged_classifier_equals_fused_kernel(variant, tol):
+    """the staged pipeline (any length) against the fused kernel on one-second clips: same midpoints, labels and band
+    sums (the float variants share the bit-exact IIR and FFT; sums differ only by the order of a double accumulation)"""
+    import torch
+    sj = _ctx()
+    n = 192
+    d = _synth_dev(sj, 2000, n)
+    fl = torch.empty(n, dtype=torch.int32, device="cuda")
+    fd = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    fm = torch.empty((n, 8), dtype=torch.float32, device="cuda")
+    sj.donut_midpoints_batch_dev(d, n, 16000, variant, fl, fd, fm)
+    torch.cuda.synchronize()
+    fl, fd, fm = fl.cpu().numpy(), fd.cpu().numpy(), fm.cpu().numpy()
+    ll, ld, lm = _long(sj, d, variant, 8)
+    assert np.array_equal(ld[:, 0], fd[:, 0])
+    assert np.array_equal(np.isnan(lm), np.isnan(fm)) and np.allclose(np.nan_to_num(lm), np.nan_to_num(fm), rtol=0, atol=1e-6)
+    assert np.abs(ld[:, 1:] - fd[:, 1:]).max() <= tol * max(1.0, np.abs(fd[:, 1:]).max())
+    assert np.array_equal(ll, fl)
+    assert (fd[:, 0] > 0).any()
+
+
+def test_ino_variant_matches_unmodified_sketch():
+    """SJ_DONUT_INO_F32 against classifier.ino's own setup() (oracle/_ref/libdonut_ref_ino.so): verdict, number of
+    midpoints and the three band sums of the last midpoint the sketch evaluated"""
+    import dsp_b200
+    if not have_ref_ino():
+        pytest.skip("oracle/_ref/libdonut_ref_ino.so not built")
+    sj = _ctx()
+    n = 96
+    d = _synth_dev(sj, 5000, n)
+    labels, detail, mids = _long(sj, d, dsp_b200.DONUT_INO_F32, 16)
+    clips = d.cpu().numpy()
+    ref = DonutRefIno()
+    pos = 0
+    for i in range(n):
+        lab, nm, sums = ref.classify(clips[i])
+        assert int(detail[i, 0]) == nm, i
+        if sums:
+            assert np.allclose(detail[i, 1:], sums[-1], rtol=1e-4, atol=2e-2), (i, detail[i], sums[-1])
+        assert labels[i] == lab, (i, detail[i], sums)
+        pos += lab
+    assert 0 < pos < n
+    # the batch entry point routes this variant to the staged pipeline by itself
+    l2, d2 = sj.donut_classify_batch(clips, dsp_b200.DONUT_INO_F32)
+    assert np.array_equal(l2, labels) and np.array_equal(d2, detail)
+
+
+@pytest.mark.parametrize("secs", [2, 5])
+def test_long_signals_match_unmodified_reference(secs):
+    """whole recordings (classifier.c:37-210 works on complete files): classify(float*, n) of the unmodified
+    classifier.cpp and find_midpoints of classifier.c on signals longer than the fused kernel's 1.3 s"""
+    import dsp_b200
+    if not have_ref():
+        pytest.skip("oracle/_ref not built")
+    sj = _ctx()
+    n = 12
+    d = _synth_dev(sj, 7000, n * secs).view(n, secs * 16000)
+    x = d.cpu().numpy()
+    l32, d32, m32 = _long(sj, d, dsp_b200.DONUT_SYNC_F32, 64)
+    l64, d64, m64 = _long(sj, d, dsp_b200.DONUT_DESKTOP_F64, 64)
+    r32, r64 = DonutRef32(), DonutRef64()
+    for i in range(n):
+        assert l32[i] == r32.classify(x[i]), i
+        w32 = r32.midpoints(x[i])
+        assert int(d32[i, 0]) == len(w32) and np.allclose(m32[i, :len(w32)], w32, rtol=0, atol=1e-6)
+        w64 = r64.midpoints(x[i])
+        assert int(d64[i, 0]) == len(w64) and np.allclose(m64[i, :len(w64)], w64, rtol=0, atol=1e-6)
+    # the host entry point and the reference's own symbol accept the long signal as well
+    lh, dh = sj.donut_classify_batch(x, dsp_b200.DONUT_SYNC_F32)
+    assert np.array_equal(lh, l32) and np.array_equal(dh, d32)
+    assert dsp_b200.classify(x[0]) == l32[0]

@@ -51,4 +51,15 @@ for name, tdt, prec in (("f32", torch.float32, dsp_b200.F32), ("f64", torch.floa
         ms = timed(lambda: sj.spectrogram_batch_dev(x, n, ns, ns, prec, nperseg, 16000, S))
         out["spectrogram_%s_%d" % (name, nperseg)] = {"signals": n, "frames": frames, "ms": ms, "frames_per_s": n * frames / ms * 1e3}
         del x, S
+# staged classifier: the .ino variant on 1 s clips, and whole recordings (10 min each)
+for name, variant, n, ns in (("ino_f32_1s", dsp_b200.DONUT_INO_F32, 50000, 16000), ("sync_f32_1s_staged", dsp_b200.DONUT_SYNC_F32, 50000, 16000),
+                             ("sync_f32_10min", dsp_b200.DONUT_SYNC_F32, 64, 9600000), ("desktop_f64_10min", dsp_b200.DONUT_DESKTOP_F64, 64, 9600000)):
+    d = torch.empty((n * ns // 16000, 16000), dtype=torch.float32, device="cuda")
+    sj.synth_clips_dev(d, 0, n * ns // 16000, 16000)
+    lab = torch.empty(n, dtype=torch.int32, device="cuda")
+    det = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    ms = timed(lambda: sj.donut_classify_long_dev(d, n, ns, variant, lab, det, None, 64), 2)
+    out["classify_" + name] = {"signals": n, "samples": ns, "ms": ms, "audio_seconds_per_s": n * (ns / 16000) / ms * 1e3,
+                               "positives": int(lab.sum().item())}
+    del d
 print(json.dumps(out))
