@@ -64,16 +64,74 @@ __device__ __forceinline__ void iir_block8(const T (&x)[8], T (&r)[8], const T (
     }
 }
 
+// eight consecutive elements of one row: 16-byte accesses when the row is 16-byte aligned (each lane walks its own row,
+// so a warp-level access touches 32 different lines either way -- wide accesses cut the number of such instructions)
+template <typename E> __device__ __forceinline__ void load8(const E *p, E (&d)[8], bool vec)
+{
+    if (vec) {
+        constexpr int kChunks = int(sizeof(E)) * 8 / 16;
+        uint4 u[kChunks];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) u[c] = __ldg(reinterpret_cast<const uint4 *>(p) + c);
+        const E *e = reinterpret_cast<const E *>(u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) d[k] = e[k];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) d[k] = __ldg(p + k);
+    }
+}
+template <typename E> __device__ __forceinline__ void store8(E *p, const E (&v)[8], bool vec)
+{
+    if (vec) {
+        constexpr int kChunks = int(sizeof(E)) * 8 / 16;
+        uint4 u[kChunks];
+        E *e = reinterpret_cast<E *>(u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) e[k] = v[k];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) reinterpret_cast<uint4 *>(p)[c] = u[c];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) p[k] = v[k];
+    }
+}
+
 // run `n` samples of one signal from state w (shifted form); out may be NULL (state only)
 template <typename T, bool WRITE, typename IN = T>
 __device__ __forceinline__ void iir_run(const IN *__restrict__ in, T *__restrict__ out, long n, T (&w)[8],
-                                        const T (&a)[9], const T (&b)[9])
+                                        const T (&a)[9], const T (&b)[9], bool vec_in, bool vec_out)
 {
     T r[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) r[7 - k] = w[k]; // w0 of time n-1-k = r[(0-(k+1))&7]
-    long i = 0;
-    for (; i + 8 <= n; i += 8) {
+    // The recurrence is one dependent chain per lane, so nothing but the lane itself can hide the latency of its
+    // own input: a register ring of kPre blocks of 8 samples, each requested kPre blocks before it is filtered.
+    constexpr int kPre = 4;
+    IN ring[kPre][8];
+    const long nblk = n / 8;
+#pragma unroll
+    for (int j = 0; j < kPre; ++j) {
+        if ((long)j < nblk) load8<IN>(in + 8 * j, ring[j], vec_in);
+        else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) ring[j][k] = (IN)0;
+        }
+    }
+    long blk = 0;
+    for (; blk + kPre <= nblk; blk += kPre) {
+#pragma unroll
+        for (int j = 0; j < kPre; ++j) {
+            T x[8], y[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = (T)ring[j][k];
+            if (blk + j + kPre < nblk) load8<IN>(in + 8 * (blk + j + kPre), ring[j], vec_in);
+            iir_block8<T>(x, r, a, b, y);
+            if (WRITE) store8<T>(out + 8 * (blk + j), y, vec_out);
+        }
+    }
+    long i = 8 * blk;
+    for (; i + 8 <= n; i += 8) { // the last (< kPre) whole blocks
         T x[8], y[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) x[k] = (T)__ldg(in + i + k);
@@ -109,10 +167,10 @@ template <typename T> __global__ void __launch_bounds__(128) iir_exact_kernel(co
     for (int k = 0; k < 8; ++k) w[k] = st ? st[k] : (T)0;
     if (sizeof(T) == 8 && p.in_f32)
         iir_run<T, true, float>(reinterpret_cast<const float *>(p.in) + s * p.in_stride,
-                                reinterpret_cast<T *>(p.out) + s * p.out_stride, p.n_samples, w, a, b);
+                                reinterpret_cast<T *>(p.out) + s * p.out_stride, p.n_samples, w, a, b, p.vec_in, p.vec_out);
     else
         iir_run<T, true>(reinterpret_cast<const T *>(p.in) + s * p.in_stride, reinterpret_cast<T *>(p.out) + s * p.out_stride,
-                         p.n_samples, w, a, b);
+                         p.n_samples, w, a, b, p.vec_in, p.vec_out);
     if (st) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) st[k] = w[k];
@@ -130,7 +188,8 @@ template <typename T> __global__ void __launch_bounds__(128) iir_scan_local_kern
     load_coef<T>(p.coef, a, b);
 #pragma unroll
     for (int j = 0; j < 8; ++j) w[j] = 0;
-    iir_run<T, false>(reinterpret_cast<const T *>(p.in) + s * p.in_stride + k * SJ_SCAN_BLOCK, nullptr, SJ_SCAN_BLOCK, w, a, b);
+    iir_run<T, false>(reinterpret_cast<const T *>(p.in) + s * p.in_stride + k * SJ_SCAN_BLOCK, nullptr, SJ_SCAN_BLOCK, w, a, b,
+                      p.vec_in, false);
     T *f = reinterpret_cast<T *>(p.blk_final) + id * 8;
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = w[j];
@@ -178,7 +237,7 @@ template <typename T> __global__ void __launch_bounds__(128) iir_scan_apply_kern
     const long i0 = k * SJ_SCAN_BLOCK;
     const long n = (k == p.n_blocks - 1) ? p.n_samples - i0 : SJ_SCAN_BLOCK;
     iir_run<T, true>(reinterpret_cast<const T *>(p.in) + s * p.in_stride + i0,
-                     reinterpret_cast<T *>(p.out) + s * p.out_stride + i0, n, w, a, b);
+                     reinterpret_cast<T *>(p.out) + s * p.out_stride + i0, n, w, a, b, p.vec_in, p.vec_out);
     if (p.state && k == p.n_blocks - 1) {
         T *st = reinterpret_cast<T *>(p.state) + s * 8;
 #pragma unroll
@@ -476,8 +535,17 @@ cudaError_t sj_launch_donut_epilogue(const SjEpilogueArgs &a, bool f64, cudaStre
     return cudaGetLastError();
 }
 
-cudaError_t sj_launch_iir_exact(const SjIirArgs &a, bool f64, cudaStream_t stream)
+static SjIirArgs with_alignment(SjIirArgs a, bool f64)
 {
+    const size_t es_out = f64 ? 8 : 4, es_in = (f64 && !a.in_f32) ? 8 : 4;
+    a.vec_in = (reinterpret_cast<uintptr_t>(a.in) % 16 == 0) && ((size_t)a.in_stride * es_in % 16 == 0);
+    a.vec_out = (reinterpret_cast<uintptr_t>(a.out) % 16 == 0) && ((size_t)a.out_stride * es_out % 16 == 0);
+    return a;
+}
+
+cudaError_t sj_launch_iir_exact(const SjIirArgs &a0, bool f64, cudaStream_t stream)
+{
+    const SjIirArgs a = with_alignment(a0, f64);
     if (a.n_signals <= 0 || a.n_samples <= 0) return cudaSuccess;
     const unsigned grid = (unsigned)((a.n_signals + 127) / 128);
     if (f64) iir_exact_kernel<double><<<grid, 128, 0, stream>>>(a);
@@ -485,8 +553,9 @@ cudaError_t sj_launch_iir_exact(const SjIirArgs &a, bool f64, cudaStream_t strea
     return cudaGetLastError();
 }
 
-cudaError_t sj_launch_iir_scan(const SjIirArgs &a, bool f64, cudaStream_t stream)
+cudaError_t sj_launch_iir_scan(const SjIirArgs &a0, bool f64, cudaStream_t stream)
 {
+    const SjIirArgs a = with_alignment(a0, f64);
     if (a.n_signals <= 0 || a.n_samples <= 0) return cudaSuccess;
     const long items = a.n_signals * a.n_blocks;
     const unsigned grid = (unsigned)((items + 127) / 128), grid_s = (unsigned)((a.n_signals + 127) / 128);

@@ -31,6 +31,7 @@ struct SjIirArgs {
     const void *coef; // device: T a[9], T b[9]
     void *state;      // device [n_signals][8] of T, read at entry and written at exit; NULL = zero state, not returned
     int in_f32;       // exact mode: the input rows are float even when T is double (converted on load)
+    bool vec_in, vec_out; // set by the launchers: rows are 16-byte aligned (128-bit accesses)
     // scan mode only
     void *blk_final;  // [n_signals][n_blocks][8] of T
     const void *M;    // device: T M[64]
