@@ -313,6 +313,26 @@ def run_ours(args, rank, local_rank, world):
                "note": "outputs bit-identical to the float path on s/32768 (tests/test_pcm16_gpu.py)"}
         del pcm_dev
 
+    # ---- donut path (BASELINE config 3: Butterworth IIR + FFT band energies), the same resident clips, per GPU
+    donut = None
+    if args.donut:
+        import dsp_b200
+        Cd = min(C, args.donut_clips)
+        det = torch.empty((Cd, 4), dtype=torch.float32, device=dev)
+        donut = {"clips": Cd, "bytes_per_clip": N_SAMPLES * 4 + 4, "frames_per_clip": 142}
+        for name, variant in (("sync_f32", dsp_b200.DONUT_SYNC_F32), ("desktop_f64", dsp_b200.DONUT_DESKTOP_F64)):
+            kd = []
+            for i in range(3):
+                sj.donut_classify_batch_dev(clips, Cd, N_SAMPLES, variant, labels[:Cd], det)
+                kd.append(sj.last_kernel_ms())
+            kd = min(kd[1:])
+            donut[name] = {"kernel_ms": kd, "clips_per_s_per_gpu": Cd / (kd * 1e-3), "frames_per_s_per_gpu": 142 * Cd / (kd * 1e-3),
+                           "achieved_gbs": (N_SAMPLES * 4 + 4) * Cd / (kd * 1e-3) / 1e9,
+                           "positives": int(labels[:Cd].sum().item())}
+        donut["note"] = ("fused donut_kernel (IIR x2 bit-exact, spectrogram x2, band sums, verdict); instruction-bound "
+                         "(exact no-FMA replay of the reference FFT), see DESIGN.md section 6")
+        del det
+
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
@@ -338,6 +358,7 @@ def run_ours(args, rank, local_rank, world):
                     "d2h_bytes_per_step": E * 12, "clips_per_step": E, "steps": args.e2e_steps,
                     "api": "scrubjay_infer_batch (host pointers, pinned)"},
             "pcm16": pcm,
+            "donut": donut,
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
@@ -364,6 +385,8 @@ def main():
     ap.add_argument("--ref-clips-per-thread", type=int, default=1024)
     ap.add_argument("--no-pcm16", dest="pcm16", action="store_false", help="skip the int16 PCM ingest measurement")
     ap.add_argument("--pcm16-clips", type=int, default=500000)
+    ap.add_argument("--no-donut", dest="donut", action="store_false", help="skip the donut-path measurement")
+    ap.add_argument("--donut-clips", type=int, default=500000)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

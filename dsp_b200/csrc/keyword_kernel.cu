@@ -179,9 +179,16 @@ __global__ void __launch_bounds__(kWarps * 32, 2) keyword_kernel(const KwArgs a,
                 __syncwarp();
                 // DCT (mfcc.c:213-220): lane l < 26 sums mel rows 20*(l/13) .. +19 of coefficient l % 13
                 float acc = 0.f;
-                const float *lgh = lg + (lane >= 13 ? 20 : 0);
+                // (the 20 dB values of a half as five 128-bit words: two addresses per warp)
+                const float4 *lgh = reinterpret_cast<const float4 *>(lg + (lane >= 13 ? 20 : 0));
 #pragma unroll
-                for (int j = 0; j < 20; ++j) acc = fmaf(T->dct[j][lane], lgh[j], acc);
+                for (int q = 0; q < 5; ++q) {
+                    const float4 e = lgh[q];
+                    acc = fmaf(T->dct[4 * q][lane], e.x, acc);
+                    acc = fmaf(T->dct[4 * q + 1][lane], e.y, acc);
+                    acc = fmaf(T->dct[4 * q + 2][lane], e.z, acc);
+                    acc = fmaf(T->dct[4 * q + 3][lane], e.w, acc);
+                }
                 acc += __shfl_down_sync(kFull, acc, 13);
                 if (lane < KW_NMFCC) {
                     feat[lane * KW_MAX_FRAMES + tf] = acc;
