@@ -105,6 +105,37 @@ def cpu_baseline(clips_np, target_seconds=12.0):
                       % (n, dt)}
 
 
+def donut_cpu_reference(clips_np, n=4096):
+    """the UNMODIFIED reference classify() (sync/lib/classifier.cpp built into oracle/_ref by oracle/Makefile) on one
+    host thread -- it keeps static buffers, so it is not thread-safe -- over a bounded sample of the same clips"""
+    import ctypes
+    path = os.path.join(ROOT, "oracle", "_ref", "libdonut_ref_f32.so")
+    if not os.path.exists(path):
+        return None
+    L = ctypes.CDLL(path)
+    fn = getattr(L, "_Z8classifyPfi")
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    n = min(n, clips_np.shape[0])
+    x = clips_np[:n].copy()
+    labels = []
+    sys.stdout.flush()
+    saved, null = os.dup(1), os.open(os.devnull, os.O_WRONLY)  # the reference prints from inside classify()
+    os.dup2(null, 1)
+    try:
+        t0 = time.perf_counter()
+        for i in range(n):
+            labels.append(int(fn(x[i].ctypes.data, x.shape[1])))
+        dt = time.perf_counter() - t0
+    finally:
+        ctypes.CDLL(None).fflush(None)
+        os.dup2(saved, 1)
+        os.close(null)
+        os.close(saved)
+    return {"value": n / dt, "unit": "clips/s", "cores": 1, "kind": "reference",
+            "sample": "%d of the step's clips, %.1f s wall, unmodified sync/lib/classifier.cpp + PlainFFT.cpp -O3, one thread "
+                      "(static buffers: not thread-safe)" % (n, dt)}, labels
+
+
 # ---------------------------------------------------------------- clocks sampler
 class ClockSampler:
     """samples SM clock and throttle reasons (NVML) while the timed region runs"""
@@ -329,6 +360,13 @@ def run_ours(args, rank, local_rank, world):
             donut[name] = {"kernel_ms": kd, "clips_per_s_per_gpu": Cd / (kd * 1e-3), "frames_per_s_per_gpu": 142 * Cd / (kd * 1e-3),
                            "achieved_gbs": (N_SAMPLES * 4 + 4) * Cd / (kd * 1e-3) / 1e9,
                            "positives": int(labels[:Cd].sum().item())}
+        if args.cpu_baseline and world == 1:
+            ref = donut_cpu_reference(host[:4096].numpy())
+            if ref is not None:
+                nr = len(ref[1])
+                sj.donut_classify_batch_dev(clips, nr, N_SAMPLES, dsp_b200.DONUT_SYNC_F32, labels[:nr], det[:nr])
+                same = int((labels[:nr].cpu().numpy() == np.array(ref[1], dtype=np.int32)).sum())
+                donut["cpu_reference"] = dict(ref[0], labels_equal_to_gpu="%d of %d" % (same, len(ref[1])))
         donut["note"] = ("fused donut_kernel (IIR x2 bit-exact, spectrogram x2, band sums, verdict); instruction-bound "
                          "(exact no-FMA replay of the reference FFT), see DESIGN.md section 6")
         del det
