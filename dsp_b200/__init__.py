@@ -76,6 +76,7 @@ def load_library():
     L.scrubjay_stream_windows.argtypes = [c_long, c_int, c_int]
     L.scrubjay_stream_windows.restype = c_long
     L.scrubjay_stream_infer_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
+    L.scrubjay_stream_infer_pcm16_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
     L.scrubjay_set_stream_chunk.argtypes = [vp, c_int]
     L.scrubjay_mfcc_stats.argtypes = [vp, vp, c_long, vp]
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
@@ -206,6 +207,13 @@ class ScrubJay:
         self._check(self._L.scrubjay_stream_infer_dev(self._h, _ptr(streams), n_channels, n_samples, chan_stride,
                                                       _ptr(prev_hop), win_frames, step_frames, _ptr(labels),
                                                       _ptr(conf), _ptr(score), _ptr(feats)))
+
+    def stream_infer_pcm16_dev(self, streams, n_channels, n_samples, chan_stride, labels, conf=None, score=None,
+                               feats=None, win_frames=16, step_frames=16, prev_hop=None):
+        """scrubjay_stream_infer_pcm16_dev: stream_infer_dev on int16 PCM channels (s / 32768 inside the kernel)."""
+        self._check(self._L.scrubjay_stream_infer_pcm16_dev(self._h, _ptr(streams), n_channels, n_samples, chan_stride,
+                                                            _ptr(prev_hop), win_frames, step_frames, _ptr(labels),
+                                                            _ptr(conf), _ptr(score), _ptr(feats)))
 
     def set_stream_chunk(self, windows_per_item):
         self._check(self._L.scrubjay_set_stream_chunk(self._h, windows_per_item))

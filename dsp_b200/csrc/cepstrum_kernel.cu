@@ -675,13 +675,14 @@ cudaError_t sj_cepstrum_setup(int maxseg)
     cudaError_t e = setup_four<false, false>(maxseg);
     if (e == cudaSuccess) e = setup_four<true, false>(maxseg);
     if (e == cudaSuccess) e = setup_four<false, true>(maxseg);
+    if (e == cudaSuccess) e = setup_four<true, true>(maxseg);
     return e;
 }
 
 cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int num_sms, cudaStream_t stream)
 {
     if (a.n_clips <= 0) return cudaSuccess;
-    if (a.pcm16) return a.n_windows > 0 ? cudaErrorInvalidValue : launch_any<false, true>(a, h, num_sms, stream);
+    if (a.pcm16) return a.n_windows > 0 ? launch_any<true, true>(a, h, num_sms, stream) : launch_any<false, true>(a, h, num_sms, stream);
     if (a.n_windows > 0) return launch_any<true, false>(a, h, num_sms, stream);
     return launch_any<false, false>(a, h, num_sms, stream);
 }

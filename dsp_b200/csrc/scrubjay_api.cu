@@ -358,9 +358,29 @@ long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames)
     return hops < win_frames ? 0 : (hops - win_frames) / step_frames + 1;
 }
 
+static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_channels, long n_samples, long chan_stride,
+                            const void *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
+                            float *d_conf, float *d_score, float *d_feats, int pcm16);
+
 int scrubjay_stream_infer_dev(scrubjay_ctx *c, const float *d_streams, long n_channels, long n_samples, long chan_stride,
                               const float *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
                               float *d_conf, float *d_score, float *d_feats)
+{
+    return stream_infer_any(c, d_streams, n_channels, n_samples, chan_stride, d_prev_hop, win_frames, step_frames, d_labels,
+                            d_conf, d_score, d_feats, 0);
+}
+
+int scrubjay_stream_infer_pcm16_dev(scrubjay_ctx *c, const int16_t *d_streams, long n_channels, long n_samples,
+                                    long chan_stride, const int16_t *d_prev_hop, int win_frames, int step_frames,
+                                    int32_t *d_labels, float *d_conf, float *d_score, float *d_feats)
+{
+    return stream_infer_any(c, d_streams, n_channels, n_samples, chan_stride, d_prev_hop, win_frames, step_frames, d_labels,
+                            d_conf, d_score, d_feats, 1);
+}
+
+static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_channels, long n_samples, long chan_stride,
+                            const void *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
+                            float *d_conf, float *d_score, float *d_feats, int pcm16)
 {
     if (!c) return SJ_EINVAL;
     if (!d_streams || !d_labels || n_channels < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
@@ -372,10 +392,10 @@ int scrubjay_stream_infer_dev(scrubjay_ctx *c, const float *d_streams, long n_ch
     if (nw == 0 || n_channels == 0) return SJ_OK;
     SJ_CUDA(c, cudaSetDevice(c->device));
     SjCepstrumArgs a;
-    a.pcm16 = 0;
-    a.clips = d_streams; a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
+    a.pcm16 = pcm16;
+    a.clips = reinterpret_cast<const float *>(d_streams); a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
     a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
-    a.chan_stride = chan_stride; a.prev_hop = d_prev_hop; a.n_windows = nw;
+    a.chan_stride = chan_stride; a.prev_hop = reinterpret_cast<const float *>(d_prev_hop); a.n_windows = nw;
     a.win_frames = win_frames; a.step_frames = step_frames;
     // work items: enough of them that the static round-robin over the resident warps ends evenly (>= 16 per
     // warp), but long enough that the win - step frames recomputed at the head of each item stay below ~20 %

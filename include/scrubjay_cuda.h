@@ -137,6 +137,11 @@ SJ_API long scrubjay_stream_windows(long n_samples, int win_frames, int step_fra
 SJ_API int scrubjay_stream_infer_dev(scrubjay_ctx *ctx, const float *d_streams, long n_channels, long n_samples,
                               long chan_stride, const float *d_prev_hop, int win_frames, int step_frames,
                               int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+/* The same on int16 PCM streams (d_streams / d_prev_hop hold samples s, the kernel works on s / 32768): outputs
+ * bit-identical to the float entry point on the converted samples, at half the resident bytes per channel. */
+SJ_API int scrubjay_stream_infer_pcm16_dev(scrubjay_ctx *ctx, const int16_t *d_streams, long n_channels, long n_samples,
+                                           long chan_stride, const int16_t *d_prev_hop, int win_frames, int step_frames,
+                                           int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
 /* windows per work item of the stream mode (0 = automatic); a tuning / test knob */
 SJ_API int scrubjay_set_stream_chunk(scrubjay_ctx *ctx, int windows_per_item);
 

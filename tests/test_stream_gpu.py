@@ -111,3 +111,34 @@ def test_stream_rejects_bad_windows():
             sj.stream_infer_dev(d, 1, 32768, 32768, lab, None, None, None, W, S)
     assert sj.stream_windows(1024 * 15, 16, 16) == 0
     sj.stream_infer_dev(d, 1, 1024 * 15, 32768, lab, None, None, None, 16, 16)  # no window fits: a no-op
+
+
+@pytest.mark.parametrize("W,S,n_samples,carry", [(16, 16, 16384 * 5, False), (16, 1, 16000 * 4 + 517, False),
+                                                 (8, 4, 1024 * 60 + 8, True), (16, 4, 1024 * 48 + 3, False)])
+def test_pcm16_stream_equals_float_stream(W, S, n_samples, carry):
+    """int16 PCM channels give bit-identical windows to the float entry point on s / 32768 (the conversion is exact
+    in fp32), TMA path (rows 16-byte aligned) and the ragged plain-load path alike"""
+    import torch
+    sj = _ctx()
+    n_channels = 5
+    g = torch.Generator(device="cpu").manual_seed(1234 + W * 100 + S)
+    stride = n_samples + (8 - n_samples % 8) % 8 + (0 if n_samples % 8 == 0 else 3)  # odd stride on the ragged cases
+    pcm = torch.randint(-32768, 32768, (n_channels, stride), dtype=torch.int16, generator=g)
+    t = torch.arange(stride, dtype=torch.float32)
+    tone = (6000 * torch.sin(2 * np.pi * 3100 * t / 16000)).to(torch.int16)
+    pcm = (pcm // 8 + tone).to(torch.int16).cuda()
+    prev16 = torch.randint(-3000, 3000, (n_channels, 1024), dtype=torch.int16, generator=g).cuda() if carry else None
+    f = pcm.to(torch.float32) / 32768.0
+    prevf = None if prev16 is None else prev16.to(torch.float32) / 32768.0
+    ref = _run(sj, f, n_channels, n_samples, stride, W, S, prevf)
+    nw = sj.stream_windows(n_samples, W, S)
+    labels = torch.full((n_channels, nw), -1, dtype=torch.int32, device="cuda")
+    conf = torch.empty((n_channels, nw), dtype=torch.float32, device="cuda")
+    score = torch.empty((n_channels, nw), dtype=torch.float32, device="cuda")
+    feats = torch.empty((n_channels, nw, 40), dtype=torch.float32, device="cuda")
+    sj.stream_infer_pcm16_dev(pcm, n_channels, n_samples, stride, labels, conf, score, feats, W, S, prev16)
+    torch.cuda.synchronize()
+    assert np.array_equal(feats.cpu().numpy(), ref[3])
+    assert np.array_equal(score.cpu().numpy(), ref[2])
+    assert np.array_equal(conf.cpu().numpy(), ref[1])
+    assert np.array_equal(labels.cpu().numpy(), ref[0])
