@@ -257,15 +257,40 @@ def run_ours(args, rank, local_rank, world):
     score = torch.empty(C, dtype=torch.float32, device=dev)
     # weak scaling: rank r owns global clips [r*C, (r+1)*C) of the counter-based synthetic set
     sj.synth_clips_dev(clips, rank * C, C, N_SAMPLES, SEED)
+    # the path's only exchange: the final label/score gather, 8 B per clip.  Default: fused into the kernel (every
+    # result is stored into every rank's arrays through NVLink peer mappings, dsp_b200.sharded.PeerGather);
+    # --gather nccl (or a box without CUDA IPC / peer access) runs two NCCL all-gathers after the kernel instead.
+    peer, gather_mode = None, "none (1 GPU)"
     if dist is not None:
-        all_labels = torch.empty(world * C, dtype=torch.int32, device=dev)
-        all_score = torch.empty(world * C, dtype=torch.float32, device=dev)
+        gather_mode = "nccl all-gather after the kernel"
+        if args.gather == "p2p":
+            from dsp_b200.sharded import PeerGather
+            ok = torch.ones(1, dtype=torch.int32, device=dev)
+            try:
+                peer = PeerGather(sj, C, dist)
+            except Exception as e:  # every rank must take the same path
+                sys.stderr.write("bench.py: rank %d: peer gather unavailable (%s)\n" % (rank, e))
+                ok.zero_()
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 1:
+                gather_mode = "fused into the kernel: peer stores over NVLink (CUDA IPC mappings)"
+            else:
+                if peer is not None:
+                    peer.close()
+                peer = None
+                gather_mode += " (peer mapping failed on some rank)"
+        if peer is None:
+            all_labels = torch.empty(world * C, dtype=torch.int32, device=dev)
+            all_score = torch.empty(world * C, dtype=torch.float32, device=dev)
 
     def step():
-        sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
-        if dist is not None:  # the path's only exchange: final label/score gather, 8 B per clip
-            dist.all_gather_into_tensor(all_labels, labels)
-            dist.all_gather_into_tensor(all_score, score)
+        if peer is not None:
+            sj.infer_batch_gather_dev(clips, C, N_SAMPLES, conf)
+        else:
+            sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
+            if dist is not None:
+                dist.all_gather_into_tensor(all_labels, labels)
+                dist.all_gather_into_tensor(all_score, score)
 
     for _ in range(args.warmup):
         step()
@@ -281,6 +306,14 @@ def run_ours(args, rank, local_rank, world):
         barrier()
     total_ms = ev[0].elapsed_time(ev[args.steps])
     launches = sj.launch_count - launches0
+    if peer is not None:  # the gathered arrays must hold this rank's results at its slots and be complete
+        sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
+        torch.cuda.synchronize()
+        assert torch.equal(peer.labels[rank * C:(rank + 1) * C], labels), "fused gather: own slots differ"
+        assert torch.equal(peer.score[rank * C:(rank + 1) * C], score), "fused gather: own slots differ"
+        cnt = torch.tensor([int(labels.sum().item())], dtype=torch.int64, device=dev)
+        dist.all_reduce(cnt)
+        assert int(peer.labels.sum().item()) == int(cnt.item()), "fused gather: arrays incomplete"
     # kernel-only time, measured live: events bracketing the kernel alone (no gather), same stream
     for i in range(min(args.steps, 5)):
         sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
@@ -382,7 +415,8 @@ def run_ours(args, rank, local_rank, world):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "batched cepstrum features + SVM on 1M synthetic 1 s 16 kHz mono clips, per GPU",
                        "clips_per_gpu": C, "n_samples": N_SAMPLES, "frames_per_clip": FRAMES_PER_CLIP,
-                       "sharding": "clip-sharded x%d, label/score all-gather (8 B/clip) inside each step" % world,
+                       "sharding": "clip-sharded x%d, label/score gather (8 B/clip) inside each step" % world,
+                       "gather": gather_mode,
                        "l2": "inputs (%.0f GB/GPU) >> L2, no flush needed" % (C * N_SAMPLES * 4 / 1e9),
                        "timing": "CUDA events on the launching stream, max over ranks"},
             "frames_per_s": value * FRAMES_PER_CLIP,
@@ -405,6 +439,8 @@ def run_ours(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
         os.dup2(2, 1)
     barrier()
+    if peer is not None:
+        peer.close()
     sj.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -421,6 +457,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--ref-clips-per-thread", type=int, default=1024)
+    ap.add_argument("--gather", choices=["p2p", "nccl"], default="p2p",
+                    help="N > 1: fused peer-store gather inside the kernel (default) or NCCL all-gathers after it")
     ap.add_argument("--no-pcm16", dest="pcm16", action="store_false", help="skip the int16 PCM ingest measurement")
     ap.add_argument("--pcm16-clips", type=int, default=500000)
     ap.add_argument("--no-donut", dest="donut", action="store_false", help="skip the donut-path measurement")

@@ -33,6 +33,8 @@ F32, F64 = 0, 1                  # element type of the donut stage functions
 IIR_EXACT, IIR_SCAN = 0, 1       # one recurrence per lane (bit-identical) / block-wise state-space scan over time
 BUTTER_16K, BUTTER_48K_DESIGN = 0, 1
 DONUT_MAX_MID = 8
+MAX_PEERS = 8
+PEER_HANDLE_BYTES = 64
 
 
 class ScrubJayError(RuntimeError):
@@ -62,6 +64,12 @@ def load_library():
     L.scrubjay_predict_batch_dev.argtypes = [vp, vp, c_long, vp, vp, vp]
     L.scrubjay_infer_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_infer_batch_pcm16_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_peer_alloc.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp), vp]
+    L.scrubjay_peer_free.argtypes = [vp, vp]
+    L.scrubjay_peer_open.argtypes = [vp, vp, ctypes.POINTER(vp)]
+    L.scrubjay_peer_close.argtypes = [vp, vp]
+    L.scrubjay_gather_bind.argtypes = [vp, c_int, vp, vp, c_long]
+    L.scrubjay_infer_batch_gather_dev.argtypes = [vp, vp, c_long, c_int, vp, vp]
     L.scrubjay_infer_batch_pcm16.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_wav_parse.argtypes = [vp, ctypes.c_size_t, vp]
     L.scrubjay_decode_pcm16_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
@@ -196,6 +204,36 @@ class ScrubJay:
         self._check(self._L.scrubjay_infer_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_labels),
                                                      _ptr(d_conf), _ptr(d_score), _ptr(d_feats)))
 
+    # ---- fused multi-GPU gather (peer stores over NVLink instead of a collective after the kernel)
+    def peer_alloc(self, nbytes, want_handle=True):
+        """-> (device address, 64-byte IPC handle or None)"""
+        p = ctypes.c_void_p()
+        h = (ctypes.c_ubyte * PEER_HANDLE_BYTES)() if want_handle else None
+        self._check(self._L.scrubjay_peer_alloc(self._h, nbytes, ctypes.byref(p), h))
+        return p.value, (bytes(h) if want_handle else None)
+
+    def peer_free(self, addr):
+        self._check(self._L.scrubjay_peer_free(self._h, addr))
+
+    def peer_open(self, handle):
+        p = ctypes.c_void_p()
+        buf = (ctypes.c_ubyte * PEER_HANDLE_BYTES).from_buffer_copy(bytes(handle))
+        self._check(self._L.scrubjay_peer_open(self._h, buf, ctypes.byref(p)))
+        return p.value
+
+    def peer_close(self, addr):
+        self._check(self._L.scrubjay_peer_close(self._h, addr))
+
+    def gather_bind(self, peer_labels, peer_score=None, out_base=0):
+        """peer_labels / peer_score: device addresses (or tensors), one per rank, in rank order."""
+        n = len(peer_labels)
+        la = (ctypes.c_void_p * max(n, 1))(*[_ptr(x) for x in peer_labels])
+        sa = (ctypes.c_void_p * max(n, 1))(*[_ptr(x) for x in peer_score]) if peer_score is not None else None
+        self._check(self._L.scrubjay_gather_bind(self._h, n, la, sa, out_base))
+
+    def infer_batch_gather_dev(self, d_clips, n_clips, n_samples, d_conf=None, d_feats=None):
+        self._check(self._L.scrubjay_infer_batch_gather_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_conf),
+                                                            _ptr(d_feats)))
 
     def stream_windows(self, n_samples, win_frames=16, step_frames=16):
         return self._L.scrubjay_stream_windows(n_samples, win_frames, step_frames)

@@ -311,7 +311,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
         __syncwarp();
         if (a.do_svm) {
             const SvmOut r = svm_eval(a.tables, lg, lane);
-            if (lane == 0) {
+            if (a.peers) { // fused gather: lane p stores the result into rank p's arrays (its own, or a peer's over NVLink)
+                if (lane < a.peers->n_peers) {
+                    const long at = a.peers->out_base + out;
+                    a.peers->labels[lane][at] = r.label;
+                    float *ps = a.peers->score[lane];
+                    if (ps) ps[at] = r.score;
+                }
+                if (lane == 0 && a.conf) a.conf[out] = r.conf;
+            } else if (lane == 0) {
                 if (a.labels) a.labels[out] = r.label;
                 if (a.conf) a.conf[out] = r.conf;
                 if (a.score) a.score[out] = r.score;

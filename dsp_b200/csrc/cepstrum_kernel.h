@@ -5,6 +5,16 @@
 
 #include "sj_tables.h"
 
+// gather targets of the fused multi-GPU result gather (device memory, written by scrubjay_gather_bind): label /
+// score of output index i go to labels[p][out_base + i], score[p][out_base + i], p < n_peers
+#define SJ_KMAX_PEERS 8
+struct SjPeerTable {
+    int32_t *labels[SJ_KMAX_PEERS];
+    float *score[SJ_KMAX_PEERS];
+    long out_base;
+    int n_peers, pad;
+};
+
 struct SjCepstrumArgs {
     const float *clips;   // [n_clips][n_samples], device (int16_t samples when pcm16 != 0)
     int pcm16;            // clips are int16 PCM, converted as s / 32768 in the kernel (clip mode only)
@@ -16,6 +26,7 @@ struct SjCepstrumArgs {
     float *score;         // [n_clips] or NULL
     float *feats;         // [n_clips][40] or NULL
     int do_svm;           // 0: features only
+    const SjPeerTable *peers; // non-NULL: labels / score go to every target of the table instead of labels / score
     // stream mode (n_windows > 0): `clips` holds n_clips channels of n_samples samples, chan_stride apart; the
     // pvoc runs on continuously; window j covers frames [j*step_frames, j*step_frames + win_frames) and the
     // outputs are [channel][window].  prev_hop ([n_clips][1024] or NULL) is the hop before sample 0 (carried

@@ -61,6 +61,10 @@ struct scrubjay_ctx {
     size_t kw_stage_bytes = 0;
     long kw_stage_clips = 0;
     int stream_chunk_windows = 0; // 0 = automatic work-item size of the stream mode
+    // fused multi-GPU gather (scrubjay_gather_bind): the target table on the device
+    SjPeerTable *d_peers = nullptr;
+    int n_peers = 0;
+    int peer_access_on[SJ_MAX_PEERS * 2] = {0}; // devices this context has enabled peer access to (index = device id)
     // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
     void *d_donut_tables[SJ_DONUT_N_VARIANTS] = {nullptr, nullptr, nullptr, nullptr};
     int donut_grid[SJ_DONUT_N_VARIANTS] = {0, 0, 0, 0};
@@ -139,10 +143,12 @@ int ensure_stages(scrubjay_ctx *c, int n_samples)
 }
 
 int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, long n_clips, int n_samples,
-                    int32_t *labels, float *conf, float *score, float *feats, int do_svm, bool timed, int pcm16 = 0)
+                    int32_t *labels, float *conf, float *score, float *feats, int do_svm, bool timed, int pcm16 = 0,
+                    const SjPeerTable *peers = nullptr)
 {
     SjCepstrumArgs a;
     a.pcm16 = pcm16;
+    a.peers = peers;
     a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
     a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
     a.chan_stride = 0; a.prev_hop = nullptr; a.n_windows = 0; a.win_frames = a.step_frames = 0;
@@ -215,6 +221,7 @@ void scrubjay_destroy(scrubjay_ctx *c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
+    cudaFree(c->d_peers);
     for (void *t : c->d_donut_tables) cudaFree(t);
     cudaFree(c->d_donut_scratch);
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
@@ -289,6 +296,98 @@ int scrubjay_infer_batch_pcm16_dev(scrubjay_ctx *c, const int16_t *d_clips, long
     SJ_CUDA(c, cudaSetDevice(c->device));
     return launch_cepstrum(c, c->stream, reinterpret_cast<const float *>(d_clips), n_clips, n_samples, d_labels, d_conf,
                            d_score, d_feats, 1, true, 1);
+}
+
+int scrubjay_peer_alloc(scrubjay_ctx *c, size_t bytes, void **d_ptr, unsigned char handle[SJ_PEER_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == SJ_PEER_HANDLE_BYTES, "handle size");
+    if (!c) return SJ_EINVAL;
+    if (!d_ptr || bytes == 0) return set_err(c, SJ_EINVAL, "NULL pointer or empty allocation");
+    *d_ptr = nullptr;
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    void *p = nullptr;
+    SJ_CUDA(c, cudaMalloc(&p, bytes)); // a whole allocation: IPC handles name allocations, not sub-ranges
+    if (handle) {
+        cudaIpcMemHandle_t h;
+        const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+        if (e != cudaSuccess) { cudaFree(p); return set_err(c, SJ_ECUDA, "cudaIpcGetMemHandle", e); }
+        memcpy(handle, &h, sizeof h);
+    }
+    *d_ptr = p;
+    return SJ_OK;
+}
+
+int scrubjay_peer_free(scrubjay_ctx *c, void *d_ptr)
+{
+    if (!c) return SJ_EINVAL;
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, cudaFree(d_ptr));
+    return SJ_OK;
+}
+
+int scrubjay_peer_open(scrubjay_ctx *c, const unsigned char handle[SJ_PEER_HANDLE_BYTES], void **d_ptr)
+{
+    if (!c) return SJ_EINVAL;
+    if (!handle || !d_ptr) return set_err(c, SJ_EINVAL, "NULL pointer");
+    *d_ptr = nullptr;
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    SJ_CUDA(c, cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return SJ_OK;
+}
+
+int scrubjay_peer_close(scrubjay_ctx *c, void *d_ptr)
+{
+    if (!c) return SJ_EINVAL;
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SJ_CUDA(c, cudaIpcCloseMemHandle(d_ptr));
+    return SJ_OK;
+}
+
+int scrubjay_gather_bind(scrubjay_ctx *c, int n_peers, int32_t *const *peer_labels, float *const *peer_score, long out_base)
+{
+    if (!c) return SJ_EINVAL;
+    if (n_peers < 0 || n_peers > SJ_MAX_PEERS || out_base < 0) return set_err(c, SJ_EINVAL, "n_peers out of range or negative base");
+    if (n_peers > 0 && !peer_labels) return set_err(c, SJ_EINVAL, "NULL target list");
+    static_assert(SJ_MAX_PEERS == SJ_KMAX_PEERS, "peer table size");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    SjPeerTable t;
+    memset(&t, 0, sizeof t);
+    for (int p = 0; p < n_peers; ++p) {
+        if (!peer_labels[p]) return set_err(c, SJ_EINVAL, "NULL label target");
+        t.labels[p] = peer_labels[p];
+        t.score[p] = peer_score ? peer_score[p] : nullptr;
+        // same-process targets on another device need peer access; targets mapped with scrubjay_peer_open already have it
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, peer_labels[p]) == cudaSuccess && at.type == cudaMemoryTypeDevice &&
+            at.device != c->device && at.device >= 0 && at.device < SJ_MAX_PEERS * 2 && !c->peer_access_on[at.device]) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return set_err(c, SJ_ECUDA, "cudaDeviceEnablePeerAccess", e);
+            (void)cudaGetLastError();
+            c->peer_access_on[at.device] = 1;
+        } else (void)cudaGetLastError();
+    }
+    t.out_base = out_base;
+    t.n_peers = n_peers;
+    if (!c->d_peers) SJ_CUDA(c, cudaMalloc(&c->d_peers, sizeof(SjPeerTable)));
+    // stream-ordered with respect to the launches that use the table
+    SJ_CUDA(c, cudaMemcpyAsync(c->d_peers, &t, sizeof t, cudaMemcpyHostToDevice, c->stream));
+    SJ_CUDA(c, cudaStreamSynchronize(c->stream)); // `t` is on the stack
+    c->n_peers = n_peers;
+    return SJ_OK;
+}
+
+int scrubjay_infer_batch_gather_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, float *d_conf,
+                                    float *d_feats)
+{
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    if (c->n_peers <= 0) return set_err(c, SJ_EINVAL, "no gather targets bound (scrubjay_gather_bind)");
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    return launch_cepstrum(c, c->stream, d_clips, n_clips, n_samples, nullptr, d_conf, nullptr, d_feats, 1, true, 0,
+                           c->d_peers);
 }
 
 int scrubjay_wav_parse(const void *bytes, size_t n, scrubjay_wav_info *info)
@@ -393,6 +492,7 @@ static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_chann
     SJ_CUDA(c, cudaSetDevice(c->device));
     SjCepstrumArgs a;
     a.pcm16 = pcm16;
+    a.peers = nullptr;
     a.clips = reinterpret_cast<const float *>(d_streams); a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
     a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
     a.chan_stride = chan_stride; a.prev_hop = reinterpret_cast<const float *>(d_prev_hop); a.n_windows = nw;

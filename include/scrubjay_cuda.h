@@ -88,6 +88,34 @@ SJ_API int scrubjay_predict_batch_dev(scrubjay_ctx *ctx, const float *d_feats, l
 SJ_API int scrubjay_infer_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                              int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
 
+/* ---- multi-GPU result gather fused into the kernel (clips are sharded by contiguous ranges, the path's
+ * only exchange is the final gather of label int32 + score fp32 = 8 B per clip).  The reference has no counterpart:
+ * its main loop prints every file's label as it goes (cepstrum/scrubjay_infer.c:166-176).  Instead of a collective
+ * after the kernel, the kernel itself stores every clip's label and score into the result arrays of ALL ranks
+ * (its own and, through NVLink/NVSwitch peer mappings, the other GPUs'), so that when the kernels of all ranks have
+ * finished every rank holds the complete arrays.  One process per GPU: each rank allocates its result arrays
+ * with scrubjay_peer_alloc, hands the 64-byte handles to the other ranks over any transport it likes, and maps theirs
+ * with scrubjay_peer_open (CUDA IPC).  In a single process the arrays of other devices can be passed as they are
+ * (after cudaDeviceEnablePeerAccess). */
+#define SJ_MAX_PEERS 8
+#define SJ_PEER_HANDLE_BYTES 64
+/* device allocation on the context's GPU that other processes can map; `handle` may be NULL */
+SJ_API int scrubjay_peer_alloc(scrubjay_ctx *ctx, size_t bytes, void **d_ptr, unsigned char handle[SJ_PEER_HANDLE_BYTES]);
+SJ_API int scrubjay_peer_free(scrubjay_ctx *ctx, void *d_ptr);
+/* map / unmap an allocation exported by another process (peer access is enabled as needed) */
+SJ_API int scrubjay_peer_open(scrubjay_ctx *ctx, const unsigned char handle[SJ_PEER_HANDLE_BYTES], void **d_ptr);
+SJ_API int scrubjay_peer_close(scrubjay_ctx *ctx, void *d_ptr);
+/* Bind the gather targets: result i of a later scrubjay_infer_batch_gather_dev goes to
+ * peer_labels[p][out_base + i] and peer_score[p][out_base + i] for every p < n_peers (the caller's own arrays are
+ * one of the entries; peer_score may be NULL or hold NULL entries).  n_peers = 0 unbinds. */
+SJ_API int scrubjay_gather_bind(scrubjay_ctx *ctx, int n_peers, int32_t *const *peer_labels, float *const *peer_score,
+                         long out_base);
+/* scrubjay_infer_batch_dev with the labels and scores stored to every bound target.  Stream-ordered like every
+ * *_dev call; the arrays of a rank are complete once the calls of all ranks have completed (the caller's own
+ * barrier).  d_conf, d_feats (local, [n_clips]...) may be NULL. */
+SJ_API int scrubjay_infer_batch_gather_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
+                                    float *d_conf, float *d_feats);
+
 /* int16 PCM input: the format the reference actually reads (WAV decoded by aubio_source_do,
  * cepstrum/scrubjay_infer.c:21,41; `data[i] / 32768` at donut-classifier/classifier.c:56-60).  Clips are
  * [n_clips][n_samples] int16 mono; the conversion x = s / 32768 is exact and done inside the kernel, so the
