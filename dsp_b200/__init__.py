@@ -85,6 +85,8 @@ def load_library():
     L.scrubjay_stream_windows.restype = c_long
     L.scrubjay_stream_infer_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
     L.scrubjay_stream_infer_pcm16_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp, vp, vp]
+    L.scrubjay_stream_infer_gather_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp]
+    L.scrubjay_stream_infer_pcm16_gather_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp]
     L.scrubjay_set_stream_chunk.argtypes = [vp, c_int]
     L.scrubjay_mfcc_stats.argtypes = [vp, vp, c_long, vp]
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
@@ -252,6 +254,13 @@ class ScrubJay:
         self._check(self._L.scrubjay_stream_infer_pcm16_dev(self._h, _ptr(streams), n_channels, n_samples, chan_stride,
                                                             _ptr(prev_hop), win_frames, step_frames, _ptr(labels),
                                                             _ptr(conf), _ptr(score), _ptr(feats)))
+
+    def stream_infer_gather_dev(self, streams, n_channels, n_samples, chan_stride, conf=None, feats=None,
+                                win_frames=16, step_frames=16, prev_hop=None, pcm16=False):
+        """stream mode with the fused gather: labels / scores go to every target bound with gather_bind."""
+        fn = self._L.scrubjay_stream_infer_pcm16_gather_dev if pcm16 else self._L.scrubjay_stream_infer_gather_dev
+        self._check(fn(self._h, _ptr(streams), n_channels, n_samples, chan_stride, _ptr(prev_hop), win_frames,
+                       step_frames, _ptr(conf), _ptr(feats)))
 
     def set_stream_chunk(self, windows_per_item):
         self._check(self._L.scrubjay_set_stream_chunk(self._h, windows_per_item))

@@ -459,7 +459,7 @@ long scrubjay_stream_windows(long n_samples, int win_frames, int step_frames)
 
 static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_channels, long n_samples, long chan_stride,
                             const void *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
-                            float *d_conf, float *d_score, float *d_feats, int pcm16);
+                            float *d_conf, float *d_score, float *d_feats, int pcm16, bool gather = false);
 
 int scrubjay_stream_infer_dev(scrubjay_ctx *c, const float *d_streams, long n_channels, long n_samples, long chan_stride,
                               const float *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
@@ -477,12 +477,29 @@ int scrubjay_stream_infer_pcm16_dev(scrubjay_ctx *c, const int16_t *d_streams, l
                             d_conf, d_score, d_feats, 1);
 }
 
+int scrubjay_stream_infer_gather_dev(scrubjay_ctx *c, const float *d_streams, long n_channels, long n_samples,
+                                     long chan_stride, const float *d_prev_hop, int win_frames, int step_frames,
+                                     float *d_conf, float *d_feats)
+{
+    return stream_infer_any(c, d_streams, n_channels, n_samples, chan_stride, d_prev_hop, win_frames, step_frames, nullptr,
+                            d_conf, nullptr, d_feats, 0, true);
+}
+
+int scrubjay_stream_infer_pcm16_gather_dev(scrubjay_ctx *c, const int16_t *d_streams, long n_channels, long n_samples,
+                                           long chan_stride, const int16_t *d_prev_hop, int win_frames, int step_frames,
+                                           float *d_conf, float *d_feats)
+{
+    return stream_infer_any(c, d_streams, n_channels, n_samples, chan_stride, d_prev_hop, win_frames, step_frames, nullptr,
+                            d_conf, nullptr, d_feats, 1, true);
+}
+
 static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_channels, long n_samples, long chan_stride,
                             const void *d_prev_hop, int win_frames, int step_frames, int32_t *d_labels,
-                            float *d_conf, float *d_score, float *d_feats, int pcm16)
+                            float *d_conf, float *d_score, float *d_feats, int pcm16, bool gather)
 {
     if (!c) return SJ_EINVAL;
-    if (!d_streams || !d_labels || n_channels < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (!d_streams || (!d_labels && !gather) || n_channels < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (gather && c->n_peers <= 0) return set_err(c, SJ_EINVAL, "no gather targets bound (scrubjay_gather_bind)");
     if (n_samples <= 0 || n_samples > 0x7fffffffL) return set_err(c, SJ_EINVAL, "samples per channel must be in 1 .. 2^31-1");
     if (chan_stride < n_samples) return set_err(c, SJ_EINVAL, "channel stride shorter than the channel");
     if (win_frames < 1 || win_frames > SJ_STREAM_MAX_WIN || step_frames < 1 || step_frames > win_frames)
@@ -492,7 +509,7 @@ static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_chann
     SJ_CUDA(c, cudaSetDevice(c->device));
     SjCepstrumArgs a;
     a.pcm16 = pcm16;
-    a.peers = nullptr;
+    a.peers = gather ? c->d_peers : nullptr;
     a.clips = reinterpret_cast<const float *>(d_streams); a.n_clips = n_channels; a.n_samples = (int)n_samples; a.tables = c->d_tables;
     a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
     a.chan_stride = chan_stride; a.prev_hop = reinterpret_cast<const float *>(d_prev_hop); a.n_windows = nw;

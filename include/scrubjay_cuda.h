@@ -170,6 +170,15 @@ SJ_API int scrubjay_stream_infer_dev(scrubjay_ctx *ctx, const float *d_streams, 
 SJ_API int scrubjay_stream_infer_pcm16_dev(scrubjay_ctx *ctx, const int16_t *d_streams, long n_channels, long n_samples,
                                            long chan_stride, const int16_t *d_prev_hop, int win_frames, int step_frames,
                                            int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+/* Stream mode with the fused multi-GPU gather (scrubjay_gather_bind): window j of channel c of this call is result
+ * c * n_windows + j, stored at out_base + that index into every bound target (channels are sharded over ranks, so
+ * out_base = first channel of the rank * n_windows). */
+SJ_API int scrubjay_stream_infer_gather_dev(scrubjay_ctx *ctx, const float *d_streams, long n_channels, long n_samples,
+                                     long chan_stride, const float *d_prev_hop, int win_frames, int step_frames,
+                                     float *d_conf, float *d_feats);
+SJ_API int scrubjay_stream_infer_pcm16_gather_dev(scrubjay_ctx *ctx, const int16_t *d_streams, long n_channels,
+                                           long n_samples, long chan_stride, const int16_t *d_prev_hop, int win_frames,
+                                           int step_frames, float *d_conf, float *d_feats);
 /* windows per work item of the stream mode (0 = automatic); a tuning / test knob */
 SJ_API int scrubjay_set_stream_chunk(scrubjay_ctx *ctx, int windows_per_item);
 

@@ -76,3 +76,26 @@ def test_peer_alloc_round_trip(sj):
     assert int(v.sum().item()) == 3072
     del v
     sj.peer_free(addr)
+
+
+def test_stream_mode_gather(sj):
+    nch, secs, W, S = 6, 9, 16, 8
+    ns = secs * NS
+    d = torch.empty((nch * secs, NS), device="cuda")
+    sj.synth_clips_dev(d, 100, nch * secs, NS)
+    nw = sj.stream_windows(ns, W, S)
+    lab = torch.empty((nch, nw), dtype=torch.int32, device="cuda")
+    sc = torch.empty((nch, nw), device="cuda")
+    sj.stream_infer_dev(d, nch, ns, ns, lab, None, sc, None, W, S)
+    base = 3 * nw  # as if three channels of other ranks came first
+    tl = [torch.full((nch * nw + base + 4,), -7, dtype=torch.int32, device="cuda") for _ in range(2)]
+    ts = [torch.full((nch * nw + base + 4,), -7.0, device="cuda") for _ in range(2)]
+    sj.gather_bind(tl, ts, base)
+    sj.stream_infer_gather_dev(d, nch, ns, ns, win_frames=W, step_frames=S)
+    torch.cuda.synchronize()
+    for l, s in zip(tl, ts):
+        assert torch.equal(l[base:base + nch * nw], lab.reshape(-1)) and torch.equal(s[base:base + nch * nw], sc.reshape(-1))
+        assert bool((l[:base] == -7).all()) and bool((l[base + nch * nw:] == -7).all())
+    sj.gather_bind([], None, 0)
+    with pytest.raises(dsp_b200.ScrubJayError):
+        sj.stream_infer_gather_dev(d, nch, ns, ns, win_frames=W, step_frames=S)
