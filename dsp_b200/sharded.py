@@ -63,28 +63,62 @@ class PeerGather:
         if self.world > 8:
             raise ValueError("at most 8 peers (one NVSwitch domain)")
         self.total, self.base = gather_layout(n_per_rank, self.rank, self.world)
-        self.l_addr, l_h = sj.peer_alloc(self.total * 4)
-        self.s_addr, s_h = sj.peer_alloc(self.total * 4)
         if exchange is None:
             def exchange(item):
                 out = [None] * self.world
                 dist.all_gather_object(out, item)
                 return out
-        handles = exchange((l_h, s_h))
+        # Every step below is collective: a rank that fails locally still takes part in both exchanges (with its
+        # error text), so that all ranks raise together instead of one of them waiting for the others for ever.
+        self.l_addr = self.s_addr = None
         self.opened = []
+        mine = err = None
+        try:
+            self.l_addr, l_h = sj.peer_alloc(self.total * 4)
+            self.s_addr, s_h = sj.peer_alloc(self.total * 4)
+            mine = (l_h, s_h)
+        except Exception as e:
+            err = "rank %d: %s" % (self.rank, e)
+        handles = exchange(mine if err is None else ("error", err))
+        bad = [h[1] for h in handles if h[0] == "error"]
         pl, ps = [], []
-        for r, (hl, hs) in enumerate(handles):
-            if r == self.rank:
-                pl.append(self.l_addr)
-                ps.append(self.s_addr)
-            else:
-                a, b = sj.peer_open(hl), sj.peer_open(hs)
-                self.opened += [a, b]
-                pl.append(a)
-                ps.append(b)
+        if not bad:
+            try:
+                for r, (hl, hs) in enumerate(handles):
+                    if r == self.rank:
+                        pl.append(self.l_addr)
+                        ps.append(self.s_addr)
+                    else:
+                        a = sj.peer_open(hl)
+                        self.opened.append(a)
+                        b = sj.peer_open(hs)
+                        self.opened.append(b)
+                        pl.append(a)
+                        ps.append(b)
+                sj.gather_bind(pl, ps, self.base)
+            except Exception as e:
+                err = "rank %d: %s" % (self.rank, e)
+        bad += [m for m in exchange(err) if m]
+        if bad:
+            self._release()
+            raise RuntimeError("peer gather unavailable: " + "; ".join(bad))
         self.peer_labels, self.peer_score = pl, ps
-        sj.gather_bind(pl, ps, self.base)
         self._views = None
+
+    def _release(self):
+        for a in self.opened:
+            try:
+                self.sj.peer_close(a)
+            except Exception:
+                pass
+        self.opened = []
+        for a in (self.l_addr, self.s_addr):
+            if a:
+                try:
+                    self.sj.peer_free(a)
+                except Exception:
+                    pass
+        self.l_addr = self.s_addr = None
 
     def _view(self):
         if self._views is None:
@@ -111,7 +145,6 @@ class PeerGather:
         for a in self.opened:
             self.sj.peer_close(a)
         self.opened = []
-        self.dist.barrier()
+        self.dist.barrier()  # nobody maps these arrays any more
         self._views = None
-        self.sj.peer_free(self.l_addr)
-        self.sj.peer_free(self.s_addr)
+        self._release()

@@ -73,11 +73,46 @@ def _worker(rank, world, port, shm):
     want_l = np.concatenate([100 * r + np.arange(N_PER_RANK) for r in range(world)])
     want_s = np.concatenate([r + np.arange(N_PER_RANK) / 16.0 for r in range(world)]).astype(np.float32)
     assert np.array_equal(lab, want_l) and np.array_equal(sco, want_s)
+    own = sorted([g.l_addr, g.s_addr])
     g.close()
     assert ctx.bound == ([], None, 0)
-    assert len(ctx.closed) == 2 * (world - 1) and sorted(ctx.freed) == sorted([g.l_addr, g.s_addr])
+    assert len(ctx.closed) == 2 * (world - 1) and sorted(ctx.freed) == own
     dist.barrier()
     dist.destroy_process_group()
+
+
+def _worker_fail(rank, world, port, shm):
+    """rank 1 cannot allocate: both ranks must raise (nobody may be left waiting in the exchange)."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from dsp_b200.sharded import PeerGather
+
+    class Broken(FakeCtx):
+        def peer_alloc(self, nbytes, want_handle=True):
+            if self.rank == 1:
+                raise RuntimeError("out of memory (simulated)")
+            return super().peer_alloc(nbytes, want_handle)
+
+    class NoOpen(FakeCtx):
+        def peer_open(self, handle):
+            if self.rank == 0:
+                raise RuntimeError("peer access unsupported (simulated)")
+            return super().peer_open(handle)
+
+    for cls, what in ((Broken, "out of memory"), (NoOpen, "peer access unsupported")):
+        ctx = cls(rank, shm)
+        with pytest.raises(RuntimeError, match=what):
+            PeerGather(ctx, N_PER_RANK, dist)
+        assert len(ctx.freed) == (0 if (cls is Broken and rank == 1) else 2)  # what was allocated is released
+        dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_failure_is_collective(tmp_path):
+    port = 33500 + os.getpid() % 2000
+    mp.spawn(_worker_fail, args=(2, port, str(tmp_path)), nprocs=2, join=True)
 
 
 def test_two_rank_peer_gather_host_logic(tmp_path):
