@@ -4,7 +4,7 @@
 // mfcc_stats (cepstrum/scrubjay_infer.c:19-77: aubio_pvoc_do + aubio_mfcc_do per hop, mean/std over
 // hops) followed by ort_predict (:105-141: ONNX Scaler + SVMClassifier).
 //
-// Mapping: persistent grid, one CTA per SM, each WARP owns whole clips (clip = warp id + k*stride)
+// Mapping: persistent grid, one CTA per SM, each WARP owns whole clips (clip = CTA + grid * warp + k*stride)
 // and walks their hops in order, so no block-level synchronisation exists after the prologue.
 //   * HBM -> shared: every hop (1024 samples, 4 KB) is fetched exactly once by a bulk async copy
 //     (cp.async.bulk, the TMA engine) into a 2-slot per-warp ring, completion on an mbarrier; hop
@@ -230,7 +230,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const int last_valid = n_samples - (F - 1) * SJ_HOP;
     const long stride = long(gridDim.x) * WARPS;
     const long n_items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
-    long item = long(blockIdx.x) * WARPS + warp;
+    // items are dealt to CTAs first and to the warps of a CTA second, so that a batch smaller than the resident
+    // warp count spreads over the SMs instead of filling a few of them (latency of small batches: one warp alone on
+    // an SM walks a clip in 42 us, twelve sharing one SM take 72 us); for large batches this is only a permutation
+    long item = long(warp) * gridDim.x + blockIdx.x;
     const int W = a.win_frames, S = a.step_frames;
     // hann[64 m1 + 2 lane + d] = 0.5 - 0.5 cos(a + b), a = 2 pi m1/32, b = pi (2 lane + d)/1024
     float2 sb, cb;
@@ -648,8 +651,7 @@ cudaError_t launch_one(const SjCepstrumArgs &a, int maxseg, int num_sms, cudaStr
 {
     constexpr int W = warps_of<STREAM, PCM16>();
     const long items = STREAM ? a.n_clips * a.chunks_per_chan : a.n_clips;
-    long ctas = (items + W - 1) / W;
-    if (ctas > num_sms) ctas = num_sms;
+    long ctas = items < num_sms ? items : num_sms;
     cepstrum_kernel<W, TMA, FAST, STREAM, PCM16>
         <<<(unsigned)ctas, W * 32, smem_bytes<W>(maxseg, STREAM, PCM16), stream>>>(a, maxseg);
     return cudaGetLastError();
