@@ -88,6 +88,7 @@ def load_library():
     L.scrubjay_stream_infer_gather_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp]
     L.scrubjay_stream_infer_pcm16_gather_dev.argtypes = [vp, vp, c_long, c_long, c_long, vp, c_int, c_int, vp, vp]
     L.scrubjay_set_stream_chunk.argtypes = [vp, c_int]
+    L.scrubjay_set_latency_mode.argtypes = [vp, c_int]
     L.scrubjay_mfcc_stats.argtypes = [vp, vp, c_long, vp]
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
     L.scrubjay_infer_batch.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
@@ -261,6 +262,10 @@ class ScrubJay:
         fn = self._L.scrubjay_stream_infer_pcm16_gather_dev if pcm16 else self._L.scrubjay_stream_infer_gather_dev
         self._check(fn(self._h, _ptr(streams), n_channels, n_samples, chan_stride, _ptr(prev_hop), win_frames,
                        step_frames, _ptr(conf), _ptr(feats)))
+
+    def set_latency_mode(self, on):
+        """frame-parallel path for small batches (default on); False forces the one-kernel path"""
+        self._check(self._L.scrubjay_set_latency_mode(self._h, 1 if on else 0))
 
     def set_stream_chunk(self, windows_per_item):
         self._check(self._L.scrubjay_set_stream_chunk(self._h, windows_per_item))

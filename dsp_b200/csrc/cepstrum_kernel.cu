@@ -187,6 +187,45 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
     return r;
 }
 
+// window statistics (cepstrum/scrubjay_infer.c:61-67) -> Scaler -> SVM -> outputs at index `out`; `lg` is a
+// per-warp shared scratch of >= 40 floats; all 32 lanes call, lanes < 20 hold the sums of their coefficient
+__device__ __forceinline__ void sj_emit(const SjCepstrumArgs &a, float *lg, int lane, long out, double sum, double sq,
+                                        int nframes)
+{
+    __syncwarp();
+    if (lane < SJ_NCOEF) {
+        const double mean = sum / (double)nframes;
+        const double var = sq / (double)nframes - mean * mean;
+        const float fm = (float)mean;
+        const float fs = sqrtf((float)(var > 0 ? var : 0));
+        if (a.feats) {
+            a.feats[out * SJ_FEAT + lane] = fm;
+            a.feats[out * SJ_FEAT + SJ_NCOEF + lane] = fs;
+        }
+        const SjTables *G = a.tables;
+        lg[lane] = (fm - __ldg(&G->sv_off[lane])) * __ldg(&G->sv_scale[lane]);
+        lg[lane + SJ_NCOEF] = (fs - __ldg(&G->sv_off[lane + SJ_NCOEF])) * __ldg(&G->sv_scale[lane + SJ_NCOEF]);
+    }
+    __syncwarp();
+    if (a.do_svm) {
+        const SvmOut r = svm_eval(a.tables, lg, lane);
+        if (a.peers) { // fused gather: lane p stores the result into rank p's arrays (its own, or a peer's over NVLink)
+            if (lane < a.peers->n_peers) {
+                const long at = a.peers->out_base + out;
+                a.peers->labels[lane][at] = r.label;
+                float *ps = a.peers->score[lane];
+                if (ps) ps[at] = r.score;
+            }
+            if (lane == 0 && a.conf) a.conf[out] = r.conf;
+        } else if (lane == 0) {
+            if (a.labels) a.labels[out] = r.label;
+            if (a.conf) a.conf[out] = r.conf;
+            if (a.score) a.score[out] = r.score;
+        }
+    }
+    __syncwarp();
+}
+
 // FAST: the 16 kHz layout (28-bin lane chunks, static flush slots, <= 5 combine entries, mirror bins of
 // the first 4 untangling rows skipped); otherwise every mel parameter is read from the tables.
 // STREAM: the batch is a set of long channels cut into work items of `chunk_windows` analysis windows; the
@@ -295,41 +334,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             __syncwarp();
         }
     };
-    // window statistics (cepstrum/scrubjay_infer.c:61-67) -> Scaler -> SVM -> outputs at index `out`
-    auto emit = [&](long out, double sum, double sq, int nframes) {
-        __syncwarp();
-        if (lane < SJ_NCOEF) {
-            const double mean = sum / (double)nframes;
-            const double var = sq / (double)nframes - mean * mean;
-            const float fm = (float)mean;
-            const float fs = sqrtf((float)(var > 0 ? var : 0));
-            if (a.feats) {
-                a.feats[out * SJ_FEAT + lane] = fm;
-                a.feats[out * SJ_FEAT + SJ_NCOEF + lane] = fs;
-            }
-            const SjTables *G = a.tables;
-            lg[lane] = (fm - __ldg(&G->sv_off[lane])) * __ldg(&G->sv_scale[lane]);
-            lg[lane + SJ_NCOEF] = (fs - __ldg(&G->sv_off[lane + SJ_NCOEF])) * __ldg(&G->sv_scale[lane + SJ_NCOEF]);
-        }
-        __syncwarp();
-        if (a.do_svm) {
-            const SvmOut r = svm_eval(a.tables, lg, lane);
-            if (a.peers) { // fused gather: lane p stores the result into rank p's arrays (its own, or a peer's over NVLink)
-                if (lane < a.peers->n_peers) {
-                    const long at = a.peers->out_base + out;
-                    a.peers->labels[lane][at] = r.label;
-                    float *ps = a.peers->score[lane];
-                    if (ps) ps[at] = r.score;
-                }
-                if (lane == 0 && a.conf) a.conf[out] = r.conf;
-            } else if (lane == 0) {
-                if (a.labels) a.labels[out] = r.label;
-                if (a.conf) a.conf[out] = r.conf;
-                if (a.score) a.score[out] = r.score;
-            }
-        }
-        __syncwarp();
-    };
+    auto emit = [&](long out, double sum, double sq, int nframes) { sj_emit(a, lg, lane, out, sum, sq, nframes); };
 
     uint32_t q = 0; // running hop number of this warp: ring slot q&1, mbarrier parity (q>>1)&1
     Seg sg = seg_of(item < n_items ? item : 0);
@@ -620,6 +625,27 @@ __global__ void __launch_bounds__(256) svm_kernel(const float *feats, long n, co
     }
 }
 
+// Second half of the frame-parallel clip mode (small batches): frames[clip][f][40] holds the MFCC vector of every
+// frame in its first 20 floats (written by the STREAM instantiation run with one-frame windows); one warp per clip adds
+// them up in frame order in double, exactly like the per-clip loop, and finishes with the same sj_emit.
+__global__ void __launch_bounds__(128) clip_stats_kernel(const SjCepstrumArgs a, const float *frames, int F)
+{
+    __shared__ float z[4][SJ_FEAT];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long i = (long)blockIdx.x * 4 + warp; i < a.n_clips; i += (long)gridDim.x * 4) {
+        double sum = 0.0, sq = 0.0;
+        if (lane < SJ_NCOEF) {
+            const float *p = frames + i * F * SJ_FEAT + lane;
+            for (int f = 0; f < F; ++f) {
+                const double dv = (double)p[(long)f * SJ_FEAT];
+                sum += dv;
+                sq += dv * dv;
+            }
+        }
+        sj_emit(a, z[warp], lane, i, sum, sq, F);
+    }
+}
+
 template <int WARPS> size_t smem_bytes(int maxseg, bool stream, bool pcm16)
 {
     size_t off = (kHotBytes + 127) & ~size_t(127);
@@ -700,6 +726,15 @@ cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *h, int n
     if (a.pcm16) return a.n_windows > 0 ? launch_any<true, true>(a, h, num_sms, stream) : launch_any<false, true>(a, h, num_sms, stream);
     if (a.n_windows > 0) return launch_any<true, false>(a, h, num_sms, stream);
     return launch_any<false, false>(a, h, num_sms, stream);
+}
+
+cudaError_t sj_launch_clip_stats(const SjCepstrumArgs &a, const float *frames, int n_frames, cudaStream_t stream)
+{
+    if (a.n_clips <= 0) return cudaSuccess;
+    long blocks = (a.n_clips + 3) / 4;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    clip_stats_kernel<<<(unsigned)blocks, 128, 0, stream>>>(a, frames, n_frames);
+    return cudaGetLastError();
 }
 
 int sj_cepstrum_resident_warps(int num_sms) { return num_sms * warps_of<true, false>(); }

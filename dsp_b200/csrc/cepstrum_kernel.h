@@ -43,6 +43,9 @@ struct SjCepstrumArgs {
 // Enqueues the kernel on `stream`.  `host_tables` is the host copy of a.tables (selects the mel layout),
 // `num_sms` the SM count of the device.  Returns the cudaError_t of the launch.
 cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *host_tables, int num_sms, cudaStream_t stream);
+// frame-parallel clip mode, second kernel: per-clip statistics over frames[clip][n_frames][40] (+ Scaler + SVM, outputs
+// as named by `a`; a.clips / stream fields are not used)
+cudaError_t sj_launch_clip_stats(const SjCepstrumArgs &a, const float *frames, int n_frames, cudaStream_t stream);
 // warps the persistent grid keeps resident (work-item sizing of the stream mode)
 int sj_cepstrum_resident_warps(int num_sms);
 // one-time attribute set-up (max dynamic shared memory); returns cudaError_t

@@ -61,6 +61,11 @@ struct scrubjay_ctx {
     size_t kw_stage_bytes = 0;
     long kw_stage_clips = 0;
     int stream_chunk_windows = 0; // 0 = automatic work-item size of the stream mode
+    // frame-parallel clip mode for small batches (scrubjay_set_latency_mode; on by default)
+    int latency_mode = 1;
+    float *d_frame_scratch = nullptr;
+    size_t frame_scratch_bytes = 0;
+    cudaEvent_t frame_scratch_free = nullptr;
     // fused multi-GPU gather (scrubjay_gather_bind): the target table on the device
     SjPeerTable *d_peers = nullptr;
     int n_peers = 0;
@@ -153,6 +158,45 @@ int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, 
     a.labels = labels; a.conf = conf; a.score = score; a.feats = feats; a.do_svm = do_svm;
     a.chan_stride = 0; a.prev_hop = nullptr; a.n_windows = 0; a.win_frames = a.step_frames = 0;
     a.chunk_windows = 0; a.chunks_per_chan = 0;
+    // Small batches (fewer clips than half the resident warps) run frame-parallel: the stream instantiation with
+    // one-frame windows writes every frame's MFCC vector to a scratch ([clip][frame][40]), work items of k frames, and
+    // a second small kernel adds them up per clip in frame order -- the same per-frame arithmetic and the same order
+    // of the double sums as the per-clip loop, so the outputs are bit-identical; one clip takes 2 frames of latency
+    // instead of 16.
+    const long F = ((long)n_samples + SJ_HOP - 1) / SJ_HOP;
+    const long resident = sj_cepstrum_resident_warps(c->num_sms);
+    const bool frame_parallel = c->latency_mode && n_clips > 0 && F >= 2 && n_clips * 2 <= resident &&
+                                (size_t)n_clips * F * SJ_FEAT * sizeof(float) <= (64u << 20);
+    if (frame_parallel) {
+        const size_t need = (size_t)n_clips * F * SJ_FEAT * sizeof(float);
+        // one scratch per context: its users on different streams (the host pipeline's stages) are chained by an event
+        if (!c->frame_scratch_free) SJ_CUDA(c, cudaEventCreateWithFlags(&c->frame_scratch_free, cudaEventDisableTiming));
+        else SJ_CUDA(c, cudaStreamWaitEvent(stream, c->frame_scratch_free, 0));
+        if (need > c->frame_scratch_bytes) {
+            SJ_CUDA(c, cudaEventSynchronize(c->frame_scratch_free)); // unrecorded event: returns at once
+            cudaFree(c->d_frame_scratch);
+            c->d_frame_scratch = nullptr;
+            c->frame_scratch_bytes = 0;
+            SJ_CUDA(c, cudaMalloc(&c->d_frame_scratch, need));
+            c->frame_scratch_bytes = need;
+        }
+        SjCepstrumArgs f = a;
+        f.labels = nullptr; f.conf = nullptr; f.score = nullptr; f.peers = nullptr; f.do_svm = 0;
+        f.feats = c->d_frame_scratch;
+        f.chan_stride = n_samples; f.prev_hop = nullptr; f.n_windows = F; f.win_frames = f.step_frames = 1;
+        long k = (n_clips * F + resident - 1) / resident; // frames per work item: about one item per resident warp
+        if (k < 1) k = 1;
+        if (k > F) k = F;
+        f.chunk_windows = (int)k;
+        f.chunks_per_chan = (F + k - 1) / k;
+        if (timed) SJ_CUDA(c, cudaEventRecord(c->ev0, stream));
+        SJ_CUDA(c, sj_launch_cepstrum(f, c->h_tables, c->num_sms, stream));
+        SJ_CUDA(c, sj_launch_clip_stats(a, c->d_frame_scratch, (int)F, stream));
+        SJ_CUDA(c, cudaEventRecord(c->frame_scratch_free, stream));
+        if (timed) { SJ_CUDA(c, cudaEventRecord(c->ev1, stream)); c->have_timing = true; }
+        c->launches += 2;
+        return SJ_OK;
+    }
     if (timed) SJ_CUDA(c, cudaEventRecord(c->ev0, stream));
     SJ_CUDA(c, sj_launch_cepstrum(a, c->h_tables, c->num_sms, stream));
     if (timed) { SJ_CUDA(c, cudaEventRecord(c->ev1, stream)); c->have_timing = true; }
@@ -222,6 +266,8 @@ void scrubjay_destroy(scrubjay_ctx *c)
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
     cudaFree(c->d_peers);
+    cudaFree(c->d_frame_scratch);
+    if (c->frame_scratch_free) cudaEventDestroy(c->frame_scratch_free);
     for (void *t : c->d_donut_tables) cudaFree(t);
     cudaFree(c->d_donut_scratch);
     cudaFree(c->d_donut_clips); cudaFree(c->d_donut_labels); cudaFree(c->d_donut_detail);
@@ -532,6 +578,13 @@ static int stream_infer_any(scrubjay_ctx *c, const void *d_streams, long n_chann
     SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->have_timing = true;
     c->launches += 1;
+    return SJ_OK;
+}
+
+int scrubjay_set_latency_mode(scrubjay_ctx *c, int on)
+{
+    if (!c) return SJ_EINVAL;
+    c->latency_mode = on ? 1 : 0;
     return SJ_OK;
 }
 

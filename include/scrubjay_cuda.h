@@ -179,6 +179,12 @@ SJ_API int scrubjay_stream_infer_gather_dev(scrubjay_ctx *ctx, const float *d_st
 SJ_API int scrubjay_stream_infer_pcm16_gather_dev(scrubjay_ctx *ctx, const int16_t *d_streams, long n_channels,
                                            long n_samples, long chan_stride, const int16_t *d_prev_hop, int win_frames,
                                            int step_frames, float *d_conf, float *d_feats);
+/* Small batches (fewer clips than half the warps the GPU keeps resident, i.e. < 888 on a B200) run frame-parallel by
+ * default: the frames of a clip are spread over warps and SMs and a second small kernel forms the per-clip statistics in
+ * frame order, so a single clip costs about two frames of latency instead of ceil(n/1024) (the reference's use: one
+ * file / one second at a time, cepstrum/scrubjay_infer.c:156-177).  Outputs are bit-identical to the one-kernel
+ * path.  on = 0 forces the one-kernel path. */
+SJ_API int scrubjay_set_latency_mode(scrubjay_ctx *ctx, int on);
 /* windows per work item of the stream mode (0 = automatic); a tuning / test knob */
 SJ_API int scrubjay_set_stream_chunk(scrubjay_ctx *ctx, int windows_per_item);
 
