@@ -404,11 +404,30 @@ def run_ours(args, rank, local_rank, world):
                          "(exact no-FMA replay of the reference FFT), see DESIGN.md section 6")
         del det
 
+    # ---- BASELINE config 1 (single-clip inference): latency of one 1 s clip through the host-pointer call
+    single = None
+    if rank == 0:
+        one = torch.empty((1, N_SAMPLES), dtype=torch.float32, pin_memory=True)
+        one.copy_(clips[:1])
+        torch.cuda.synchronize()
+        ws, ks = [], []
+        for i in range(24):
+            t0 = time.perf_counter()
+            sj.infer_batch(one.data_ptr(), n_clips=1, n_samples=N_SAMPLES)
+            ws.append((time.perf_counter() - t0) * 1e6)
+        for i in range(8):
+            sj.infer_batch_dev(clips, 1, N_SAMPLES, labels, conf, score, None)
+            ks.append(sj.last_kernel_ms() * 1e3)
+        single = {"host_call_us": statistics.median(ws[4:]), "kernels_us": statistics.median(ks[2:]),
+                  "api": "scrubjay_infer_batch, 1 clip (H2D 64 KB + 2 kernels + D2H); frame-parallel small-batch path"}
+
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_clip()
         cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if (args.cpu_baseline and world == 1) else None  # N = 1 only
+        if cpu and single and cpu.get("one_thread_value"):
+            single["cpu_port_us"] = 1e6 / cpu["one_thread_value"]
         line = {
             "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -431,6 +450,7 @@ def run_ours(args, rank, local_rank, world):
                     "api": "scrubjay_infer_batch (host pointers, pinned)"},
             "pcm16": pcm,
             "donut": donut,
+            "single_clip": single,
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
