@@ -134,12 +134,12 @@ __device__ __forceinline__ void bfly(float2 &lo, float2 &hi, float u1, float u2)
 // stages 4-7 act on h inside a lane (lane = r).
 __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, int pos, int t, int tb,
                                                              const SjDonutTables<float> *tab, RowState<float> *st,
-                                                             float *scratch, int lane, int warp)
+                                                             float *scratch, int lane, int warp, int nact)
 {
     const int half = lane >> 4, h = lane & 15;
     float2 *xb = st->xbuf[warp][half];
     const float a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
-    for (int p = warp; p < 16; p += DnWarps<float>::value) {
+    for (int p = warp; p < nact; p += DnWarps<float>::value) { // pass p = the two rows (filters) of clip p
         const int r = 2 * p + half;
         const float *rowp = rows + r * kRow;
         const float mean = st->mean[r];
@@ -260,9 +260,14 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
     const int k2 = ((g & 1) << 1) | (g >> 1); // which quarter of the 128-point spectrum this lane ends up holding
     const T U = tab->U, a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
 
-    for (long base = long(blockIdx.x) * DN_CLIPS_PER_WARP; base < a.n_clips; base += long(gridDim.x) * DN_CLIPS_PER_WARP) {
+    // a CTA owns `cpc` clips at a time: 16 for large batches; small batches are spread over the resident CTAs (down to
+    // one clip per CTA), because a hop costs the same recurrence time however many lanes carry a clip, and the
+    // spectrogram passes of absent clips are skipped -- the latency of a small batch is that of one clip
+    const int cpc = a.clips_per_cta;
+    for (long base = long(blockIdx.x) * cpc; base < a.n_clips; base += long(gridDim.x) * cpc) {
+        const int nact = a.n_clips - base < cpc ? (int)(a.n_clips - base) : cpc; // clips of this group
         long clip = base + ci;
-        if (clip >= a.n_clips) clip = a.n_clips - 1; // idle lanes shadow the last clip; nothing is written for them
+        if (ci >= nact) clip = base + nact - 1; // idle lanes shadow the group's last clip; nothing is written for them
         // clip -> samples: contiguous clips, or second k of channel r of a stream array (sync/sync.cpp:190-203
         // classifies every full second of the microphone stream from zero state)
         const float *src = a.clips_per_row > 0
@@ -335,10 +340,10 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 
             // ---- phase 2 (all warps): spectrogram column t of all 32 rows, the row passes dealt round-robin
             if constexpr (sizeof(T) == 4) {
-                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane, warp);
+                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane, warp, nact);
             } else
             // double: 8 rows per pass, 4 lanes per row (no bit-exact FFT to follow: FFTW's order is unknown)
-            for (int bq = warp; bq < 4; bq += kDnWarps) {
+            for (int bq = warp; 4 * bq < nact; bq += kDnWarps) { // pass bq = the rows of clips 4 bq .. 4 bq + 3
                 const int r = 8 * bq + q;
                 const T *rowp = rows + r * kRow;
                 T2 v[32];
@@ -438,7 +443,7 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 
         // ---- epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
         const T fs = tab->fs;
-        if (warp == 0 && lane < DN_CLIPS_PER_WARP) {
+        if (warp == 0 && lane < nact) {
             const uint32_t *fl = st->flags[2 * lane];
             const T tol = tab->gap_tol, mind = tab->min_dur;
             int count = 0, size = 0;
@@ -472,8 +477,7 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
         // a_lo <= a < a_hi with per-clip thresholds found by a 32-way search over bit patterns that evaluates
         // the reference's own expression (double log10 included); the logarithm is then only taken for the
         // cells that pass, compacted through a small queue so that all 32 lanes work on passing cells.
-        for (int c2 = warp; c2 < DN_CLIPS_PER_WARP; c2 += kDnWarps) { // clips dealt round-robin to the warps
-            if (base + c2 >= a.n_clips) break;
+        for (int c2 = warp; c2 < nact; c2 += kDnWarps) { // clips dealt round-robin to the warps
             const int nm = st->n_mid[c2];
             int label = 0;
             T s_above = 0, s_mid = 0, s_below = 0;
@@ -617,10 +621,15 @@ size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
     return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
 }
 
-cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream_t stream)
+cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int grid, cudaStream_t stream)
 {
-    if (a.n_clips <= 0) return cudaSuccess;
-    long groups = (a.n_clips + DN_CLIPS_PER_WARP - 1) / DN_CLIPS_PER_WARP;
+    if (a_in.n_clips <= 0) return cudaSuccess;
+    SjDonutArgs a = a_in;
+    long cpc = (a.n_clips + grid - 1) / grid; // spread small batches over the resident CTAs
+    if (cpc > DN_CLIPS_PER_WARP) cpc = DN_CLIPS_PER_WARP;
+    if (cpc < 1) cpc = 1;
+    a.clips_per_cta = (int)cpc;
+    long groups = (a.n_clips + cpc - 1) / cpc;
     if (groups < grid) grid = (int)groups;
     const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
                          (a.clips_per_row <= 0 || a.row_stride % 4 == 0);

@@ -45,6 +45,7 @@ template <typename T> struct SjDonutTables {
 struct SjDonutArgs {
     const float *clips;   // [n_clips][n_samples] device
     long n_clips;
+    int clips_per_cta;    // set by sj_launch_donut: clips a CTA owns at a time (1 .. DN_CLIPS_PER_WARP)
     int n_samples;
     int tb;               // frames per clip = (n_samples - 256) / 224 + 1
     const void *tables;   // SjDonutTables<T> on the device

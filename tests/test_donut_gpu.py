@@ -191,3 +191,15 @@ def test_stream_decision_track_equals_clip_path():
     torch.cuda.synchronize()
     labels, _ = _gpu(sj, clips, dsp_b200.DONUT_SYNC_F32)
     assert np.array_equal(track2.cpu().numpy().reshape(-1), labels.astype(np.int8) + 1)
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_small_batch_grouping_equals_large_batch_grouping(variant):
+    """Small batches are spread over the CTAs (down to one clip per CTA, absent clips' passes skipped), large ones
+    use 16 clips per CTA: the same clips must give the same bits either way, for every group size in between."""
+    sj = _ctx()
+    big = _synth(sj, 4242, 14000)          # 16 clips per CTA
+    ref_l, ref_d = _gpu(sj, big, variant)
+    for n in (1, 2, 37, 700, 1500, 5000):  # 1, 1, 1, 1-2, 3, 8-ish clips per CTA
+        l, d = _gpu(sj, big[:n].contiguous(), variant)
+        assert np.array_equal(l, ref_l[:n]) and np.array_equal(d, ref_d[:n], equal_nan=True), "n = %d" % n
