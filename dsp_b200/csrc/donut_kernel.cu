@@ -134,12 +134,15 @@ __device__ __forceinline__ void bfly(float2 &lo, float2 &hi, float u1, float u2)
 // stages 4-7 act on h inside a lane (lane = r).
 __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, int pos, int t, int tb,
                                                              const SjDonutTables<float> *tab, RowState<float> *st,
-                                                             float *scratch, int lane, int warp, int nact)
+                                                             float *scratch, int lane, int warp, int nact, bool pipe)
 {
     const int half = lane >> 4, h = lane & 15;
     float2 *xb = st->xbuf[warp][half];
     const float a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
-    for (int p = warp; p < nact; p += DnWarps<float>::value) { // pass p = the two rows (filters) of clip p
+    // pipe (at most one pass per warp, none on warp 0): the CTA barrier that frees the rows for the next hop sits
+    // right after this warp has its frame in registers, so that warp 0 filters hop t+1 while the frame is transformed
+    bool freed = false;
+    for (int p = pipe ? warp - 1 : warp; p >= 0 && p < nact; p += pipe ? DnWarps<float>::value - 1 : DnWarps<float>::value) { // pass p = the two rows (filters) of clip p
         const int r = 2 * p + half;
         const float *rowp = rows + r * kRow;
         const float mean = st->mean[r];
@@ -152,6 +155,7 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
             const float x = rowp[(pos + n) & 255];
             v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
         }
+        if (pipe) { __syncthreads(); freed = true; }
         // stages 0 and 1 act on purely real data with the twiddles (1, 0) and (0, -1) (exact in the reference's
         // recurrence): products with 0 and 1 and sums with 0 are exact, so the ten operations of a butterfly
         // collapse to the two that change a value (the sign of a zero is the only thing lost; it squares away)
@@ -230,9 +234,10 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
             } else if ((ballot >> (16 * half)) & 0xFFFFu) st->flags[r][t >> 5] |= 1u << (t & 31);
         }
     }
+    if (pipe && !freed) __syncthreads(); // warp 0 and warps without a pass
 }
 
-template <typename T, bool ALIGNED>
+template <typename T, bool ALIGNED, bool PIPE>
 __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjDonutArgs a)
 {
     typedef typename V2<T>::type T2;
@@ -264,6 +269,9 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
     // one clip per CTA), because a hop costs the same recurrence time however many lanes carry a clip, and the
     // spectrogram passes of absent clips are skipped -- the latency of a small batch is that of one clip
     const int cpc = a.clips_per_cta;
+    // small groups (at most one spectrogram pass per warp with warp 0 left out): the recurrence of hop t+1 runs on
+    // warp 0 while the other warps transform frame t (see spectrogram_column_exact_f32)
+    constexpr bool pipe = PIPE; // chosen by sj_launch_donut: float cpc <= warps - 1, double cpc <= 4 (warps - 1)
     for (long base = long(blockIdx.x) * cpc; base < a.n_clips; base += long(gridDim.x) * cpc) {
         const int nact = a.n_clips - base < cpc ? (int)(a.n_clips - base) : cpc; // clips of this group
         long clip = base + ci;
@@ -340,10 +348,12 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 
             // ---- phase 2 (all warps): spectrogram column t of all 32 rows, the row passes dealt round-robin
             if constexpr (sizeof(T) == 4) {
-                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane, warp, nact);
+                spectrogram_column_exact_f32(rows, pos, t, tb, tab, st, scratch, lane, warp, nact, pipe);
             } else
             // double: 8 rows per pass, 4 lanes per row (no bit-exact FFT to follow: FFTW's order is unknown)
-            for (int bq = warp; 4 * bq < nact; bq += kDnWarps) { // pass bq = the rows of clips 4 bq .. 4 bq + 3
+            {
+            bool freed = false;
+            for (int bq = pipe ? warp - 1 : warp; bq >= 0 && 4 * bq < nact; bq += pipe ? kDnWarps - 1 : kDnWarps) { // pass bq = the rows of clips 4 bq .. 4 bq + 3
                 const int r = 8 * bq + q;
                 const T *rowp = rows + r * kRow;
                 T2 v[32];
@@ -355,6 +365,7 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     v[n].x = mul_rn(sub_rn(v[n].x, mean), wv.x);
                     v[n].y = mul_rn(sub_rn(v[n].y, mean), wv.y);
                 }
+                if (pipe) { __syncthreads(); freed = true; }
                 fft32(v); // over n: Y_g[k1] in v[SJ_BREV32(k1)]
 #pragma unroll
                 for (int k1 = 1; k1 < 32; ++k1) {
@@ -438,8 +449,11 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     } else if ((ballot >> (4 * q)) & 0xFu) st->flags[r][t >> 5] |= 1u << (t & 31);
                 }
             }
-            __syncthreads(); // the rows are overwritten by the next hop; cells and row state become visible to all warps
+            if (pipe && !freed) __syncthreads(); // warp 0 and warps without a pass
+            }
+            if (!pipe) __syncthreads(); // the rows are overwritten by the next hop; cells and row state become visible to all warps
         }
+        if (pipe) __syncthreads(); // the last frame's cells and row state
 
         // ---- epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
         const T fs = tab->fs;
@@ -597,21 +611,21 @@ template <typename T> size_t smem_total()
 
 cudaError_t sj_donut_setup()
 {
-    cudaError_t e;
-    e = cudaFuncSetAttribute(donut_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<float>());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(donut_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<float>());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(donut_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<double>());
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(donut_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<double>());
+    cudaError_t e = cudaSuccess;
+#define SJ_DN_ATTR(T, AL, PI)                                                                                          \
+    if (e == cudaSuccess)                                                                                              \
+    e = cudaFuncSetAttribute(donut_kernel<T, AL, PI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total<T>())
+    SJ_DN_ATTR(float, true, false); SJ_DN_ATTR(float, false, false); SJ_DN_ATTR(float, true, true); SJ_DN_ATTR(float, false, true);
+    SJ_DN_ATTR(double, true, false); SJ_DN_ATTR(double, false, false); SJ_DN_ATTR(double, true, true); SJ_DN_ATTR(double, false, true);
+#undef SJ_DN_ATTR
+    return e;
 }
 
 int sj_donut_grid(int num_sms, bool f64)
 {
     int per_sm = 0;
-    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true>, DnWarps<double>::value * 32, smem_total<double>());
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true>, DnWarps<float>::value * 32, smem_total<float>());
+    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true, false>, DnWarps<double>::value * 32, smem_total<double>());
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true, false>, DnWarps<float>::value * 32, smem_total<float>());
     if (per_sm < 1) per_sm = 1;
     return num_sms * per_sm;
 }
@@ -633,12 +647,15 @@ cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int grid, cudaStr
     if (groups < grid) grid = (int)groups;
     const bool aligned = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
                          (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
+    const bool pipe = f64 ? cpc <= 4 * (DnWarps<double>::value - 1) : cpc <= DnWarps<float>::value - 1;
+#define SJ_DN_LAUNCH(T, AL, PI) donut_kernel<T, AL, PI><<<grid, DnWarps<T>::value * 32, smem_total<T>(), stream>>>(a)
     if (f64) {
-        if (aligned) donut_kernel<double, true><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);
-        else donut_kernel<double, false><<<grid, DnWarps<double>::value * 32, smem_total<double>(), stream>>>(a);
+        if (aligned) { if (pipe) SJ_DN_LAUNCH(double, true, true); else SJ_DN_LAUNCH(double, true, false); }
+        else { if (pipe) SJ_DN_LAUNCH(double, false, true); else SJ_DN_LAUNCH(double, false, false); }
     } else {
-        if (aligned) donut_kernel<float, true><<<grid, DnWarps<float>::value * 32, smem_total<float>(), stream>>>(a);
-        else donut_kernel<float, false><<<grid, DnWarps<float>::value * 32, smem_total<float>(), stream>>>(a);
+        if (aligned) { if (pipe) SJ_DN_LAUNCH(float, true, true); else SJ_DN_LAUNCH(float, true, false); }
+        else { if (pipe) SJ_DN_LAUNCH(float, false, true); else SJ_DN_LAUNCH(float, false, false); }
     }
+#undef SJ_DN_LAUNCH
     return cudaGetLastError();
 }
