@@ -100,6 +100,27 @@ __device__ __forceinline__ void iir8(const T (&x)[8], T (&w)[8], const T (&a)[9]
     }
 }
 
+// float: for even j the products a[j] w and b[j] w of the same delayed value come from ONE packed multiply
+// (mul.rn.f32x2 rounds each half like the scalar instruction; the sums stay scalar and ordered, see bfly) -- four
+// issue slots fewer per sample on a warp whose only other limit is the dependent chain
+__device__ __forceinline__ void iir8(const float (&x)[8], float (&w)[8], const float (&a)[9], const float (&b)[9], float (&y)[8])
+{
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        float2 pe[4];
+#pragma unroll
+        for (int j = 2; j < 9; j += 2) pe[j / 2 - 1] = pk_mul(pk_bc(w[(s - j + 8) & 7]), make_float2(a[j], b[j]));
+        float w0 = x[s];
+#pragma unroll
+        for (int j = 1; j < 9; ++j) w0 = sub_rn(w0, (j & 1) ? mul_rn(a[j], w[(s - j + 8) & 7]) : pe[j / 2 - 1].x);
+        float yy = mul_rn(b[0], w0);
+#pragma unroll
+        for (int j = 2; j < 9; j += 2) yy = add_rn(yy, pe[j / 2 - 1].y); // b[odd] == 0
+        w[s] = w0;
+        y[s] = yy;
+    }
+}
+
 template <typename T> struct RowState {
     T min_in[32], max_in[32];   // min / max of a = re^2 + im^2 over the cells with Sxx > 0: inner bins 1..127 (doubled)
     T min_ed[32], max_ed[32];   // ... and the edge bins 0 and 128
@@ -326,7 +347,7 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 #pragma unroll
                         for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
                     }
-                    iir8<T>(x, w, ca, cb, y);
+                    iir8(x, w, ca, cb, y); // float: the packed overload
                     // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
                     const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
 #pragma unroll
