@@ -374,7 +374,10 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
             // double: 8 rows per pass, 4 lanes per row (no bit-exact FFT to follow: FFTW's order is unknown)
             {
             bool freed = false;
-            for (int bq = pipe ? warp - 1 : warp; bq >= 0 && 4 * bq < nact; bq += pipe ? kDnWarps - 1 : kDnWarps) { // pass bq = the rows of clips 4 bq .. 4 bq + 3
+            // pass bq = the rows of clips 4 bq .. 4 bq + 3: four passes at most and four warps, so a warp has one pass or none
+            static_assert(sizeof(T) == 4 || kDnWarps * 4 >= DN_CLIPS_PER_WARP, "one pass per warp");
+            // (large groups run all four passes: the test on the group size would cost this 255-register kernel a spill)
+            if (const int bq = pipe ? warp - 1 : warp; !pipe || (bq >= 0 && 4 * bq < nact)) {
                 const int r = 8 * bq + q;
                 const T *rowp = rows + r * kRow;
                 T2 v[32];
