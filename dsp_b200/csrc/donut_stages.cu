@@ -64,6 +64,28 @@ __device__ __forceinline__ void iir_block8(const T (&x)[8], T (&r)[8], const T (
     }
 }
 
+// float: a[j] w and b[j] w of the same delayed value from ONE packed multiply (mul.rn.f32x2 rounds each half like the
+// scalar instruction; the ordered subtractions / sums stay scalar, so nothing is contracted and the results keep the
+// reference's bits) -- 9 instead of 17 multiply issue slots per sample
+__device__ __forceinline__ void iir_block8(const float (&x)[8], float (&r)[8], const float (&a)[9], const float (&b)[9],
+                                           float (&y)[8])
+{
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        float2 p[8];
+#pragma unroll
+        for (int j = 1; j < 9; ++j) p[j - 1] = pk_mul(pk_bc(r[(s - j + 8) & 7]), make_float2(a[j], b[j]));
+        float w0 = x[s];
+#pragma unroll
+        for (int j = 1; j < 9; ++j) w0 = sub_rn(w0, p[j - 1].x);
+        float yy = mul_rn(b[0], w0);
+#pragma unroll
+        for (int j = 1; j < 9; ++j) yy = add_rn(yy, p[j - 1].y);
+        r[s] = w0;
+        y[s] = yy;
+    }
+}
+
 // eight consecutive elements of one row: 16-byte accesses when the row is 16-byte aligned (each lane walks its own row,
 // so a warp-level access touches 32 different lines either way -- wide accesses cut the number of such instructions)
 template <typename E> __device__ __forceinline__ void load8(const E *p, E (&d)[8], bool vec)
@@ -126,7 +148,7 @@ __device__ __forceinline__ void iir_run(const IN *__restrict__ in, T *__restrict
 #pragma unroll
             for (int k = 0; k < 8; ++k) x[k] = (T)ring[j][k];
             if (blk + j + kPre < nblk) load8<IN>(in + 8 * (blk + j + kPre), ring[j], vec_in);
-            iir_block8<T>(x, r, a, b, y);
+            iir_block8(x, r, a, b, y);
             if (WRITE) store8<T>(out + 8 * (blk + j), y, vec_out);
         }
     }
@@ -135,7 +157,7 @@ __device__ __forceinline__ void iir_run(const IN *__restrict__ in, T *__restrict
         T x[8], y[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) x[k] = (T)__ldg(in + i + k);
-        iir_block8<T>(x, r, a, b, y);
+        iir_block8(x, r, a, b, y);
         if (WRITE) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) out[i + k] = y[k];
