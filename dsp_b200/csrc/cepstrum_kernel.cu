@@ -34,8 +34,14 @@
 
 namespace {
 
+#ifndef SJ_WIDE_TRANSPOSE
+#define SJ_WIDE_TRANSPOSE 1
+#endif
 constexpr int kTStride = 36;                 // row stride of the transpose plane: 144 B => conflict-free 128-bit row reads
 constexpr int kTFloats = 32 * kTStride;      // 1152 floats: transpose plane, then |X| bins 0..1024
+// plane size per warp: the interleaved transpose needs 32 x 68 = 2176 floats INCLUDING the slot of the previous hop:
+// 1024 + 1152 with float hops; int16 hops are 512 floats, so their plane grows to 1664
+__host__ __device__ constexpr int t_floats(bool pcm16) { return (SJ_WIDE_TRANSPOSE && pcm16) ? 2176 - SJ_HOP / 2 : kTFloats; }
 constexpr int kLogFloats = 96;               // folded log-energies of two frames (2 x 40, +pad)
 
 // mel partial sums: generic layout 32*maxseg, fast layout 32*SJ_MEL_FAST_SLOTS, + the zero slot
@@ -46,7 +52,7 @@ __host__ __device__ constexpr int p_floats(int maxseg)
 // per-warp shared memory in floats: the 2-slot hop ring (int16 hops need half a slot), the transpose plane, logs, partials
 __host__ __device__ constexpr int warp_floats(int maxseg, bool pcm16)
 {
-    return (pcm16 ? SJ_HOP : 2 * SJ_HOP) + kTFloats + kLogFloats + p_floats(maxseg);
+    return (pcm16 ? SJ_HOP : 2 * SJ_HOP) + t_floats(pcm16) + kLogFloats + p_floats(maxseg);
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -246,8 +252,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     constexpr int kRingFloats = STREAM ? SJ_STREAM_MAX_WIN * SJ_NCOEF : 0;
     float *wbase = reinterpret_cast<float *>(smem_raw + off) + size_t(warp) * (warp_floats(maxseg, PCM16) + kRingFloats);
     constexpr int kSlot = PCM16 ? SJ_HOP / 2 : SJ_HOP; // floats per ring slot
-    float *tb = wbase + 2 * kSlot;    // transpose plane, later |X|
-    float *lg = tb + kTFloats;        // log energies / standardised features
+    // [slot 0 | plane | slot 1], so that the plane and whichever slot holds the PREVIOUS hop are contiguous and together
+    // hold the 32 x 68 floats of the interleaved transpose (see below)
+    constexpr bool kWide = SJ_WIDE_TRANSPOSE;
+    constexpr int kPlane = t_floats(PCM16);
+    float *tb = kWide ? wbase + kSlot : wbase + 2 * kSlot; // transpose plane, later |X|
+    float *lg = wbase + 2 * kSlot + kPlane;                 // log energies / standardised features
+    auto slot_ptr = [&](int slot) -> float * { return kWide ? (slot ? wbase + kSlot + kPlane : wbase) : wbase + slot * kSlot; };
     float *P = lg + kLogFloats;       // mel partial sums
     float *mring = P + p_floats(maxseg); // STREAM: the last win_frames MFCC vectors, [frame % W][coef]
 
@@ -318,7 +329,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     auto fetch = [&](const Seg &g, int h, int slot) {
         const unsigned char *src = h < 0 ? g.prev : g.base + (long)h * SJ_HOP * ES;
         const int cnt = (h == F - 1) ? last_valid : SJ_HOP;
-        float *dst = wbase + slot * kSlot;
+        float *dst = slot_ptr(slot);
         if (TMA) {
             if (lane == 0) {
                 fence_proxy_async();
@@ -348,7 +359,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
         for (int hr = 0; hr < nh; ++hr, ++q) {
             const int slot = q & 1, ha = sg.hop0 + hr;
             if (TMA) mbar_wait(&bars[slot], (q >> 1) & 1);
-            float *curf = wbase + slot * kSlot;
+            float *curf = slot_ptr(slot);
             if (ha == F - 1 && last_valid < SJ_HOP) { // zero-padded last read (aubio_source_do)
                 if (PCM16)
                     for (int i = last_valid + lane; i < SJ_HOP; i += 32) reinterpret_cast<int16_t *>(curf)[i] = 0;
@@ -361,7 +372,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 continue;
             }
             // sample pair (2m, 2m+1), m = 32*m1 + lane, of the current / previous hop as floats
-            const float *prvf = wbase + (slot ^ 1) * kSlot;
+            const float *prvf = slot_ptr(slot ^ 1);
             auto pair_at = [&](const float *hop, int m1) -> float2 {
                 if (PCM16) {
                     // int16 -> float without the conversion pipe (I2F.S16 runs at a quarter of the FMA rate): the
@@ -398,13 +409,38 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             __syncwarp();
             // prefetch the next hop (of this item, else the first hop of the warp's next item) into the slot that
             // just became free
-            if (hr + 1 < nh) fetch(sg, ha + 1, slot ^ 1);
-            else if (item + stride < n_items) {
-                nxt = seg_of(item + stride);
-                fetch(nxt, nxt.hop0, slot ^ 1);
-            }
+            auto prefetch_next = [&]() {
+                if (hr + 1 < nh) fetch(sg, ha + 1, slot ^ 1);
+                else if (item + stride < n_items) {
+                    nxt = seg_of(item + stride);
+                    fetch(nxt, nxt.hop0, slot ^ 1);
+                }
+            };
+            if (!kWide) prefetch_next();
             // ---- 1024-point complex FFT, 32 x 32 split
             sj_fft32(v); // over m1: Y[k1] in v[SJ_BREV32(k1)]
+            if (kWide) {
+                // transpose (lane = m2, reg = k1) -> (lane = k1, reg = m2) with (re, im) interleaved: 32 64-bit stores
+                // (256 contiguous bytes each) and 16 conflict-free 128-bit row loads (row stride 68 floats = 17 x 16 B)
+                // that deliver the register pairs of the packed arithmetic as they are -- the same 128 wavefronts as two
+                // float planes but half the store instructions and one round trip instead of two.  The 32 x 68 floats
+                // span the plane and the slot of the previous hop, which is dead by now; the next hop is requested
+                // into that slot afterwards.
+                float *pl = (slot ^ 1) ? tb : wbase;
+                float2 *pl2 = reinterpret_cast<float2 *>(pl);
+#pragma unroll
+                for (int k1 = 0; k1 < 32; ++k1) pl2[k1 * 34 + lane] = v[SJ_BREV32(k1)];
+                __syncwarp();
+                const float4 *row = reinterpret_cast<const float4 *>(pl + lane * 68);
+#pragma unroll
+                for (int g = 0; g < 16; ++g) {
+                    const float4 q4 = row[g];
+                    v[2 * g] = make_float2(q4.x, q4.y);
+                    v[2 * g + 1] = make_float2(q4.z, q4.w);
+                }
+                __syncwarp();
+                prefetch_next();
+            } else
             // transpose (lane = m2, reg = k1) -> (lane = k1, reg = m2), one float plane at a time
             {
                 const float4 *row = reinterpret_cast<const float4 *>(tb + lane * kTStride);
