@@ -87,3 +87,20 @@ def test_slaney_bank_shape(oracle):
     nz = np.nonzero(fb.sum(0))[0]
     assert nz[0] == 18 and nz[-1] == 877
     assert (fb > 0).sum(0).max() == 2
+
+
+def test_slaney_bank_against_an_independent_implementation(oracle):
+    """Second opinion on the restated aubio filterbank (the reference's own library is absent): torchaudio's
+    Slaney-scale, Slaney-normalised bank -- a different code lineage (librosa / Auditory Toolbox) -- between the same edge
+    frequencies.  aubio keeps the toolbox's constants (13 linear filters from 133.33 Hz, then a ratio of 1.0711703, which
+    puts the knee at 999.8 Hz), librosa's scale has its knee at exactly 1000 Hz, so centres differ by up to ~0.2 Hz and
+    weights by a few 1e-5; what must agree exactly is the structure: which bins each filter touches."""
+    ta = pytest.importorskip("torchaudio")
+    fb = oracle.fbank()
+    lo = 133.3333
+    top = (lo + 12 * 66.66666666) * 1.0711703 ** 29  # upper edge of filter 39
+    ref = ta.functional.melscale_fbanks(n_freqs=1025, f_min=lo, f_max=float(top), n_mels=40, sample_rate=16000,
+                                        norm="slaney", mel_scale="slaney").numpy().T
+    assert np.array_equal(ref > 0, fb > 0)
+    assert np.abs(ref - fb).max() < 0.005 * fb.max()
+    assert abs(ref.sum() - fb.sum()) < 1e-4 * fb.sum()
