@@ -576,13 +576,17 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     double acc = 0.0;
                     const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
                     int nq = 0; // queued cells (warp-uniform)
+                    // cell c = c0 + lane sits at (frame j, bin i) = (c / nf, c % nf): one division per box, then the pair
+                    // advances by 32 cells per round
+                    const int q32 = 32 / nf, r32 = 32 - q32 * nf;
+                    int cj = lane / nf, ci = lane - cj * nf;
                     for (int c0 = 0; c0 < ncell; c0 += 32) {
                         const int c = c0 + lane;
                         T av = 0;
-                        if (c < ncell) {
-                            const int j = c / nf, i = c - j * nf;
-                            av = scr[(t0 + j) * DN_BINS + f0 + i];
-                        }
+                        if (c < ncell) av = scr[(t0 + cj) * DN_BINS + f0 + ci];
+                        ci += r32;
+                        cj += q32;
+                        if (ci >= nf) { ci -= nf; ++cj; }
                         const bool pass = c < ncell && av >= a_lo && av < a_hi;
                         const unsigned bal = __ballot_sync(kFull, pass);
                         if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
