@@ -580,13 +580,15 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     // advances by 32 cells per round
                     const int q32 = 32 / nf, r32 = 32 - q32 * nf;
                     int cj = lane / nf, ci = lane - cj * nf;
+                    // the cell of the next round is requested before this round's is tested (the scratch sits in L2)
+                    T av_next = lane < ncell ? scr[(t0 + cj) * DN_BINS + f0 + ci] : (T)0;
                     for (int c0 = 0; c0 < ncell; c0 += 32) {
                         const int c = c0 + lane;
-                        T av = 0;
-                        if (c < ncell) av = scr[(t0 + cj) * DN_BINS + f0 + ci];
+                        const T av = av_next;
                         ci += r32;
                         cj += q32;
                         if (ci >= nf) { ci -= nf; ++cj; }
+                        av_next = c + 32 < ncell ? scr[(t0 + cj) * DN_BINS + f0 + ci] : (T)0;
                         const bool pass = c < ncell && av >= a_lo && av < a_hi;
                         const unsigned bal = __ballot_sync(kFull, pass);
                         if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
