@@ -222,24 +222,36 @@ __device__ __forceinline__ void spectrogram_column_exact_f32(const float *rows, 
         const bool is_band = r & 1;
         float *cell = scratch + (size_t(r >> 1) * tb + t) * DN_BINS;
         float lmin = INFINITY, lmax = 0.f, emin = INFINITY, emax = 0.f;
-        bool any = false;
+        float imax = 0.f, xmax = 0.f; // flag rows: largest a over the inner / the edge cells (any(a >= thr) = max(a) >= thr)
         // a = re^2 + im^2 with the reference's operations; "/ U", "* 2" (classifier.cpp:349-364) are applied
-        // later, only where a value is needed; the tests on Sxx use exact thresholds on a
+        // later, only where a value is needed; the tests on Sxx use exact thresholds on a.
+        // The two half-warps of a pass hold a flag row and a band row: both kinds of bookkeeping are done by every lane
+        // (selects, no branches -- a branch on the row kind diverges in every one of the nine rounds) and each row
+        // keeps what it needs.
 #pragma unroll
         for (int hh = 0; hh < 9; ++hh) {
             const int k = 16 * hh + h;
             if (hh < 8 || h == 0) {
                 const float av = add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y));
-                const bool edge = (hh == 0 || hh == 8) && h == 0;
-                if (is_band) {
-                    cell[k] = av;
-                    if (av >= a_pos) {
-                        if (edge) { emin = fminf(emin, av); emax = fmaxf(emax, av); }
-                        else { lmin = fminf(lmin, av); lmax = fmaxf(lmax, av); }
-                    }
-                } else any = any || (av >= (edge ? a_thr_e : a_thr_i));
+                if (is_band) cell[k] = av;
+                const bool pos = av >= a_pos;
+                const float vmin = pos ? av : INFINITY, vmax = pos ? av : 0.f;
+                if (hh == 0 || hh == 8) { // bins 0 and 128 (lane h == 0) are the edge cells
+                    const bool edge = h == 0;
+                    emin = fminf(emin, edge ? vmin : INFINITY);
+                    emax = fmaxf(emax, edge ? vmax : 0.f);
+                    xmax = fmaxf(xmax, edge ? av : 0.f);
+                    lmin = fminf(lmin, edge ? INFINITY : vmin);
+                    lmax = fmaxf(lmax, edge ? 0.f : vmax);
+                    imax = fmaxf(imax, edge ? 0.f : av);
+                } else {
+                    lmin = fminf(lmin, vmin);
+                    lmax = fmaxf(lmax, vmax);
+                    imax = fmaxf(imax, av);
+                }
             }
         }
+        const bool any = !is_band && (imax >= a_thr_i || xmax >= a_thr_e);
 #pragma unroll
         for (int o = 1; o < 16; o <<= 1) {
             lmin = fminf(lmin, __shfl_xor_sync(kFull, lmin, o));
