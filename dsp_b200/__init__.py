@@ -52,6 +52,9 @@ def load_library():
     L = ctypes.CDLL(LIB_PATH)
     vp, c_long, c_int, c_uint = ctypes.c_void_p, ctypes.c_long, ctypes.c_int, ctypes.c_uint
     L.scrubjay_create.argtypes = [ctypes.POINTER(vp), c_int, vp, ctypes.c_size_t, c_uint]
+    L.scrubjay_create_ex.argtypes = [ctypes.POINTER(vp), c_int, vp, ctypes.c_size_t, c_uint, vp]
+    L.scrubjay_cepstrum_params_default.argtypes = [vp]
+    L.scrubjay_cepstrum_params_default.restype = None
     L.scrubjay_destroy.argtypes = [vp]
     L.scrubjay_destroy.restype = None
     L.scrubjay_last_error.argtypes = [vp]
@@ -93,6 +96,7 @@ def load_library():
     L.scrubjay_predict.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_float)]
     L.scrubjay_infer_batch.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_synth_clips_dev.argtypes = [vp, vp, c_long, c_long, c_int, c_uint]
+    L.scrubjay_synth_clips_ex_dev.argtypes = [vp, vp, c_long, c_long, c_int, c_uint, c_int]
     L.scrubjay_donut_classify_batch_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.scrubjay_donut_classify_batch.argtypes = [vp, vp, c_long, c_int, c_int, vp, vp]
     L.classify.argtypes = [vp, c_int]
@@ -119,6 +123,7 @@ def load_library():
     L.find_midpoints.restype = ctypes.POINTER(ctypes.c_float)
     L.sum_intense.argtypes = [ctypes.c_float, ctypes.c_float, ctypes.c_float, vp, c_int, vp, c_int, vp, ctypes.c_float]
     L.sum_intense.restype = ctypes.c_float
+    L.scrubjay_debug_inject_failure.argtypes = [vp, c_long]
     L.scrubjay_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
     L.scrubjay_host_free.argtypes = [vp]
     L.scrubjay_host_free.restype = None
@@ -139,10 +144,33 @@ def _ptr(x):
     raise TypeError("cannot take the address of %r" % type(x))
 
 
+WINDOW_HANN_PERIODIC, WINDOW_HANN_SYMMETRIC = 0, 1
+SPECTRUM_MAGNITUDE, SPECTRUM_POWER = 0, 1
+DCT_ORTHO, DCT_UNNORMALISED = 0, 1
+LABEL_PREDICT, LABEL_VOTE, LABEL_PROB_ARGMAX = 0, 1, 2
+
+
+class CepstrumParams(ctypes.Structure):
+    """scrubjay_cepstrum_params (include/scrubjay_cuda.h): the switchable aubio-isms / ORT-isms of the cepstrum path.
+    CepstrumParams() holds the defaults (the restated aubio 0.4.x / onnxruntime behaviour); keyword arguments override."""
+    _fields_ = [("window", ctypes.c_int32), ("spectrum", ctypes.c_int32), ("log_floor", ctypes.c_float),
+                ("dct_norm", ctypes.c_int32), ("half_swap", ctypes.c_int32), ("label_rule", ctypes.c_int32),
+                ("reserved", ctypes.c_int32 * 2)]
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.window, self.spectrum, self.log_floor = WINDOW_HANN_PERIODIC, SPECTRUM_MAGNITUDE, 2e-42
+        self.dct_norm, self.half_swap, self.label_rule = DCT_ORTHO, 1, LABEL_PREDICT
+        for k, v in kw.items():
+            if k not in dict(self._fields_):
+                raise TypeError("unknown cepstrum parameter %r" % k)
+            setattr(self, k, v)
+
+
 class ScrubJay:
     """One context per GPU (scrubjay_create / scrubjay_destroy)."""
 
-    def __init__(self, device=0, samplerate=16000, model_blob=None):
+    def __init__(self, device=0, samplerate=16000, model_blob=None, params=None):
         self._L = load_library()
         self._h = ctypes.c_void_p()
         if model_blob is None:
@@ -150,7 +178,8 @@ class ScrubJay:
         else:
             blob = bytes(model_blob)
             n = len(blob)
-        rc = self._L.scrubjay_create(ctypes.byref(self._h), device, blob, n, samplerate)
+        rc = self._L.scrubjay_create_ex(ctypes.byref(self._h), device, blob, n, samplerate,
+                                        ctypes.addressof(params) if params is not None else None)
         if rc != 0:
             msg = self._L.scrubjay_last_error(None).decode()
             self._h = ctypes.c_void_p()
@@ -263,6 +292,10 @@ class ScrubJay:
         self._check(fn(self._h, _ptr(streams), n_channels, n_samples, chan_stride, _ptr(prev_hop), win_frames,
                        step_frames, _ptr(conf), _ptr(feats)))
 
+    def debug_inject_failure(self, chunk):
+        """test hook: the next host-pointer batch call fails before enqueueing chunk number `chunk`"""
+        self._check(self._L.scrubjay_debug_inject_failure(self._h, chunk))
+
     def set_latency_mode(self, on):
         """frame-parallel path for small batches (default on); False forces the one-kernel path"""
         self._check(self._L.scrubjay_set_latency_mode(self._h, 1 if on else 0))
@@ -270,8 +303,9 @@ class ScrubJay:
     def set_stream_chunk(self, windows_per_item):
         self._check(self._L.scrubjay_set_stream_chunk(self._h, windows_per_item))
 
-    def synth_clips_dev(self, d_out, first_clip, n_clips, n_samples, seed=0x5C2B):
-        self._check(self._L.scrubjay_synth_clips_dev(self._h, _ptr(d_out), first_clip, n_clips, n_samples, seed))
+    def synth_clips_dev(self, d_out, first_clip, n_clips, n_samples, seed=0x5C2B, flavour=0):
+        """flavour: SYNTH_MIXED (noise + chirps) or SYNTH_CALLS ("donut"-shaped calls: both donut verdicts occur)"""
+        self._check(self._L.scrubjay_synth_clips_ex_dev(self._h, _ptr(d_out), first_clip, n_clips, n_samples, seed, flavour))
 
     def donut_classify_batch_dev(self, d_clips, n_clips, n_samples, variant, d_labels, d_detail=None):
         self._check(self._L.scrubjay_donut_classify_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, variant,
@@ -422,6 +456,7 @@ class ScrubJay:
 
 
 MIX_FIRST, MIX_MEAN = 0, 1
+SYNTH_MIXED, SYNTH_CALLS = 0, 1
 
 
 class WavInfo(ctypes.Structure):

@@ -91,9 +91,9 @@ __device__ __forceinline__ void fence_proxy_async()
 }
 // log10(max(x, 2e-42)) (aubio fvec_log10 / SAFE_LOG10) on one MUFU.LG2: values below 1e-30 (the floor
 // itself is subnormal) are scaled by 2^64 first.  Absolute error <= 2 ulp of log2(x) * 0.30103.
-__device__ __forceinline__ float floor_log10(float x)
+__device__ __forceinline__ float floor_log10(float x, float floor_v = 2.e-42f)
 {
-    x = fmaxf(x, 2.e-42f);
+    x = fmaxf(x, floor_v);
     const bool tiny = x < 1e-30f;
     const float y = tiny ? x * 18446744073709551616.f : x;
     float l;
@@ -186,9 +186,12 @@ __device__ __forceinline__ SvmOut svm_eval(const SjTables *T, const float *z, in
     const float s = part + T->rho; // onnxruntime score: positive => class 0
     SvmOut r;
     r.score = -s;                  // sklearn decision_function
-    r.label = r.score > 0.f ? 1 : 0; // rule of cepstrum/run.py:46 (model.predict)
     double p[2];
     platt_pair((double)s, (double)T->prob_a, (double)T->prob_b, p);
+    // label rule at the onnxruntime boundary (scrubjay_cepstrum_params.label_rule); default = the rule
+    // of cepstrum/run.py:46 (model.predict): decision_function > 0
+    const int rule = T->label_rule;
+    r.label = rule == SJ_LABEL_VOTE ? (s <= 0.f ? 1 : 0) : rule == SJ_LABEL_PROB_ARGMAX ? (p[1] > p[0] ? 1 : 0) : (r.score > 0.f ? 1 : 0);
     r.conf = (float)p[r.label];
     return r;
 }
@@ -298,6 +301,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
     const float4 *X4 = reinterpret_cast<const float4 *>(tb + T->mel_lo + lane * mel_ch);
     const int partner = (32 - lane) & 31;
     constexpr int PSKIP = FAST ? 4 : 0;
+    // generic instantiation only: the switches of scrubjay_cepstrum_params (warp-uniform)
+    const bool win_tab = !FAST && (T->gen_flags & SJ_GEN_WINDOW_TABLE), pw = !FAST && (T->gen_flags & SJ_GEN_POWER);
+    const float log_floor = FAST ? 2.e-42f : T->log_floor;
+    const float2 *wtab = reinterpret_cast<const float2 *>(a.tables->window) + lane; // pair (2m, 2m+1), m = 32 m1 + lane
     uint32_t cmb[5]; // fast layout: this lane's combine entries live in registers
 #pragma unroll
     for (int e = 0; e < 5; ++e) cmb[e] = T->comb2[e][lane];
@@ -389,7 +396,14 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             // The window is rebuilt from the angle sum 2 pi (64 m1 + 2 lane + d)/2048: 0.5 cos/sin of the m1 part
             // are immediates, cos/sin of the lane part sit in four registers -- two FMAs per pair of samples
             // instead of a table read (shared-memory bandwidth binds this kernel, not issue).
-            if (hr == 0) { // no previous hop: aubio_pvoc starts from zeros
+            if (win_tab) { // any window, from the table: lower half on the previous hop, upper half on the current one
+#pragma unroll
+                for (int m1 = 0; m1 < 16; ++m1) {
+                    const float2 c = pair_at(curf, m1), s = hr == 0 ? make_float2(0.f, 0.f) : pair_at(prvf, m1);
+                    v[m1] = pk_mul(s, __ldg(wtab + 32 * m1));
+                    v[m1 + 16] = pk_mul(c, __ldg(wtab + 512 + 32 * m1));
+                }
+            } else if (hr == 0) { // no previous hop: aubio_pvoc starts from zeros
 #pragma unroll
                 for (int m1 = 0; m1 < 16; ++m1) {
                     const float2 c = pair_at(curf, m1);
@@ -483,8 +497,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                     const float2 X = pk_fma(pk_bc(t.x), make_float2(1.f, -1.f), pk_bc(e.x));
                     const float2 Y = pk_fma(pk_bc(t.y), make_float2(1.f, -1.f), pk_bc(e.y));
                     const float2 m = pk_fma(Y, Y, pk_mul(X, X));
-                    tb[lane + 32 * j] = fast_sqrt(m.x);
-                    tb[1024 - lane - 32 * j] = fast_sqrt(m.y);
+                    tb[lane + 32 * j] = pw ? m.x : fast_sqrt(m.x); // (2|X|)^2 for the power filterbank
+                    tb[1024 - lane - 32 * j] = pw ? m.y : fast_sqrt(m.y);
                 } else { // the mirrors of the first rows lie above the filterbank
                     const float2 xa = pk_add(e, t);
                     tb[lane + 32 * j] = fast_sqrt(fmaf(xa.x, xa.x, xa.y * xa.y));
@@ -492,7 +506,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             }
             if (lane == 0) {
                 const float2 c = v[SJ_BREV32(16)];
-                tb[512] = 2.f * fast_sqrt(fmaf(c.x, c.x, c.y * c.y));
+                const float m = fmaf(c.x, c.x, c.y * c.y);
+                tb[512] = pw ? 4.f * m : 2.f * fast_sqrt(m);
             }
             __syncwarp();
 
@@ -560,8 +575,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                     }
                 }
                 // aubio fvec_log10: log10(max(x, 2e-42)); lane m holds band m, lanes 0..7 also band m+32
-                e0 = floor_log10(e0);
-                e1 = floor_log10(e1);
+                e0 = floor_log10(e0, log_floor);
+                e1 = floor_log10(e1, log_floor);
                 // DCT-II symmetry D[c][39-m] = (-1)^c D[c][m]: fold the 40 log energies into 20 sums
                 // (even c) and 20 differences (odd c)
                 const float far0 = __shfl_sync(kFull, e0, (39 - lane) & 31); // band 39-m for m = 8..19
@@ -728,7 +743,8 @@ cudaError_t launch_any(const SjCepstrumArgs &a, const SjTables *h, int num_sms, 
     if (STREAM) tma = tma && (a.chan_stride % per16 == 0) && ((reinterpret_cast<uintptr_t>(a.prev_hop) & 15) == 0);
     // the fast instantiation hard-codes the 16 kHz layout: 28-bin chunks, static flush slots, <= 5
     // combine entries, the mirrors of the first 4 untangling rows above the bank
-    const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4;
+    const bool fast = h->mel_fast && h->mel_ch == SJ_MEL_FAST_CH && h->mel_ncomb <= 5 && h->mel_pskip >= 4 &&
+                      !h->gen_flags && h->log_floor == 2.e-42f;
     const int maxseg = h->mel_maxseg;
     if (fast) return tma ? launch_one<true, true, STREAM, PCM16>(a, maxseg, num_sms, stream)
                          : launch_one<false, true, STREAM, PCM16>(a, maxseg, num_sms, stream);

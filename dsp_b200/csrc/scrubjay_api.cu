@@ -18,7 +18,7 @@
 #include "sj_tables.h"
 
 cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
-                            cudaStream_t stream);
+                            int flavour, cudaStream_t stream);
 
 namespace {
 
@@ -54,6 +54,11 @@ struct scrubjay_ctx {
     int chunk_n_samples = 0;
     // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
     float *d_small = nullptr;
+    // grow-only device buffer of scrubjay_mfcc_stats (one clip): allocated on first use, never on the steady-state path
+    float *d_one = nullptr;
+    size_t one_bytes = 0;
+    // fault injection for tests (scrubjay_debug_inject_failure): the host pipeline fails before chunk number `fail_at_chunk`
+    long fail_at_chunk = -1;
     // keyword path (scrubjay_keyword_load): tables on the device, staging for the host form
     KwTables *d_kw_tables = nullptr;
     int kw_maxseg = 0;
@@ -208,7 +213,18 @@ int launch_cepstrum(scrubjay_ctx *c, cudaStream_t stream, const float *d_clips, 
 
 extern "C" {
 
+void scrubjay_cepstrum_params_default(scrubjay_cepstrum_params *p)
+{
+    if (p) sj_default_cepstrum_params(p);
+}
+
 int scrubjay_create(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes, unsigned samplerate)
+{
+    return scrubjay_create_ex(out, device, model_blob, blob_bytes, samplerate, nullptr);
+}
+
+int scrubjay_create_ex(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes, unsigned samplerate,
+                       const scrubjay_cepstrum_params *params)
 {
     g_create_err[0] = 0;
     if (!out) { snprintf(g_create_err, sizeof g_create_err, "out is NULL"); return SJ_EINVAL; }
@@ -234,7 +250,7 @@ int scrubjay_create(scrubjay_ctx **out, int device, const void *model_blob, size
     char terr[256] = {0};
     int rc = SJ_OK;
     if (!c->h_tables) rc = SJ_ENOMEM;
-    else if (sj_build_tables(c->h_tables, model_blob, blob_bytes, samplerate, terr)) {
+    else if (sj_build_tables(c->h_tables, model_blob, blob_bytes, samplerate, params, terr)) {
         snprintf(g_create_err, sizeof g_create_err, "%s", terr);
         rc = strstr(terr, "model") || strstr(terr, "support-vector") ? SJ_EMODEL : SJ_EINVAL;
     }
@@ -265,6 +281,7 @@ void scrubjay_destroy(scrubjay_ctx *c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
+    cudaFree(c->d_one);
     cudaFree(c->d_peers);
     cudaFree(c->d_frame_scratch);
     if (c->frame_scratch_free) cudaEventDestroy(c->frame_scratch_free);
@@ -613,9 +630,33 @@ int drain(scrubjay_ctx *c, Stage &s, int32_t *labels, float *conf, float *score,
     return SJ_OK;
 }
 
+// After a failed call nothing of it may survive into the next one: wait for whatever the stages still have in flight
+// and forget their pending outputs (they belong to the failed call's arrays).
+void reset_stages(scrubjay_ctx *c)
+{
+    for (Stage &s : c->st) {
+        if (s.stream && s.pending_first >= 0) cudaStreamSynchronize(s.stream);
+        s.pending_first = -1;
+        s.pending_count = 0;
+    }
+    (void)cudaGetLastError();
+}
+
+int run_host_batch_impl(scrubjay_ctx *c, const void *clips_v, long n_clips, int n_samples, int32_t *labels, float *conf,
+                        float *score, float *feats, int do_svm, int pcm16);
+
 // host clips -> chunked 3-stage pipeline.  do_svm = 0 computes features only.
 int run_host_batch(scrubjay_ctx *c, const void *clips_v, long n_clips, int n_samples, int32_t *labels, float *conf,
                    float *score, float *feats, int do_svm, int pcm16 = 0)
+{
+    reset_stages(c); // a previous call that failed half-way must not drain into this call's arrays
+    const int rc = run_host_batch_impl(c, clips_v, n_clips, n_samples, labels, conf, score, feats, do_svm, pcm16);
+    if (rc != SJ_OK) reset_stages(c);
+    return rc;
+}
+
+int run_host_batch_impl(scrubjay_ctx *c, const void *clips_v, long n_clips, int n_samples, int32_t *labels, float *conf,
+                        float *score, float *feats, int do_svm, int pcm16)
 {
     const unsigned char *clips = static_cast<const unsigned char *>(clips_v);
     const size_t es = pcm16 ? 2 : 4; // bytes per sample; the staging buffers are sized for float
@@ -628,6 +669,7 @@ int run_host_batch(scrubjay_ctx *c, const void *clips_v, long n_clips, int n_sam
         rc = drain(c, s, labels, conf, score, feats);
         if (rc != SJ_OK) return rc;
         const long n = (n_clips - done < c->chunk_clips) ? n_clips - done : c->chunk_clips;
+        if (c->fail_at_chunk == i) { c->fail_at_chunk = -1; return set_err(c, SJ_ECUDA, "injected failure (scrubjay_debug_inject_failure)"); }
         SJ_CUDA(c, cudaMemcpyAsync(s.d_clips, clips + (size_t)done * n_samples * es, (size_t)n * n_samples * es,
                                    cudaMemcpyHostToDevice, s.stream));
         rc = launch_cepstrum(c, s.stream, s.d_clips, n, n_samples, s.d_labels, s.d_conf, s.d_score,
@@ -680,16 +722,26 @@ int scrubjay_mfcc_stats(scrubjay_ctx *c, const float *samples, long n_samples, f
     if (!samples || !out) return set_err(c, SJ_EINVAL, "NULL pointer");
     if (n_samples <= 0 || n_samples > 0x7fffffffL) return set_err(c, SJ_EINVAL, "empty clip");
     SJ_CUDA(c, cudaSetDevice(c->device));
-    float *d = nullptr;
-    SJ_CUDA(c, cudaMalloc(&d, (size_t)n_samples * 4));
-    cudaError_t e = cudaMemcpyAsync(d, samples, (size_t)n_samples * 4, cudaMemcpyHostToDevice, c->stream);
+    // the clip goes through a grow-only buffer owned by the context (sized for 4 s at 96 kHz at first use): no
+    // allocation on the steady-state path
+    const size_t need = (size_t)n_samples * 4;
+    if (need > c->one_bytes) {
+        SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_one);
+        c->d_one = nullptr;
+        c->one_bytes = 0;
+        const size_t want = need > (1536u << 10) ? need : (size_t)(1536u << 10);
+        SJ_CUDA(c, cudaMalloc(&c->d_one, want));
+        c->one_bytes = want;
+    }
+    float *d = c->d_one;
+    cudaError_t e = cudaMemcpyAsync(d, samples, need, cudaMemcpyHostToDevice, c->stream);
     int rc = SJ_OK;
     if (e == cudaSuccess)
         rc = launch_cepstrum(c, c->stream, d, 1, (int)n_samples, nullptr, nullptr, nullptr, c->d_small, 0, false);
     if (e == cudaSuccess && rc == SJ_OK)
         e = cudaMemcpyAsync(out, c->d_small, SJ_FEAT * 4, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess && rc == SJ_OK) e = cudaStreamSynchronize(c->stream);
-    cudaFree(d);
     if (e != cudaSuccess) return set_err(c, SJ_ECUDA, "scrubjay_mfcc_stats", e);
     return rc;
 }
@@ -717,10 +769,17 @@ int scrubjay_predict(scrubjay_ctx *c, const float feat[SJ_FEAT_DIM], float *conf
 int scrubjay_synth_clips_dev(scrubjay_ctx *c, float *d_out, long first_clip, long n_clips, int n_samples,
                              unsigned seed)
 {
+    return scrubjay_synth_clips_ex_dev(c, d_out, first_clip, n_clips, n_samples, seed, SJ_SYNTH_MIXED);
+}
+
+int scrubjay_synth_clips_ex_dev(scrubjay_ctx *c, float *d_out, long first_clip, long n_clips, int n_samples,
+                                unsigned seed, int flavour)
+{
     if (!c) return SJ_EINVAL;
     if (!d_out || n_clips < 0 || n_samples <= 0) return set_err(c, SJ_EINVAL, "bad argument");
+    if (flavour != SJ_SYNTH_MIXED && flavour != SJ_SYNTH_CALLS) return set_err(c, SJ_EINVAL, "unknown synth flavour");
     SJ_CUDA(c, cudaSetDevice(c->device));
-    SJ_CUDA(c, sj_launch_synth(d_out, first_clip, n_clips, n_samples, seed, (float)c->samplerate, c->stream));
+    SJ_CUDA(c, sj_launch_synth(d_out, first_clip, n_clips, n_samples, seed, (float)c->samplerate, flavour, c->stream));
     if (n_clips > 0) c->launches += 1;
     return SJ_OK;
 }
@@ -733,10 +792,19 @@ int scrubjay_debug_mel_dense(unsigned samplerate, float *out)
     SjTables *t = new (std::nothrow) SjTables;
     if (!t) return SJ_ENOMEM;
     char err[256];
-    int rc = sj_build_tables(t, nullptr, 0, samplerate, err);
+    int rc = sj_build_tables(t, nullptr, 0, samplerate, nullptr, err);
     if (rc) { snprintf(g_create_err, sizeof g_create_err, "%s", err); delete t; return SJ_EINVAL; }
     sj_replay_mel_dense(t, out);
     delete t;
+    return SJ_OK;
+}
+
+/* test hook: the next host-pointer batch call fails (SJ_ECUDA) right before it would enqueue chunk number `chunk`
+ * (0-based), after the earlier chunks are in flight; -1 disarms */
+int scrubjay_debug_inject_failure(scrubjay_ctx *c, long chunk)
+{
+    if (!c) return SJ_EINVAL;
+    c->fail_at_chunk = chunk;
     return SJ_OK;
 }
 

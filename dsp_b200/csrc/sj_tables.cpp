@@ -64,7 +64,19 @@ static int fail(char *err, const char *msg)
     return -1;
 }
 
-static int build_mel(SjTables *t, unsigned samplerate, char *err)
+void sj_default_cepstrum_params(scrubjay_cepstrum_params *p)
+{
+    memset(p, 0, sizeof *p);
+    p->window = SJ_WINDOW_HANN_PERIODIC;
+    p->spectrum = SJ_SPECTRUM_MAGNITUDE;
+    p->log_floor = 2.e-42f;
+    p->dct_norm = SJ_DCT_ORTHO;
+    p->half_swap = 1;
+    p->label_rule = SJ_LABEL_PREDICT;
+}
+
+// `wscale`: factor folded into the weights -- the untangling step leaves |X| doubled (0.5), |X|^2 quadrupled (0.25)
+static int build_mel(SjTables *t, unsigned samplerate, float wscale, char *err)
 {
     std::vector<float> fb((size_t)SJ_NFILT * SJ_NBINS);
     sj_dense_slaney(fb.data(), samplerate);
@@ -119,8 +131,8 @@ static int build_mel(SjTables *t, unsigned samplerate, char *err)
             float a = 0.f, b = 0.f;
             bool step = false;
             if (k < SJ_NBINS && f0[k] >= 0) {
-                a = 0.5f * wlo[k];
-                b = 0.5f * whi[k];
+                a = wscale * wlo[k];
+                b = wscale * whi[k];
                 if (cur < 0) { cur = f0[k]; first_f[L] = cur; }
                 else if (f0[k] != cur) {
                     if (f0[k] != cur + 1) return fail(err, "filterbank edges skip a filter inside a bin chunk (unsupported samplerate)");
@@ -225,10 +237,20 @@ struct SjsvHeader {
     float gamma, rho, prob_a, prob_b;
 };
 
-int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned samplerate, char *err)
+int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned samplerate,
+                    const scrubjay_cepstrum_params *params, char *err)
 {
     memset(t, 0, sizeof(*t));
     if (samplerate == 0) return fail(err, "samplerate must be > 0");
+    scrubjay_cepstrum_params prm;
+    sj_default_cepstrum_params(&prm);
+    if (params) prm = *params;
+    if (prm.window != SJ_WINDOW_HANN_PERIODIC && prm.window != SJ_WINDOW_HANN_SYMMETRIC) return fail(err, "params: unknown window");
+    if (prm.spectrum != SJ_SPECTRUM_MAGNITUDE && prm.spectrum != SJ_SPECTRUM_POWER) return fail(err, "params: unknown spectrum kind");
+    if (prm.dct_norm != SJ_DCT_ORTHO && prm.dct_norm != SJ_DCT_UNNORMALISED) return fail(err, "params: unknown DCT normalisation");
+    if (prm.label_rule < SJ_LABEL_PREDICT || prm.label_rule > SJ_LABEL_PROB_ARGMAX) return fail(err, "params: unknown label rule");
+    if (!(prm.log_floor > 0.f)) return fail(err, "params: log_floor must be > 0");
+    if (prm.reserved[0] || prm.reserved[1]) return fail(err, "params: reserved fields must be 0");
     const double two_pi = 6.283185307179586476925286766559;
     for (int a = 0; a < 16; ++a)
         for (int b = 0; b < 32; ++b) {
@@ -245,12 +267,23 @@ int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned s
         t->tp4[0][b].z = 0.f;
         t->tp4[0][b].w = 0.f;
     }
-    if (build_mel(t, samplerate, err)) return -1;
-    // aubio mfcc.c: orthonormal DCT-II over the 40 log energies, first 20 rows kept
+    const bool power = prm.spectrum == SJ_SPECTRUM_POWER;
+    if (build_mel(t, samplerate, power ? 0.25f : 0.5f, err)) return -1;
+    t->gen_flags = (power ? SJ_GEN_POWER : 0) | (prm.window != SJ_WINDOW_HANN_PERIODIC ? SJ_GEN_WINDOW_TABLE : 0);
+    t->log_floor = prm.log_floor;
+    t->label_rule = prm.label_rule;
+    // the specialised 16 kHz instantiation hard-codes the in-register periodic Hann, |X| and the 2e-42 floor
+    if (t->gen_flags || prm.log_floor != 2.e-42f) t->mel_fast = 0;
+    for (int i = 0; i < SJ_WIN; ++i) {
+        const double den = prm.window == SJ_WINDOW_HANN_SYMMETRIC ? (double)(SJ_WIN - 1) : (double)SJ_WIN;
+        t->window[i] = (float)(0.5 * (1.0 - cos(two_pi * (double)i / den)));
+    }
+    // aubio mfcc.c: orthonormal DCT-II over the 40 log energies, first 20 rows kept (or the unnormalised 2 sum cos form)
     const double pi = two_pi / 2;
     for (int m = 0; m < SJ_NFILT; ++m)
         for (int c = 0; c < SJ_NCOEF; ++c) {
             double s = c == 0 ? sqrt(1.0 / SJ_NFILT) : sqrt(2.0 / SJ_NFILT);
+            if (prm.dct_norm == SJ_DCT_UNNORMALISED) s = 2.0;
             t->dct[m][c] = (float)(s * cos(pi * c * (m + 0.5) / SJ_NFILT));
         }
     if (!blob) { blob = sj_default_model_words; blob_bytes = sj_default_model_bytes; }

@@ -4,6 +4,8 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include "../../include/scrubjay_cuda.h"
+
 #define SJ_WIN 2048
 #define SJ_HOP 1024
 #define SJ_NBINS 1025
@@ -37,7 +39,12 @@ struct SjTables {
     //   generic layout: slots are filled in order, partial (L, s) at P[L*mel_maxseg + s].
     SjQuad melw4[SJ_MAX_CH / 2][32];
     int32_t mel_lo, mel_ch, mel_maxseg, mel_ncomb;
-    int32_t mel_fast, mel_pskip, pad_a, pad_b;
+    int32_t mel_fast, mel_pskip;
+    // table-driven switches of the generic instantiation (scrubjay_cepstrum_params): SJ_GEN_WINDOW_TABLE = the window
+    // comes from `window` below instead of the in-register periodic Hann; SJ_GEN_POWER = the filterbank works on
+    // |X|^2 (the mel weights then carry 0.25 instead of 0.5)
+    int32_t gen_flags;
+    float log_floor; // energies are raised to this before log10 (aubio VERY_SMALL_NUMBER = 2e-42)
     // combine lists: energy of filter m = sum_e P[comb[e][m]] over e < mel_ncomb; unused entries point
     // at a zero slot.  comb2[e][lane] packs the entries of filters lane (low 16 bits) and lane+32 (high).
     uint32_t comb2[SJ_MAX_COMB][32];
@@ -48,13 +55,20 @@ struct SjTables {
     float sv[SJ_FEAT][SJ_MAX_SV]; // support vectors transposed: sv[i][j] = SV_j[i]
     float sv_coef[SJ_MAX_SV];     // zero beyond n_sv
     float gamma, rho, prob_a, prob_b;
-    int32_t n_sv, pad0, pad1, pad2;
+    int32_t n_sv, label_rule /* SJ_LABEL_* */, pad1, pad2;
     // real-FFT untangling base twiddles W_2048^lane = (x, y) (the kernel reads its own entry once, from global memory)
     SjQuad tp4[1][32];
+    // analysis window of the generic instantiation when SJ_GEN_WINDOW_TABLE is set (read through L1 from global memory)
+    float window[SJ_WIN];
 };
+#define SJ_GEN_WINDOW_TABLE 1
+#define SJ_GEN_POWER 2
 
 // Builds the tables.  Returns 0, or a negative value and a message in `err` (size >= 256).
-int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned samplerate, char *err);
+// `params` NULL = the defaults (restated aubio 0.4.x / onnxruntime behaviour).
+int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned samplerate,
+                    const scrubjay_cepstrum_params *params, char *err);
+void sj_default_cepstrum_params(scrubjay_cepstrum_params *p);
 // dense [40][1025] Slaney bank (aubio filterbank_mel.c semantics), used by the builder and by tests
 void sj_dense_slaney(float *fb /*[40][1025]*/, unsigned samplerate);
 // dense [40][1025] bank recovered by replaying the kernel's sparse walk over the built tables (weights carry 0.5)

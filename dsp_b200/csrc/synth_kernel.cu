@@ -22,6 +22,47 @@ __device__ __forceinline__ float u01(uint32_t h) { return (float)(h >> 8) * (1.0
 
 struct Chirp { float f0, k, amp; int start, stop; };
 
+// flavour 1 (SJ_SYNTH_CALLS): "donut"-shaped calls -- a faint noise floor and three frequency-modulated bursts around a
+// common centre time (600-2400 Hz and 5100-6900 Hz for 0.4 s, 2600-4900 Hz for 0.14 s), amplitudes log-uniform per
+// clip -- placed so that every donut variant's verdict (classifier.c:184) fires on a sizeable fraction
+// of the clips and misses on the rest (the mixed flavour never makes the double-precision desktop variant say 1).
+// Mirror: tools/synth_np.py:synth_call_clips.
+__global__ void synth_calls_kernel(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs)
+{
+    const float fc_hz[3] = {3750.f, 1500.f, 6000.f}, dev_hz[3] = {1150.f, 900.f, 900.f}, half_s[3] = {0.07f, 0.20f, 0.20f};
+    const float l0[3] = {-1.5f, -1.5f, -2.7f}, span[3] = {1.1f, 1.0f, 1.2f};
+    const float fm = 15.f;
+    for (long c = blockIdx.x; c < n_clips; c += gridDim.x) {
+        const uint32_t cid = (uint32_t)(first_clip + c);
+        const uint32_t hc = hash3(seed, cid, 0xCA11u);
+        const float na = exp2f(3.3219281f * (-3.0f + 0.8f * u01(mix32(hc + 1))));
+        const float centre = 0.5f + 0.16f * (u01(mix32(hc + 2)) - 0.5f);
+        float amp[3], beta[3];
+        int start[3], stop[3];
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t h = hash3(seed, cid, 0x2000u + k);
+            amp[k] = exp2f(3.3219281f * (l0[k] + span[k] * u01(mix32(h + 1))));
+            start[k] = (int)((centre - half_s[k]) * fs);
+            stop[k] = (int)((centre + half_s[k]) * fs);
+            beta[k] = dev_hz[k] / (6.2831855f * fm);
+        }
+        float *dst = out + c * (long)n_samples;
+        for (int i = threadIdx.x; i < n_samples; i += blockDim.x) {
+            float x = na * (2.f * u01(hash3(seed, cid, 0x10000u + (uint32_t)i)) - 1.f);
+            for (int k = 0; k < 3; ++k)
+                if (i >= start[k] && i < stop[k]) {
+                    const float t = (float)(i - start[k]);
+                    float mod = t * (fm / fs);
+                    mod -= floorf(mod);
+                    float cyc = t * (fc_hz[k] / fs) + beta[k] * sinpif(2.f * mod);
+                    cyc -= floorf(cyc);
+                    x += amp[k] * sinpif(2.f * cyc);
+                }
+            dst[i] = x;
+        }
+    }
+}
+
 __global__ void synth_kernel(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs)
 {
     const float lo_hz[4] = {500.f, 2500.f, 5000.f, 1000.f}, hi_hz[4] = {2500.f, 5000.f, 7000.f, 3000.f};
@@ -66,10 +107,11 @@ __global__ void synth_kernel(float *out, long first_clip, long n_clips, int n_sa
 } // namespace
 
 cudaError_t sj_launch_synth(float *out, long first_clip, long n_clips, int n_samples, uint32_t seed, float fs,
-                            cudaStream_t stream)
+                            int flavour, cudaStream_t stream)
 {
     if (n_clips <= 0) return cudaSuccess;
     long blocks = n_clips < 148 * 16 ? n_clips : 148 * 16;
-    synth_kernel<<<(unsigned)blocks, 256, 0, stream>>>(out, first_clip, n_clips, n_samples, seed, fs);
+    if (flavour == 1) synth_calls_kernel<<<(unsigned)blocks, 256, 0, stream>>>(out, first_clip, n_clips, n_samples, seed, fs);
+    else synth_kernel<<<(unsigned)blocks, 256, 0, stream>>>(out, first_clip, n_clips, n_samples, seed, fs);
     return cudaGetLastError();
 }

@@ -57,6 +57,38 @@ typedef struct scrubjay_ctx scrubjay_ctx;
  * for the material (:28); it selects the Slaney filterbank. */
 SJ_API int scrubjay_create(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes,
                     unsigned samplerate);
+
+/* The literals of the cepstrum path that live in the two UN-VENDORED libraries behind
+ * cepstrum/scrubjay_infer.c (aubio: :21,29-30,44-45; onnxruntime: :119-134) as ONE plain-data parameter
+ * block, so that each "aubio-ism" / "ORT-ism" this library restates from the published algorithms can be
+ * switched without a code change the day a real aubio / onnxruntime vector disagrees with the restatement
+ * (SURVEY 5 "Config / flags", 7 "Hard parts").  The defaults (scrubjay_cepstrum_params_default, also what
+ * scrubjay_create uses) are the restated aubio 0.4.x / ORT behaviour.  The same struct drives the CPU oracle
+ * (oracle/cepstrum_oracle.c), so every switch has a checker. */
+#define SJ_WINDOW_HANN_PERIODIC 0  /* aubio "hanningz": 0.5 (1 - cos(2 pi i / N)) -- new_aubio_pvoc's window */
+#define SJ_WINDOW_HANN_SYMMETRIC 1 /* 0.5 (1 - cos(2 pi i / (N - 1))) (numpy.hanning, aubio "hanning") */
+#define SJ_SPECTRUM_MAGNITUDE 0    /* filterbank on |X| (aubio_filterbank power = 1, the 0.4.9 default) */
+#define SJ_SPECTRUM_POWER 1        /* filterbank on |X|^2 (aubio_filterbank_set_power(fb, 2); librosa's convention) */
+#define SJ_DCT_ORTHO 0             /* aubio_dct: row 0 scaled sqrt(1/N), others sqrt(2/N) */
+#define SJ_DCT_UNNORMALISED 1      /* 2 sum_m e[m] cos(pi c (m + 1/2) / N) (scipy dct(type=2, norm=None), FFTW REDFT10) */
+#define SJ_LABEL_PREDICT 0         /* label 1 iff decision_function > 0  (cepstrum/run.py:46 model.predict; SURVEY B.3 rule ii) */
+#define SJ_LABEL_VOTE 1            /* label 1 iff ORT score <= 0, i.e. decision_function >= 0 (libsvm vote; rule i) */
+#define SJ_LABEL_PROB_ARGMAX 2     /* argmax of the Platt probability pair, ties -> class 0 (rule iii) */
+typedef struct scrubjay_cepstrum_params {
+    int32_t window;     /* SJ_WINDOW_* */
+    int32_t spectrum;   /* SJ_SPECTRUM_* */
+    float log_floor;    /* aubio VERY_SMALL_NUMBER: energies below it are raised to it before log10 (2e-42) */
+    int32_t dct_norm;   /* SJ_DCT_* */
+    int32_t half_swap;  /* aubio fvec_shift before the FFT (1 = aubio).  Multiplies bin k by (-1)^k: only the phase
+                           changes and the path uses |X| alone, so the kernel ignores it; the oracle honours it */
+    int32_t label_rule; /* SJ_LABEL_* */
+    int32_t reserved[2]; /* must be 0 */
+} scrubjay_cepstrum_params;
+SJ_API void scrubjay_cepstrum_params_default(scrubjay_cepstrum_params *p);
+/* scrubjay_create with an explicit parameter block (NULL = defaults).  Non-default window / spectrum / log_floor
+ * select the kernel's table-driven (generic) instantiation instead of the specialised 16 kHz one. */
+SJ_API int scrubjay_create_ex(scrubjay_ctx **out, int device, const void *model_blob, size_t blob_bytes,
+                       unsigned samplerate, const scrubjay_cepstrum_params *params);
 SJ_API void scrubjay_destroy(scrubjay_ctx *ctx);
 /* ctx may be NULL: returns the message of the last failed scrubjay_create on this thread */
 SJ_API const char *scrubjay_last_error(const scrubjay_ctx *ctx);
@@ -322,10 +354,23 @@ SJ_API int classify_signal_binary(const float *signal, int num_samples, float th
  * silent or with a silent tail.  Not a reference function; the bench's "data": "synthetic". */
 SJ_API int scrubjay_synth_clips_dev(scrubjay_ctx *ctx, float *d_out, long first_clip, long n_clips,
                                     int n_samples, unsigned seed);
+/* The same with a choice of flavour: SJ_SYNTH_MIXED = the generator above; SJ_SYNTH_CALLS = "donut"-shaped calls (a
+ * faint noise floor and three frequency-modulated bursts at 600-2400 / 2600-4900 / 5100-6900 Hz around a common
+ * centre) on which every donut variant's verdict -- the double-precision desktop one included -- says 1 on a
+ * sizeable fraction of the clips. */
+#define SJ_SYNTH_MIXED 0
+#define SJ_SYNTH_CALLS 1
+SJ_API int scrubjay_synth_clips_ex_dev(scrubjay_ctx *ctx, float *d_out, long first_clip, long n_clips,
+                                       int n_samples, unsigned seed, int flavour);
 
 /* Diagnostic, host only (no GPU needed): the kernel's sparse filterbank tables for `samplerate`,
  * expanded to a dense [40][1025] float array (weights carry a factor 0.5). */
 SJ_API int scrubjay_debug_mel_dense(unsigned samplerate, float *out);
+
+/* Test hook (fault injection): the next host-pointer batch call (scrubjay_infer_batch / _pcm16) returns SJ_ECUDA right
+ * before it would enqueue its chunk number `chunk` (0-based; chunks are 256 MiB of clips), with the earlier chunks in
+ * flight.  The call after a failed one must not see anything of it (tests/test_cepstrum_gpu.py).  -1 disarms. */
+SJ_API int scrubjay_debug_inject_failure(scrubjay_ctx *ctx, long chunk);
 
 /* Pinned (page-locked) host memory: clips handed to the host-pointer entry points from such a
  * buffer move at full PCIe rate; pageable memory works too, slower. */

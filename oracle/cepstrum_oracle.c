@@ -24,6 +24,10 @@
 #include <stdlib.h>
 #include <string.h>
 
+/* the parameter block (plain data) is shared with the product's public header, so that every switch of
+ * scrubjay_cepstrum_params has its checker here; nothing else of the product is used */
+#include "../include/scrubjay_cuda.h"
+
 #ifndef SJ_REAL
 #define SJ_REAL double
 #endif
@@ -41,7 +45,8 @@ typedef SJ_REAL real_t;
 
 typedef struct {
     unsigned sr;
-    float window[WIN_SIZE];           /* aubio "hanningz": 0.5*(1-cos(2*pi*i/N)), periodic */
+    scrubjay_cepstrum_params prm;     /* the switchable aubio-isms / ORT-isms; defaults = restated aubio 0.4.x / ORT */
+    float window[WIN_SIZE];           /* aubio "hanningz": 0.5*(1-cos(2*pi*i/N)), periodic (or the symmetric form) */
     float fbank[N_FILTERS][N_BINS];   /* Slaney triangles, dense like aubio's fmat */
     float dct[N_MFCC][N_FILTERS];     /* orthonormal DCT-II rows 0..19 */
     real_t tw_re[WIN_SIZE / 2], tw_im[WIN_SIZE / 2]; /* exp(-2*pi*i*k/2048), k<1024 */
@@ -81,19 +86,35 @@ static void build_slaney(float fb[N_FILTERS][N_BINS], unsigned sr)
     }
 }
 
-sj_oracle_t *sj_oracle_new(unsigned sr)
+static void default_params(scrubjay_cepstrum_params *p)
+{
+    memset(p, 0, sizeof *p);
+    p->window = SJ_WINDOW_HANN_PERIODIC;   /* new_aubio_pvoc -> new_aubio_window("hanningz") */
+    p->spectrum = SJ_SPECTRUM_MAGNITUDE;   /* aubio_filterbank power = 1 */
+    p->log_floor = 2.e-42f;                /* VERY_SMALL_NUMBER */
+    p->dct_norm = SJ_DCT_ORTHO;            /* aubio_dct */
+    p->half_swap = 1;                      /* fvec_shift in aubio_pvoc_do */
+    p->label_rule = SJ_LABEL_PREDICT;      /* cepstrum/run.py:46 */
+}
+
+sj_oracle_t *sj_oracle_new_ex(unsigned sr, const scrubjay_cepstrum_params *prm)
 {
     sj_oracle_t *o = (sj_oracle_t *)calloc(1, sizeof(*o));
     int i, j;
     if (!o) return NULL;
     o->sr = sr;
-    for (i = 0; i < WIN_SIZE; i++)
-        o->window[i] = (float)(0.5 * (1.0 - cos(2.0 * SJ_PI * i / (double)WIN_SIZE)));
+    default_params(&o->prm);
+    if (prm) o->prm = *prm;
+    for (i = 0; i < WIN_SIZE; i++) {
+        double den = o->prm.window == SJ_WINDOW_HANN_SYMMETRIC ? (double)(WIN_SIZE - 1) : (double)WIN_SIZE;
+        o->window[i] = (float)(0.5 * (1.0 - cos(2.0 * SJ_PI * i / den)));
+    }
     build_slaney(o->fbank, sr);
-    /* aubio mfcc.c / dct_plain.c: out[0] scaled by sqrt(1/N), others sqrt(2/N) */
+    /* aubio mfcc.c / dct_plain.c: out[0] scaled by sqrt(1/N), others sqrt(2/N); or the unnormalised 2 sum cos form */
     for (j = 0; j < N_MFCC; j++)
         for (i = 0; i < N_FILTERS; i++) {
             double s = (j == 0) ? sqrt(1.0 / N_FILTERS) : sqrt(2.0 / N_FILTERS);
+            if (o->prm.dct_norm == SJ_DCT_UNNORMALISED) s = 2.0;
             o->dct[j][i] = (float)(s * cos(SJ_PI * j * (i + 0.5) / N_FILTERS));
         }
     for (i = 0; i < WIN_SIZE / 2; i++) {
@@ -102,6 +123,8 @@ sj_oracle_t *sj_oracle_new(unsigned sr)
     }
     return o;
 }
+
+sj_oracle_t *sj_oracle_new(unsigned sr) { return sj_oracle_new_ex(sr, NULL); }
 
 void sj_oracle_free(sj_oracle_t *o) { free(o); }
 
@@ -153,7 +176,7 @@ static void rfft_mag(const sj_oracle_t *o, const float *frame, float *norm)
     }
 }
 
-#define VERY_SMALL_NUMBER 2.e-42f /* aubio_priv.h; SAFE_LOG10 = log10(max(x, 2e-42)) */
+/* aubio_priv.h: VERY_SMALL_NUMBER 2.e-42; SAFE_LOG10 = log10(max(x, 2e-42)) -- params.log_floor */
 
 /* One aubio_pvoc_do + aubio_mfcc_do (cepstrum/scrubjay_infer.c:44-45) on a 2048-sample buffer
  * `data` = [previous hop | new hop].  Writes 20 coefficients. */
@@ -162,14 +185,17 @@ static void frame_mfcc(const sj_oracle_t *o, const float *data, float *mfcc)
     float frame[WIN_SIZE], norm[N_BINS], in_dct[N_FILTERS];
     int i, m, c;
     /* pvoc.c: fvec_weight(data, w); fvec_shift(data) (swap halves: phase only); fft; norm */
-    for (i = 0; i < WIN_SIZE; i++) frame[(i + WIN_SIZE / 2) % WIN_SIZE] = data[i] * o->window[i];
+    for (i = 0; i < WIN_SIZE; i++) frame[o->prm.half_swap ? (i + WIN_SIZE / 2) % WIN_SIZE : i] = data[i] * o->window[i];
     rfft_mag(o, frame, norm);
-    /* filterbank.c: fmat_vecmul(filters, norm) -- dense, magnitude (power == 1) */
+    /* filterbank.c: aubio_filterbank_do raises norm to `power` when power != 1 (fvec_pow), then
+     * fmat_vecmul(filters, norm) -- dense */
+    if (o->prm.spectrum == SJ_SPECTRUM_POWER)
+        for (i = 0; i < N_BINS; i++) norm[i] = norm[i] * norm[i];
     for (m = 0; m < N_FILTERS; m++) {
         real_t acc = 0;
         for (i = 0; i < N_BINS; i++) acc += (real_t)o->fbank[m][i] * (real_t)norm[i];
         float e = (float)acc;
-        if (e < VERY_SMALL_NUMBER) e = VERY_SMALL_NUMBER;
+        if (e < o->prm.log_floor) e = o->prm.log_floor;
         in_dct[m] = (float)log10((double)e); /* fvec_log10 */
     }
     for (c = 0; c < N_MFCC; c++) {
@@ -263,7 +289,15 @@ static void multiclass_probability2(double r01, double p[2])
  * `score` receives d = -(sum_j coef_j K_j + rho) = sklearn decision_function (positive => class 1).
  * Label rule: SURVEY.md Appendix B.3 (ii), the rule of cepstrum/run.py:46 (model.predict):
  * label = 1 iff d > 0.  conf = probability of the predicted class (:134). */
+int sj_oracle_predict_ex(const void *blob, const float feat[FEAT_DIM], int label_rule, float *conf, float *score);
 int sj_oracle_predict(const void *blob, const float feat[FEAT_DIM], float *conf, float *score)
+{
+    return sj_oracle_predict_ex(blob, feat, SJ_LABEL_PREDICT, conf, score);
+}
+
+/* label_rule: the three candidate rules of SURVEY.md B.3 -- (ii) run.py's model.predict d > 0 (default),
+ * (i) libsvm's vote s <= 0, (iii) argmax of the probability pair with ties to class 0 */
+int sj_oracle_predict_ex(const void *blob, const float feat[FEAT_DIM], int label_rule, float *conf, float *score)
 {
     const sjsv_hdr_t *h = (const sjsv_hdr_t *)blob;
     const float *offset = (const float *)(h + 1), *scale = offset + h->dim;
@@ -279,11 +313,13 @@ int sj_oracle_predict(const void *blob, const float feat[FEAT_DIM], float *conf,
     }
     s += h->rho;
     double d = -s;
-    int label = d > 0 ? 1 : 0;
     double r01 = sigmoid_predict(s, h->prob_a, h->prob_b), p[2];
     if (r01 < 1e-7) r01 = 1e-7;
     if (r01 > 1 - 1e-7) r01 = 1 - 1e-7;
     multiclass_probability2(r01, p);
+    /* the GPU forms the score in float; the sign tests are taken on the float-rounded values there as here */
+    int label = label_rule == SJ_LABEL_VOTE ? ((float)s <= 0.f ? 1 : 0)
+              : label_rule == SJ_LABEL_PROB_ARGMAX ? (p[1] > p[0] ? 1 : 0) : ((float)d > 0.f ? 1 : 0);
     if (conf) *conf = (float)p[label];
     if (score) *score = (float)d;
     return label;
@@ -297,7 +333,7 @@ long sj_oracle_infer_batch(const sj_oracle_t *o, const void *blob, const float *
     for (c = 0; c < n_clips; c++) {
         float f[FEAT_DIM], cf = 0, sc = 0;
         if (sj_oracle_mfcc_stats(o, clips + c * n_samples, n_samples, f, NULL) < 0) return -1;
-        int l = sj_oracle_predict(blob, f, &cf, &sc);
+        int l = sj_oracle_predict_ex(blob, f, o->prm.label_rule, &cf, &sc);
         if (labels) labels[c] = l;
         if (conf) conf[c] = cf;
         if (score) score[c] = sc;

@@ -152,6 +152,46 @@ class DonutRef64:
         self.L.compute_spectrogram.argtypes = [vp, c_int, c_int, vp, vp, vp, vp, vp]
         self.L.find_midpoints.argtypes = [vp, c_int, c_int, vp]
         self.L.find_midpoints.restype = ctypes.POINTER(ctypes.c_double)
+        cd = ctypes.c_double
+        self.L.sum_intense.argtypes = [cd, cd, cd, vp, c_int, vp, c_int, vp, cd]
+        self.L.sum_intense.restype = cd
+
+    def sum_intense(self, lower, upper, half_range, freqs, times, plane, midpoint):
+        """the unmodified sum_intense (classifier.c:594-655) on a [freq][time] double plane (NaN = filtered out)"""
+        fr = np.ascontiguousarray(freqs, np.float64)
+        tm = np.ascontiguousarray(times, np.float64)
+        pl = np.ascontiguousarray(plane, np.float64)
+        rows = (vp * pl.shape[0])(*[pl[i].ctypes.data for i in range(pl.shape[0])])
+        return float(self.L.sum_intense(lower, upper, half_range, fr.ctypes.data, fr.size, tm.ctypes.data, tm.size,
+                                        ctypes.cast(rows, vp), midpoint))
+
+    def classify_main(self, clip, lo_norm=0.70, hi_norm=0.85, thr=(300.0, 75.0, 100.0)):
+        """The per-file body of main (classifier.c:84-198) driven through the UNMODIFIED functions of the reference
+        build: butter_bandpass_filter, compute_spectrogram, find_midpoints and sum_intense are the reference's own
+        code; only main's inline element-wise step (:104-156: dB, min / max, normalise, keep lo < v < hi) is restated
+        here in float64 numpy.  Returns (label, midpoints, [(above, middle, below) per evaluated midpoint])."""
+        x = np.ascontiguousarray(clip, np.float64)
+        S = self.spectrogram(self.filter(x, 3000, 7500))
+        import warnings
+        with np.errstate(divide="ignore", invalid="ignore"), warnings.catch_warnings():
+            warnings.simplefilter("ignore")  # an all-zero clip has no positive cell: min / max stay NaN, nothing passes
+            dB = np.where(S > 0, 10.0 * np.log10(S / 1e-12), np.nan)
+            mn, mx = np.nanmin(dB), np.nanmax(dB)
+            nv = (dB - mn) / (mx - mn)
+            plane = np.where((nv > lo_norm) & (nv < hi_norm), nv, np.nan)
+        freqs = np.arange(S.shape[0]) * (16000.0 / 256.0)              # classifier.c:466-469
+        times = (np.arange(S.shape[1]) * 224 + 128) / 16000.0          # :471-474
+        mids = self.midpoints(x)
+        sums, label = [], 0
+        for m in mids:
+            a = _silence_stdout(self.sum_intense, 5000, 7000, 0.18, freqs, times, plane, m)
+            mi = _silence_stdout(self.sum_intense, 2500, 5000, 0.05, freqs, times, plane, m)
+            b = _silence_stdout(self.sum_intense, 500, 2500, 0.18, freqs, times, plane, m)
+            sums.append((a, mi, b))
+            if mi < thr[1] and a > thr[0] and b > thr[2]:               # :184
+                label = 1
+                break
+        return label, mids, sums
 
     def filter(self, x, lo, hi):
         x = np.ascontiguousarray(x, np.float64).copy()

@@ -18,14 +18,17 @@ def build_oracle():
 class CepstrumOracle:
     """oracle/cepstrum_oracle.c: restated aubio pvoc+mfcc (+ stats) and ORT Scaler+SVMClassifier."""
 
-    def __init__(self, samplerate=16000, precision="f64"):
+    def __init__(self, samplerate=16000, precision="f64", params=None):
+        """params: a dsp_b200.CepstrumParams (the POD both the library and this oracle consume) or None = defaults"""
         path = os.path.join(ORACLE_DIR, "libsj_oracle_%s.so" % precision)
         if not os.path.exists(path):
             build_oracle()
         L = ctypes.CDLL(path)
         vp, c_long = ctypes.c_void_p, ctypes.c_long
-        L.sj_oracle_new.restype = vp
-        L.sj_oracle_new.argtypes = [ctypes.c_uint]
+        L.sj_oracle_new_ex.restype = vp
+        L.sj_oracle_new_ex.argtypes = [ctypes.c_uint, vp]
+        L.sj_oracle_predict_ex.restype = ctypes.c_int
+        L.sj_oracle_predict_ex.argtypes = [vp, vp, ctypes.c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_float)]
         L.sj_oracle_free.argtypes = [vp]
         L.sj_oracle_mfcc_stats.restype = c_long
         L.sj_oracle_mfcc_stats.argtypes = [vp, vp, c_long, vp, vp]
@@ -36,7 +39,9 @@ class CepstrumOracle:
         L.sj_oracle_fbank.restype = ctypes.POINTER(ctypes.c_float)
         L.sj_oracle_fbank.argtypes = [vp]
         self.L = L
-        self.h = L.sj_oracle_new(samplerate)
+        self.params = params
+        self.h = L.sj_oracle_new_ex(samplerate, ctypes.addressof(params) if params is not None else None)
+        self.label_rule = params.label_rule if params is not None else 0
         self.blob = open(MODEL_BLOB, "rb").read()
 
     def fbank(self):
@@ -55,7 +60,7 @@ class CepstrumOracle:
     def predict(self, feat, blob=None):
         f = np.ascontiguousarray(feat, np.float32)
         c, s = ctypes.c_float(), ctypes.c_float()
-        label = self.L.sj_oracle_predict(blob or self.blob, f.ctypes.data, ctypes.byref(c), ctypes.byref(s))
+        label = self.L.sj_oracle_predict_ex(blob or self.blob, f.ctypes.data, self.label_rule, ctypes.byref(c), ctypes.byref(s))
         return label, c.value, s.value
 
     def infer_batch(self, clips):

@@ -196,3 +196,29 @@ def test_labels_identical_on_a_model_that_splits_the_synthetic_clips():
     assert np.array_equal(gl[decided], ol[decided])
     assert (~decided).sum() <= 0.02 * n
     assert np.abs(gc - oc)[decided].max() <= 5e-3
+
+
+def test_failed_host_call_leaves_nothing_behind_for_the_next_one():
+    """a host-pointer call that fails half-way (chunks still in flight) must not drain its pending results
+    into the arrays of the NEXT call (stale data / out-of-bounds host writes when the new arrays are smaller).  The
+    failure is injected before chunk 2 of a 3-chunk batch (scrubjay_debug_inject_failure)."""
+    import dsp_b200
+    sj = _ctx()
+    ns = 1024                                  # 256 MiB chunks = 65536 clips of 1024 samples
+    big = np.random.default_rng(5).uniform(-0.5, 0.5, (65536 * 2 + 100, ns)).astype(np.float32)
+    sj.debug_inject_failure(2)
+    with pytest.raises(dsp_b200.ScrubJayError, match="injected failure"):
+        sj.infer_batch(big)
+    small = np.random.default_rng(6).uniform(-0.5, 0.5, (10, ns)).astype(np.float32)
+    guard = np.full(64, -7, np.int32)           # the labels array of the next call sits inside a guarded block
+    labels = guard[20:30]
+    conf = np.empty(10, np.float32); score = np.empty(10, np.float32)
+    sj._check(sj._L.scrubjay_infer_batch(sj._h, small.ctypes.data, 10, ns, labels.ctypes.data, conf.ctypes.data,
+                                         score.ctypes.data, None))
+    gl, gc, gs, _ = _run_dev(sj, small)
+    assert np.array_equal(labels, gl) and np.array_equal(score, gs) and np.array_equal(conf, gc)
+    assert (guard[:20] == -7).all() and (guard[30:] == -7).all(), "the failed call's results leaked into the next call"
+    # and the pipeline still works for a multi-chunk batch afterwards
+    hl, hc, hs = sj.infer_batch(big[:65536 + 50])
+    dl, dc, ds, _ = _run_dev(sj, big[:65536 + 50])
+    assert np.array_equal(hl, dl) and np.array_equal(hs, ds)

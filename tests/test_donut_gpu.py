@@ -151,7 +151,7 @@ def test_permutation_equivariance_large():
     assert np.array_equal(a[0][p], b[0]) and np.array_equal(a[1][p], b[1])
 
 
-@pytest.mark.parametrize("variant,prec,tol", [(2, "f64", 1e-3), (3, "f32", 2.0)])
+@pytest.mark.parametrize("variant,prec,tol", [(2, "f64", 1e-3), (3, "f32", 0.01)])
 def test_other_reference_variants_match_port(variant, prec, tol):
     """revert.c / microphone/src/classifier.c (double, gap tolerance 0.15 s) and microphone/src/classifier.cpp
     (float): same kernels, the variant's own constants"""
@@ -160,8 +160,10 @@ def test_other_reference_variants_match_port(variant, prec, tol):
     d = _synth(sj, 9000, 768)
     gl, gd = _gpu(sj, d, variant)
     ol, od = DonutPort(prec).classify_batch(d.cpu().numpy(), variant=variant)
+    # the float variant replays PlainFFT bit for bit, so variant 3 holds the same bar as variant 1 (0.01 on the sums,
+    # no label mismatch); only the accumulation order of the box sums differs from the reference's
     mism, near = _compare(gl, gd, ol, od, variant, sum_tol=tol)
-    assert mism <= near
+    assert mism == 0
     assert (od[:, 0] > 0).mean() > 0.5
 
 
@@ -203,3 +205,80 @@ def test_small_batch_grouping_equals_large_batch_grouping(variant):
     for n in (1, 2, 37, 700, 1500, 5000):  # 1, 1, 1, 1-2, 3, 8-ish clips per CTA
         l, d = _gpu(sj, big[:n].contiguous(), variant)
         assert np.array_equal(l, ref_l[:n]) and np.array_equal(d, ref_d[:n], equal_nan=True), "n = %d" % n
+
+
+def _synth_calls(sj, first, n, ns=16000):
+    import torch
+    import dsp_b200
+    d = torch.empty((n, ns), dtype=torch.float32, device="cuda")
+    sj.set_stream(torch.cuda.current_stream().cuda_stream)
+    sj.synth_clips_dev(d, first, n, ns, flavour=dsp_b200.SYNTH_CALLS)
+    torch.cuda.synchronize()
+    return d
+
+
+def test_f64_verdict_pinned_to_unmodified_reference_functions_on_1024_clips():
+    """the double variant's labels were pinned only through the port.  Here the GPU's midpoints, band
+    sums and labels are held against the per-file body of main (classifier.c:84-198) driven through the UNMODIFIED
+    butter_bandpass_filter / compute_spectrogram / find_midpoints / sum_intense of oracle/_ref/libdonut_ref_f64.so, on
+    768 "call"-flavoured clips -- on which the desktop variant says 1 about half the time -- and 256 mixed clips."""
+    import torch
+    import dsp_b200
+    from donut_lib import DonutRef64, have_ref
+    assert have_ref(), "oracle/_ref not shipped"
+    sj = _ctx()
+    d = torch.cat([_synth_calls(sj, 2000, 768), _synth(sj, 2000, 256)])
+    n = d.shape[0]
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    detail = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    mids = torch.empty((n, dsp_b200.DONUT_MAX_MID), dtype=torch.float32, device="cuda")
+    sj.donut_midpoints_batch_dev(d, n, 16000, dsp_b200.DONUT_DESKTOP_F64, labels, detail, mids)
+    torch.cuda.synchronize()
+    gl, gd, gm = labels.cpu().numpy(), detail.cpu().numpy(), mids.cpu().numpy()
+    ref = DonutRef64()
+    thr = np.array([300.0, 75.0, 100.0])
+    near = 0
+    pos = 0
+    for i, clip in enumerate(d.cpu().numpy()):
+        label, rm, sums = ref.classify_main(clip)
+        pos += label
+        assert int(gd[i, 0]) == len(rm), "clip %d: %d midpoints, reference %d" % (i, int(gd[i, 0]), len(rm))
+        k = min(len(rm), dsp_b200.DONUT_MAX_MID)
+        assert np.allclose(gm[i, :k], rm[:k], rtol=0, atol=1e-6) and np.isnan(gm[i, k:]).all()
+        if sums:
+            last = np.array(sums[-1])
+            assert np.abs(gd[i, 1:] - last).max() <= 1e-3, "clip %d: band sums %s vs reference %s" % (i, gd[i, 1:], last)
+            margin = np.abs(np.array(sums) - thr).min()  # distance of any evaluated sum to its verdict threshold
+            if margin <= 1e-3:
+                near += 1
+                continue
+        assert gl[i] == label, "clip %d: label %d, reference %d" % (i, gl[i], label)
+    assert near <= 2, "%d clips within 1e-3 of a verdict threshold" % near
+    assert 0.25 < pos / 768.0 < 0.75, "the f64 verdict must fire on a sizeable fraction (got %d of 768 calls)" % pos
+
+
+def test_f32_variant_on_call_clips_matches_unmodified_classify_with_margins():
+    """labels of the reference's own classify() on the call flavour (both verdicts, many band sums near the thresholds);
+    ADVICE r1: report the margin to the thresholds so "identical labels" is not luck -- the fused kernel sums the box
+    in double in warp order, the reference in float in cell order (classifier.cpp:418-430): they differ by ~1e-4"""
+    import dsp_b200
+    from donut_lib import DonutPort, DonutRef32, have_ref
+    assert have_ref(), "oracle/_ref not shipped"
+    sj = _ctx()
+    d = _synth_calls(sj, 6000, 512)
+    clips = d.cpu().numpy()
+    gl, gd = _gpu(sj, d, dsp_b200.DONUT_SYNC_F32)
+    r = DonutRef32()
+    ref = np.array([r.classify(c) for c in clips], np.int32)
+    ol, od = DonutPort("f32").classify_batch(clips, variant=1)
+    assert np.array_equal(ol, ref), "port differs from the unmodified classify()"
+    has = od[:, 0] > 0
+    margin = np.abs(od[has, 1:] - np.array([200.0, 100.0, 80.0])).min(axis=1)
+    tight = has.copy()
+    tight[has] = margin <= 1e-2
+    assert np.array_equal(gl[~tight], ref[~tight]), "labels differ on %d clips" % (gl[~tight] != ref[~tight]).sum()
+    assert tight.sum() <= 5
+    assert np.abs(gd[has, 1:] - od[has, 1:]).max() <= 0.01
+    assert 0.2 < ref.mean() < 0.8
+    print("call clips: %d positive of %d, smallest margin to a verdict threshold %.4f, %d within 0.01"
+          % (ref.sum(), ref.size, margin.min(), tight.sum()))

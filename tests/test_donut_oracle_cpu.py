@@ -65,3 +65,24 @@ def test_port_against_live_reference():
 def test_short_clip_is_rejected():
     labels, detail = DonutPort("f64").classify_batch(np.zeros((2, 100), np.float32), variant=0)
     assert labels.tolist() == [0, 0] and detail[:, 0].tolist() == [0, 0]
+
+
+def test_port_f64_verdict_pinned_to_the_unmodified_reference_functions():
+    """The f64 verdict, one step closer than midpoint counts: the per-file body of main (classifier.c:84-198) driven
+    through the UNMODIFIED butter_bandpass_filter / compute_spectrogram / find_midpoints / sum_intense of
+    oracle/_ref/libdonut_ref_f64.so (DonutRef64.classify_main) against the port, on "call"-flavoured synthetic clips
+    where the desktop variant says 1 on a sizeable fraction (the mixed flavour never does) and on mixed clips."""
+    from donut_lib import DonutPort, DonutRef64, have_ref
+    from synth_np import synth_clips
+    assert have_ref(), "oracle/_ref missing: run `make -C oracle` where /root/reference exists"
+    clips = np.concatenate([synth_clips(300, 192, 16000, flavour=1), synth_clips(300, 64, 16000, flavour=0)])
+    ref, port = DonutRef64(), DonutPort("f64")
+    pl, pd = port.classify_batch(clips, 0)
+    res = [ref.classify_main(c) for c in clips]
+    rl = np.array([r[0] for r in res], np.int32)
+    assert np.array_equal(pl, rl), "port labels differ from the reference-driven main on %d clips" % (pl != rl).sum()
+    assert 0.2 < rl[:192].mean() < 0.8, "the call flavour must give both f64 verdicts (got %.2f positive)" % rl[:192].mean()
+    for (label, mids, sums), d in zip(res, pd):
+        assert len(mids) == int(d[0])
+        if sums:
+            assert np.abs(np.array(sums[-1]) - d[1:]).max() <= 1e-4 * max(1.0, np.abs(d[1:]).max())

@@ -95,7 +95,7 @@ def test_slaney_bank_against_an_independent_implementation(oracle):
     frequencies.  aubio keeps the toolbox's constants (13 linear filters from 133.33 Hz, then a ratio of 1.0711703, which
     puts the knee at 999.8 Hz), librosa's scale has its knee at exactly 1000 Hz, so centres differ by up to ~0.2 Hz and
     weights by a few 1e-5; what must agree exactly is the structure: which bins each filter touches."""
-    ta = pytest.importorskip("torchaudio")
+    import torchaudio as ta  # mandatory (ADVICE r1): a missing second opinion must fail, not skip
     fb = oracle.fbank()
     lo = 133.3333
     top = (lo + 12 * 66.66666666) * 1.0711703 ** 29  # upper edge of filter 39

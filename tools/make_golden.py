@@ -61,21 +61,26 @@ def slaney_dense(sr, nfft=2048):
     return fb
 
 
-def mfcc_stats_np(x, sr):
+def mfcc_stats_np(x, sr, symmetric_window=False, power=False, log_floor=2e-42, dct_ortho=True):
+    """independent float64 restatement (np.fft.rfft, scipy dct) of aubio pvoc + mfcc and of the statistics of
+    cepstrum/scrubjay_infer.c:36-67; the keyword arguments are the switches of scrubjay_cepstrum_params"""
     from scipy.fft import dct
     x = np.asarray(x, np.float64)
     n = x.size
     frames = (n + 1023) // 1024
-    w = (0.5 * (1 - np.cos(2 * np.pi * np.arange(2048) / 2048))).astype(np.float32).astype(np.float64)
+    den = 2047 if symmetric_window else 2048
+    w = (0.5 * (1 - np.cos(2 * np.pi * np.arange(2048) / den))).astype(np.float32).astype(np.float64)
     fb = slaney_dense(sr).astype(np.float64)
     xp = np.concatenate([np.zeros(1024), x, np.zeros(frames * 1024 - n)])
     out = []
     for t in range(frames):
         mag = np.abs(np.fft.rfft(xp[t * 1024:t * 1024 + 2048] * w)).astype(np.float32).astype(np.float64)
+        if power:
+            mag = (mag.astype(np.float32) * mag.astype(np.float32)).astype(np.float64)
         e = (fb @ mag).astype(np.float32)
-        e = np.maximum(e, np.float32(2e-42))
+        e = np.maximum(e, np.float32(log_floor))
         lg = np.log10(e.astype(np.float64)).astype(np.float32)
-        out.append(dct(lg.astype(np.float64), type=2, norm="ortho")[:20].astype(np.float32))
+        out.append(dct(lg.astype(np.float64), type=2, norm="ortho" if dct_ortho else None)[:20].astype(np.float32))
     fr = np.array(out, np.float32)
     v = fr.astype(np.float64)
     mean = v.sum(0) / frames
