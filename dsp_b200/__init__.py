@@ -75,6 +75,7 @@ def load_library():
     L.scrubjay_infer_batch_gather_dev.argtypes = [vp, vp, c_long, c_int, vp, vp]
     L.scrubjay_infer_batch_pcm16.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_wav_parse.argtypes = [vp, ctypes.c_size_t, vp]
+    L.scrubjay_wav_parse_ex.argtypes = [vp, ctypes.c_size_t, vp, c_int]
     L.scrubjay_decode_pcm16_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
     L.scrubjay_decode_adc12_dev.argtypes = [vp, vp, c_long, vp]
     L.scrubjay_upsample_linear_dev.argtypes = [vp, vp, c_long, c_int, c_int, vp]
@@ -465,12 +466,13 @@ class WavInfo(ctypes.Structure):
                 ("frames", ctypes.c_int64)]
 
 
-def wav_parse(data):
-    """scrubjay_wav_parse over a bytes object (host only, no GPU): WavInfo, or None if the reference's
-    read_wav_file would reject the file"""
+def wav_parse(data, strict=True):
+    """scrubjay_wav_parse(_ex) over a bytes object (host only, no GPU): WavInfo, or None if the reference's
+    read_wav_file would reject the file (strict) / if no fmt + data chunk pair is found (strict=False: chunks in front
+    of "fmt " are skipped like libsndfile / aubio_source do)"""
     buf = bytes(data)
     info = WavInfo()
-    rc = load_library().scrubjay_wav_parse(buf, len(buf), ctypes.byref(info))
+    rc = load_library().scrubjay_wav_parse_ex(buf, len(buf), ctypes.byref(info), 1 if strict else 0)
     return info if rc == 0 else None
 
 

@@ -25,6 +25,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "donut_kernel.h"
 #include "sj_pk.h"
@@ -69,6 +70,18 @@ __device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(
 
 __device__ __forceinline__ void fft32(float2 (&v)[32]) { sj_fft32(v); }
 __device__ __forceinline__ void fft32(double2 (&v)[32]) { sj_fft32d(v); }
+
+// 4- / 8-byte asynchronous copy global -> shared (LDGSTS): the band-sum epilogue stages a whole box of PSD cells with
+// one round trip to L2 / DRAM instead of one dependent load per 32 cells
+__device__ __forceinline__ void cp_async_elem(float *dst, const float *src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_elem(double *dst, const double *src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // dB value exactly as the reference forms it: (T)(10 * log10((double)s / 1e-12))
 template <typename T> __device__ __forceinline__ T to_db(T s) { return (T)(10.0 * log10((double)s / 1e-12)); }
@@ -570,6 +583,9 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                 }
                 const T *scr = scratch + size_t(c2) * tb * DN_BINS;
                 T *qu = st->queue[warp];
+                // staging area of the box cells: this warp's transpose buffer (idle during the epilogue)
+                T *stage = reinterpret_cast<T *>(st->xbuf[warp]);
+                constexpr int kStage = (int)(sizeof(st->xbuf[0]) / sizeof(T)) / 32 * 32;
                 auto box = [&](int band, T half, T midpoint) -> T {
                     const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
                     // time index search exactly as sum_intense (classifier.c:619-640), evaluated lane-parallel:
@@ -589,18 +605,29 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
                     const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
                     int nq = 0; // queued cells (warp-uniform)
                     // cell c = c0 + lane sits at (frame j, bin i) = (c / nf, c % nf): one division per box, then the pair
-                    // advances by 32 cells per round
+                    // advances by 32 cells per round.  The whole box (<= 41 x 27 cells) is first staged in shared memory
+                    // by asynchronous copies -- one round trip to L2 for the box instead of one per 32 cells (the dependent
+                    // loads of this loop held 20 % of the transform warps' time, profiles/r2c) -- in chunks of kStage cells.
                     const int q32 = 32 / nf, r32 = 32 - q32 * nf;
                     int cj = lane / nf, ci = lane - cj * nf;
-                    // the cell of the next round is requested before this round's is tested (the scratch sits in L2)
-                    T av_next = lane < ncell ? scr[(t0 + cj) * DN_BINS + f0 + ci] : (T)0;
                     for (int c0 = 0; c0 < ncell; c0 += 32) {
+                        if (c0 % kStage == 0) {
+                            __syncwarp();
+                            int sj = cj, si = ci;
+                            for (int c = c0 + lane; c < ncell && c < c0 + kStage; c += 32) {
+                                cp_async_elem(stage + (c - c0), scr + (t0 + sj) * DN_BINS + f0 + si);
+                                si += r32;
+                                sj += q32;
+                                if (si >= nf) { si -= nf; ++sj; }
+                            }
+                            cp_async_wait_all();
+                            __syncwarp();
+                        }
                         const int c = c0 + lane;
-                        const T av = av_next;
+                        const T av = c < ncell ? stage[c % kStage] : (T)0;
                         ci += r32;
                         cj += q32;
                         if (ci >= nf) { ci -= nf; ++cj; }
-                        av_next = c + 32 < ncell ? scr[(t0 + cj) * DN_BINS + f0 + ci] : (T)0;
                         const bool pass = c < ncell && av >= a_lo && av < a_hi;
                         const unsigned bal = __ballot_sync(kFull, pass);
                         if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
@@ -644,12 +671,506 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
     }
 }
 
+
+// ================================================================================================
+// Warp-specialised float kernel (round 2).  One persistent CTA per SM: kIir "filter" warps and kFft
+// "transform" warps, coupled by named barriers only -- no CTA-wide barrier in the steady state.
+//   * A filter warp owns a group of 16 clips = 32 (clip, filter) rows, one direct-form-II recurrence per
+//     lane in the reference's exact operation order (iir8: bit-identical samples, classifier.cpp:193-219).
+//     One filter warp sits on each of the SM's four schedulers: measured on B200, a lone warp issues FP32
+//     instructions at one per 2 cycles (packed f32x2: one per 4), so a recurrence step costs ~50 cycles of
+//     its scheduler whatever it does -- four independent groups in flight is what fills the four FP32 pipes,
+//     and the other half of each pipe goes to the transform warps.  (A first version with both filters of
+//     a clip packed in one lane -- 13 cross-filter FMUL2 + two scalar chains -- needed 107 cycles per step
+//     on two warps and lost to the round-1 kernel: 4.85 M against 5.8 M clips/s.)
+//   * The warp writes one spectrogram hop (224 new samples per row) into circular 256-sample rows
+//     (row = filter * 16 + clip, stride 258 floats: the warp's 64-bit column stores and the 16-float row
+//     reads of two half-warps eight rows apart are bank-conflict-free), signals "full", and waits for
+//     "empty" before the next hop; the four groups drift out of phase, so the transform warps always have a
+//     frame to work on and a filter warp's idle time is the transform time of its own frame only.
+//   * The transform warps replay PlainFFT's butterfly network on 2 rows per pass (16 lanes per frame,
+//     exactly the arithmetic of spectrogram_column_exact_f32); a pass holds two rows of the SAME kind
+//     (two flag rows or two band rows), so the per-cell bookkeeping is specialised per kind instead of
+//     carried twice with selects; passes are handed out through a shared-memory counter.  After a group's
+//     last frame the transform warps run the clustering / band-sum epilogue for its clips and release it.
+namespace ws {
+
+#ifndef SJ_DONUT_IIR_WARPS
+#define SJ_DONUT_IIR_WARPS 4
+#endif
+constexpr int kIir = SJ_DONUT_IIR_WARPS; // filter warps = clip groups in flight per CTA
+#ifndef SJ_DONUT_FFT_WARPS
+#define SJ_DONUT_FFT_WARPS 8 /* measured (100 k clips): 8 warps 6.21 M clips/s (168 registers, no spill), 10: 6.04 M, 12: 6.03 M (128 registers) */
+#endif
+constexpr int kFft = SJ_DONUT_FFT_WARPS; // transform / epilogue warps
+constexpr int kGroup = 16;         // clips per group (32 rows: lane = filter * 16 + clip)
+constexpr int kPasses = 2 * kGroup / 2; // passes per group frame: two rows each
+constexpr int kRS = 258;           // row stride in floats
+constexpr int kThreads = (kIir + kFft) * 32;
+constexpr int kBarFull = 1, kBarEmpty = 1 + kIir, kBarFft = 1 + 2 * kIir; // named barriers (0 = __syncthreads)
+static_assert(kBarFft < 16, "named barriers");
+
+struct GroupState {
+    float mean[2 * kGroup];                                       // per row: frame mean, summed sequentially like the reference
+    float min_in[kGroup], max_in[kGroup], min_ed[kGroup], max_ed[kGroup]; // band rows: min / max of a over the cells with Sxx > 0
+    uint32_t flags[kGroup][3];                                    // flag rows: frames with any cell above the dB threshold
+    int next_pass;                                                // passes of the current frame handed out so far (transform warps grab them)
+    int n_mid[kGroup];
+    float mids[kGroup][DN_MAX_MID];
+};
+struct FftWarpState {
+    float2 xbuf[2][16 * 17]; // 16x16 transpose buffers of the exact float FFT (two frames per pass)
+    float queue[64];         // band-sum epilogue: a values of the cells that passed the level test
+};
+
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+constexpr size_t kTabBytes = (sizeof(SjDonutTables<float>) + 15) & ~size_t(15);
+constexpr size_t kSmem = kTabBytes + sizeof(float) * kIir * 2 * kGroup * kRS + sizeof(GroupState) * kIir + sizeof(FftWarpState) * kFft;
+
+// one pass = spectrogram column t of two rows of one kind (BAND: 3000-7500 Hz rows whose cells are kept; otherwise the
+// 1000-3000 Hz rows that only flag frames), the clips c0 and c0 + 8 of the group; PlainFFT replayed as in
+// spectrogram_column_exact_f32
+template <bool BAND>
+__device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
+                                               GroupState *st, FftWarpState *fw, float *scratch, int lane, int c0)
+{
+    const int half = lane >> 4, h = lane & 15;
+    const int clip = c0 + 8 * half, r = (BAND ? kGroup : 0) + clip;
+    float2 *xb = fw->xbuf[half];
+    const float *rowp = rows + r * kRS;
+    const float mean = st->mean[r];
+    float2 v[16];
+    const int hb = brev4(h);
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+        const int n = 16 * brev4(rr) + hb;
+        const float x = rowp[(pos + n) & 255];
+        v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+        const float t1 = v[i + 1].x;
+        v[i + 1].x = sub_rn(v[i].x, t1);
+        v[i].x = add_rn(v[i].x, t1);
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i += 4) {
+        const float t1 = v[i + 2].x; // twiddle (1, 0)
+        v[i + 2].x = sub_rn(v[i].x, t1);
+        v[i].x = add_rn(v[i].x, t1);
+        const float t2 = v[i + 3].x; // twiddle (0, -1): t = (hi.y, -hi.x) = (0, -t2)
+        v[i + 3] = make_float2(v[i + 1].x, t2);
+        v[i + 1].y = -t2;
+    }
+#pragma unroll
+    for (int l = 2; l < 4; ++l) {
+        const int l1 = 1 << l;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if ((i & l1) == 0) bfly(v[i], v[i + l1], tab->bourke[l1 - 1 + (i & (l1 - 1))][0], tab->bourke[l1 - 1 + (i & (l1 - 1))][1]);
+    }
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) xb[h * 17 + rr] = v[rr];
+    __syncwarp();
+#pragma unroll
+    for (int hh = 0; hh < 16; ++hh) v[hh] = xb[hh * 17 + h];
+    __syncwarp();
+#pragma unroll
+    for (int l = 4; l < 8; ++l) {
+        const int l1h = 1 << (l - 4), l1 = 16 << (l - 4);
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if ((i & l1h) == 0) {
+                const int m = (i & (l1h - 1)) * 16 + h;
+                bfly(v[i], v[i + l1h], tab->bourke[l1 - 1 + m][0], tab->bourke[l1 - 1 + m][1]);
+            }
+    }
+    // a = re^2 + im^2 of bins k = 16 hh + h <= 128 with the reference's operations (classifier.cpp:349-364); "/ U" and "* 2"
+    // are applied later, only where a value is needed; the tests on Sxx use exact thresholds on a
+    if (BAND) {
+        float *cell = scratch + (size_t(clip) * tb + t) * DN_BINS;
+        const float a_pos = tab->a_pos;
+        float lmin = INFINITY, lmax = 0.f, emin = INFINITY, emax = 0.f;
+#pragma unroll
+        for (int hh = 0; hh < 9; ++hh) {
+            if (hh < 8 || h == 0) {
+                const float av = add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y));
+                cell[16 * hh + h] = av;
+                const bool posv = av >= a_pos;
+                const float vmin = posv ? av : INFINITY, vmax = posv ? av : 0.f;
+                if (hh == 0 || hh == 8) { // bins 0 and 128 (lane h == 0) are the edge cells
+                    const bool edge = h == 0;
+                    emin = fminf(emin, edge ? vmin : INFINITY);
+                    emax = fmaxf(emax, edge ? vmax : 0.f);
+                    lmin = fminf(lmin, edge ? INFINITY : vmin);
+                    lmax = fmaxf(lmax, edge ? 0.f : vmax);
+                } else {
+                    lmin = fminf(lmin, vmin);
+                    lmax = fmaxf(lmax, vmax);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+            lmin = fminf(lmin, __shfl_xor_sync(kFull, lmin, o));
+            lmax = fmaxf(lmax, __shfl_xor_sync(kFull, lmax, o));
+        }
+        if (h == 0) {
+            st->min_in[clip] = fminf(st->min_in[clip], lmin);
+            st->max_in[clip] = fmaxf(st->max_in[clip], lmax);
+            st->min_ed[clip] = fminf(st->min_ed[clip], emin); // the edge bins live in lane h == 0 only
+            st->max_ed[clip] = fmaxf(st->max_ed[clip], emax);
+        }
+    } else {
+        float imax = 0.f, xmax = 0.f; // largest a over the inner / the edge cells (any(a >= thr) = max(a) >= thr)
+#pragma unroll
+        for (int hh = 0; hh < 9; ++hh) {
+            if (hh < 8 || h == 0) {
+                const float av = add_rn(mul_rn(v[hh].x, v[hh].x), mul_rn(v[hh].y, v[hh].y));
+                if (hh == 0 || hh == 8) {
+                    const bool edge = h == 0;
+                    xmax = fmaxf(xmax, edge ? av : 0.f);
+                    imax = fmaxf(imax, edge ? 0.f : av);
+                } else imax = fmaxf(imax, av);
+            }
+        }
+        const bool any = imax >= tab->a_thr[1] || xmax >= tab->a_thr[0];
+        const unsigned ballot = __ballot_sync(kFull, any);
+        if (h == 0 && ((ballot >> (16 * half)) & 0xFFFFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
+    }
+}
+
+template <bool ALIGNED>
+__global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs a)
+{
+    typedef float T;
+    extern __shared__ __align__(16) unsigned char smem[];
+    SjDonutTables<float> *tab = reinterpret_cast<SjDonutTables<float> *>(smem);
+    float *rows_all = reinterpret_cast<float *>(smem + kTabBytes);
+    GroupState *gs_all = reinterpret_cast<GroupState *>(rows_all + kIir * 2 * kGroup * kRS);
+    FftWarpState *fw_all = reinterpret_cast<FftWarpState *>(gs_all + kIir);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
+        for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<float>) / 4); i += kThreads) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 32, fewer for small batches
+    const long n_groups = (a.n_clips + cpg - 1) / cpg;
+    constexpr int kPair = 32 + 32 * kFft; // threads of a full / empty barrier: one filter warp + the transform warps
+
+    // the filter warps take the HIGHEST warp ids: the SM's warp arbiter favours high ids, and the recurrence is the
+    // latency-critical chain (a transform warp that loses a slot loses nothing)
+    if (warp >= kFft) {
+        // ------------------------------------------------------------------ filter warp: group q = g, g + kIir, ...
+        const int g = warp - kFft;
+        float *rows = rows_all + g * 2 * kGroup * kRS;
+        GroupState *st = gs_all + g;
+        const int f = lane >> 4, ci = lane & 15; // row = lane = filter * 16 + clip
+        float ca[9], cb[9];
+#pragma unroll
+        for (int j = 0; j < 9; ++j) { ca[j] = tab->a[f][j]; cb[j] = tab->b[f][j]; }
+        float *myrow = rows + lane * kRS;
+        for (long q = g;; q += kIir) {
+            const long gid = blockIdx.x + q * gridDim.x;
+            if (gid >= n_groups) break;
+            const long base = gid * cpg;
+            const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
+            const long clip = base + (ci < nact ? ci : nact - 1); // idle lanes shadow the group's last clip
+            const float *src = a.clips_per_row > 0
+                                   ? a.clips + (clip / a.clips_per_row) * a.row_stride + (clip % a.clips_per_row) * (long)n_samples
+                                   : a.clips + clip * (long)n_samples;
+            float w[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = 0.f;
+            if (lane < kGroup) {
+                st->min_in[lane] = st->min_ed[lane] = INFINITY;
+                st->max_in[lane] = st->max_ed[lane] = 0.f;
+                st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
+            }
+#ifndef SJ_DONUT_PRE
+#define SJ_DONUT_PRE 4
+#endif
+            constexpr int kPre = SJ_DONUT_PRE; // register ring of kPre blocks of 8 samples, requested kPre blocks ahead
+            float4 ring[kPre][2];
+#pragma unroll
+            for (int j = 0; j < kPre; ++j) {
+                ring[j][0] = ring[j][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ALIGNED) { // tb >= 1 guarantees 256 samples
+                    ring[j][0] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j));
+                    ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j + 4));
+                }
+            }
+            float acc_cur = 0.f, acc_next = 0.f;
+            int pos = 0, sample = 0;
+            for (int t = 0; t < tb; ++t) {
+                if (t > 0) bar_sync(kBarEmpty + g, kPair); // the transform warps are done with frame t - 1
+                const int nnew = t == 0 ? DN_WIN : DN_HOP;
+                for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) {
+#pragma unroll
+                    for (int j = 0; j < kPre; ++j) {
+                        const int i = i0 + 8 * j;
+                        float x[8], y[8];
+                        if (ALIGNED) {
+                            const float4 u0 = ring[j][0], u1 = ring[j][1];
+                            x[0] = u0.x; x[1] = u0.y; x[2] = u0.z; x[3] = u0.w; x[4] = u1.x; x[5] = u1.y; x[6] = u1.z; x[7] = u1.w;
+                            if (sample + i + 8 * kPre + 8 <= n_samples) {
+                                ring[j][0] = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8 * kPre));
+                                ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + sample + i + 8 * kPre + 4));
+                            }
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) x[k] = __ldg(src + sample + i + k);
+                        }
+#ifdef SJ_DONUT_SKIP_IIR /* timing experiment only: results are wrong */
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) y[k] = x[k];
+#else
+                        iir8(x, w, ca, cb, y); // the packed overload: (a[j] w, b[j] w) from one FMUL2 for even j
+#endif
+                        // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
+                        const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            acc_cur = add_rn(acc_cur, y[k]);
+                            if (tail) acc_next = add_rn(acc_next, y[k]);
+                        }
+                        float *dst = myrow + ((pos + i) & 255);
+#pragma unroll
+                        for (int k = 0; k < 8; k += 2) *reinterpret_cast<float2 *>(dst + k) = make_float2(y[k], y[k + 1]);
+                    }
+                }
+                sample += nnew;
+                pos = (pos + nnew) & 255;
+                st->mean[lane] = div_rn(acc_cur, (float)DN_WIN);
+                if (lane == 0) st->next_pass = 0;
+                acc_cur = acc_next;
+                acc_next = 0.f;
+                __threadfence_block();
+                bar_arrive(kBarFull + g, kPair);
+            }
+            bar_sync(kBarEmpty + g, kPair); // the group's epilogue is done: rows and state are free again
+        }
+    } else {
+        // ------------------------------------------------------------------ transform warps
+        const int w = warp;
+        FftWarpState *fw = fw_all + w;
+        const float U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
+        for (long r = 0;; ++r) {
+            if (blockIdx.x + r * kIir * gridDim.x >= n_groups) break;
+            for (int t = 0; t < tb; ++t) {
+                const int pos = (DN_HOP * t) & 255; // offset of the frame's first sample in the circular rows
+#pragma unroll 1
+                for (int g = 0; g < kIir; ++g) {
+                    const long gid = blockIdx.x + (r * kIir + g) * gridDim.x;
+                    if (gid >= n_groups) break;
+                    const long base = gid * cpg;
+                    const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
+                    const float *rows = rows_all + g * 2 * kGroup * kRS;
+                    GroupState *st = gs_all + g;
+                    float *scratch = reinterpret_cast<float *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
+                    bar_sync(kBarFull + g, kPair);
+                    // 16 passes: p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8
+                    // (handed out through a counter, so any number of transform warps shares them evenly)
+                    for (;;) {
+                        int p = 0;
+                        if (lane == 0) p = atomicAdd(&st->next_pass, 1);
+                        p = __shfl_sync(kFull, p, 0);
+                        if (p >= kPasses) break;
+                        const int c0 = p & 7;
+                        if (c0 >= nact) continue;
+#ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
+                        continue;
+#endif
+                        if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0);
+                        else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0);
+                    }
+                    if (t < tb - 1) {
+                        __threadfence_block();
+                        bar_arrive(kBarEmpty + g, kPair);
+                        continue;
+                    }
+                    // ---- the group's last frame: epilogue for its clips, then release the group
+                    __threadfence_block();
+                    bar_sync(kBarFft, 32 * kFft); // every pass of the frame has been accounted for
+                    // epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
+                    {
+                        const int c = w + kFft * lane;
+                        if (c < nact) {
+                            const uint32_t *fl = st->flags[c];
+                            const T tol = tab->gap_tol, mind = tab->min_dur;
+                            int count = 0, size = 0;
+                            T first = 0, last = 0, tsum = 0;
+                            for (int j = 0; j <= tb; ++j) {
+                                const bool on = j < tb && ((fl[j >> 5] >> (j & 31)) & 1u);
+                                const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                                const bool joins = on && size > 0 && sub_rn(tj, last) <= tol;
+                                if (size > 0 && (!on ? j == tb : !joins)) {
+                                    if (sub_rn(last, first) >= mind) {
+                                        if (count < DN_MAX_MID) st->mids[c][count] = div_rn(tsum, (T)size);
+                                        ++count;
+                                    }
+                                    size = 0;
+                                }
+                                if (on) {
+                                    if (size == 0) { first = tj; tsum = 0; }
+                                    tsum = add_rn(tsum, tj);
+                                    last = tj;
+                                    ++size;
+                                }
+                            }
+                            st->n_mid[c] = count;
+                        }
+                    }
+                    __syncwarp();
+                    // epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip (see donut_kernel)
+                    for (int c2 = w; c2 < nact; c2 += kFft) {
+                        const int nm = st->n_mid[c2];
+                        int label = 0;
+                        T s_above = 0, s_mid = 0, s_below = 0;
+                        if (nm > 0) {
+                            T smin = (T)INFINITY, smax = 0;
+                            if (st->max_in[c2] > 0) { smin = mul_rn(div_rn(st->min_in[c2], U), (T)2); smax = mul_rn(div_rn(st->max_in[c2], U), (T)2); }
+                            if (st->max_ed[c2] > 0) {
+                                const T e0 = div_rn(st->min_ed[c2], U), e1 = div_rn(st->max_ed[c2], U);
+                                smin = e0 < smin ? e0 : smin;
+                                smax = e1 > smax ? e1 : smax;
+                            }
+                            const T mn = to_db<T>(smin), mx = to_db<T>(smax);
+                            const T range = sub_rn(mx, mn), lo = tab->lo_norm, hi = tab->hi_norm;
+                            auto level = [&](T av) -> T {
+                                const T sv = mul_rn(div_rn(av, U), (T)2);
+                                return div_rn(sub_rn(to_db<T>(sv), mn), range);
+                            };
+                            const T amax = st->max_in[c2];
+                            auto first_true = [&](auto pred) -> T {
+                                typedef typename Bits<T>::type UI;
+                                UI blo = Bits<T>::of(a_pos), bhi = Bits<T>::of(amax);
+                                if (!(amax >= a_pos) || !pred(amax)) return (T)INFINITY;
+                                while (blo < bhi) {
+                                    const UI step = (bhi - blo) / 32 + 1;
+                                    UI cand = blo + step * (UI)(lane + 1) - 1;
+                                    if (cand > bhi || cand < blo) cand = bhi;
+                                    const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(cand)));
+                                    const int first = __ffs(bal) - 1;
+                                    const UI at = Bits<T>::shfl(cand, first), before = Bits<T>::shfl(cand, first > 0 ? first - 1 : 0);
+                                    bhi = at;
+                                    if (first > 0) blo = before + 1;
+                                }
+                                return Bits<T>::from(bhi);
+                            };
+                            T a_lo = (T)INFINITY, a_hi = (T)INFINITY;
+                            if (range > 0) {
+                                a_lo = first_true([&](T av) { return level(av) > lo; });
+                                a_hi = first_true([&](T av) { return !(level(av) < hi); });
+                            }
+                            const T *scr = scratch + size_t(c2) * tb * DN_BINS;
+                            T *qu = fw->queue;
+                            T *stage = reinterpret_cast<T *>(fw->xbuf); // the warp's transpose buffers are idle in the epilogue
+                            constexpr int kStage = (int)(sizeof(fw->xbuf) / sizeof(T)) / 32 * 32;
+                            auto box = [&](int band, T halfw, T midpoint) -> T {
+                                const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
+                                const T tlo = sub_rn(midpoint, halfw), thi = add_rn(midpoint, halfw);
+                                int nb = 0, na = 0;
+                                for (int j = lane; j < DN_MAX_TB; j += 32) {
+                                    const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                                    nb += __popc(__ballot_sync(kFull, j < tb && tj < tlo));
+                                    na += __popc(__ballot_sync(kFull, j < tb && tj > thi));
+                                }
+                                int t0 = nb, t1 = tb - 1 - na;
+                                if (t0 >= tb) t0 = tb - 1;
+                                if (t1 < 0) t1 = 0;
+                                if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
+                                double acc = 0.0;
+                                const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
+                                int nq = 0;
+                                // the box is staged in shared memory by asynchronous copies first (see donut_kernel)
+                                const int q32 = 32 / nf, r32 = 32 - q32 * nf;
+                                int cj = lane / nf, ci = lane - cj * nf;
+                                for (int cc = 0; cc < ncell; cc += 32) {
+                                    if (cc % kStage == 0) {
+                                        __syncwarp();
+                                        int sj = cj, si = ci;
+                                        for (int c = cc + lane; c < ncell && c < cc + kStage; c += 32) {
+                                            cp_async_elem(stage + (c - cc), scr + (t0 + sj) * DN_BINS + f0 + si);
+                                            si += r32;
+                                            sj += q32;
+                                            if (si >= nf) { si -= nf; ++sj; }
+                                        }
+                                        cp_async_wait_all();
+                                        __syncwarp();
+                                    }
+                                    const int c = cc + lane;
+                                    const T av = c < ncell ? stage[c % kStage] : (T)0;
+                                    ci += r32;
+                                    cj += q32;
+                                    if (ci >= nf) { ci -= nf; ++cj; }
+                                    const bool pass = c < ncell && av >= a_lo && av < a_hi;
+                                    const unsigned bal = __ballot_sync(kFull, pass);
+                                    if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
+                                    nq += __popc(bal);
+                                    __syncwarp();
+                                    if (nq >= 32) {
+                                        acc += (double)level(qu[lane]);
+                                        nq -= 32;
+                                        __syncwarp();
+                                        if (lane < nq) qu[lane] = qu[32 + lane];
+                                        __syncwarp();
+                                    }
+                                }
+                                if (lane < nq) acc += (double)level(qu[lane]);
+                                __syncwarp();
+#pragma unroll
+                                for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+                                return (T)acc;
+                            };
+                            const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
+                            for (int m = 0; m < cap; ++m) {
+                                const T mp = st->mids[c2][m];
+                                s_above = box(0, (T)0.18, mp);
+                                s_mid = box(1, (T)0.05, mp);
+                                s_below = box(2, (T)0.18, mp);
+                                if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
+                            }
+                        }
+                        if (lane == 0) {
+                            if (a.labels) a.labels[base + c2] = label;
+                            if (a.track) a.track[base + c2] = (int8_t)(label + 1);
+                            if (a.detail) {
+                                float *d = a.detail + (base + c2) * 4;
+                                d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
+                            }
+                        }
+                        if (a.mids && lane < DN_MAX_MID)
+                            a.mids[(base + c2) * DN_MAX_MID + lane] = lane < nm ? (float)st->mids[c2][lane] : __int_as_float(0x7fc00000);
+                    }
+                    __threadfence_block();
+                    bar_arrive(kBarEmpty + g, kPair);
+                }
+            }
+        }
+    }
+}
+
+} // namespace ws
+
 template <typename T> size_t smem_total()
 {
     return ((sizeof(SjDonutTables<T>) + 15) & ~size_t(15)) + sizeof(T) * 32 * kRow + sizeof(RowState<T>);
 }
 
 } // namespace
+
+// A/B switch: SCRUBJAY_DONUT_LEGACY=1 keeps the round-1 float kernel (CTA-wide barriers, warp 0 filters alone)
+bool sj_donut_legacy_f32()
+{
+    static const bool legacy = [] { const char *e = getenv("SCRUBJAY_DONUT_LEGACY"); return e && e[0] == '1'; }();
+    return legacy;
+}
 
 cudaError_t sj_donut_setup()
 {
@@ -660,11 +1181,14 @@ cudaError_t sj_donut_setup()
     SJ_DN_ATTR(float, true, false); SJ_DN_ATTR(float, false, false); SJ_DN_ATTR(float, true, true); SJ_DN_ATTR(float, false, true);
     SJ_DN_ATTR(double, true, false); SJ_DN_ATTR(double, false, false); SJ_DN_ATTR(double, true, true); SJ_DN_ATTR(double, false, true);
 #undef SJ_DN_ATTR
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::donut_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::kSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::donut_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::kSmem);
     return e;
 }
 
 int sj_donut_grid(int num_sms, bool f64)
 {
+    if (!f64 && !sj_donut_legacy_f32()) return num_sms; // warp-specialised float kernel: one persistent CTA per SM
     int per_sm = 0;
     if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true, false>, DnWarps<double>::value * 32, smem_total<double>());
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true, false>, DnWarps<float>::value * 32, smem_total<float>());
@@ -674,6 +1198,7 @@ int sj_donut_grid(int num_sms, bool f64)
 
 size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
 {
+    if (!f64 && !sj_donut_legacy_f32()) return size_t(ws::kIir) * ws::kGroup * tb * DN_BINS * 4;
     return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
 }
 
@@ -681,6 +1206,20 @@ cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int grid, cudaStr
 {
     if (a_in.n_clips <= 0) return cudaSuccess;
     SjDonutArgs a = a_in;
+    if (!f64 && !sj_donut_legacy_f32()) {
+        // groups of up to 32 clips, two in flight per CTA; small batches are spread over the CTAs in smaller groups
+        long cpg = (a.n_clips + (long)grid * ws::kIir - 1) / ((long)grid * ws::kIir);
+        if (cpg > ws::kGroup) cpg = ws::kGroup;
+        if (cpg < 1) cpg = 1;
+        a.clips_per_cta = (int)cpg;
+        const long groups = (a.n_clips + cpg - 1) / cpg;
+        if (groups < grid) grid = (int)groups;
+        const bool al = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
+                        (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
+        if (al) ws::donut_ws_kernel<true><<<grid, ws::kThreads, ws::kSmem, stream>>>(a);
+        else ws::donut_ws_kernel<false><<<grid, ws::kThreads, ws::kSmem, stream>>>(a);
+        return cudaGetLastError();
+    }
     long cpc = (a.n_clips + grid - 1) / grid; // spread small batches over the resident CTAs
     if (cpc > DN_CLIPS_PER_WARP) cpc = DN_CLIPS_PER_WARP;
     if (cpc < 1) cpc = 1;

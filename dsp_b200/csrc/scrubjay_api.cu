@@ -453,23 +453,33 @@ int scrubjay_infer_batch_gather_dev(scrubjay_ctx *c, const float *d_clips, long 
                            c->d_peers);
 }
 
-int scrubjay_wav_parse(const void *bytes, size_t n, scrubjay_wav_info *info)
+int scrubjay_wav_parse(const void *bytes, size_t n, scrubjay_wav_info *info) { return scrubjay_wav_parse_ex(bytes, n, info, 1); }
+
+int scrubjay_wav_parse_ex(const void *bytes, size_t n, scrubjay_wav_info *info, int strict)
 {
     if (!bytes || !info) return SJ_EINVAL;
     const unsigned char *p = static_cast<const unsigned char *>(bytes);
     auto u16 = [&](size_t o) { return (uint32_t)p[o] | ((uint32_t)p[o + 1] << 8); };
     auto u32 = [&](size_t o) { return u16(o) | (u16(o + 2) << 16); };
     memset(info, 0, sizeof *info);
-    if (n < 36 || memcmp(p, "RIFF", 4) || memcmp(p + 8, "WAVE", 4) || memcmp(p + 12, "fmt ", 4)) return SJ_EINVAL;
-    const size_t fmt_size = u32(16);
-    info->audio_format = (int32_t)u16(20);
-    info->channels = (int32_t)u16(22);
-    info->sample_rate = (int32_t)u32(24);
-    info->bits_per_sample = (int32_t)u16(34);
+    if (n < 36 || memcmp(p, "RIFF", 4) || memcmp(p + 8, "WAVE", 4)) return SJ_EINVAL;
+    // strict: "fmt " must be the first chunk, as read_wav_file demands (classifier.c:248-253); otherwise chunks in
+    // front of it (JUNK, bext, LIST ...) are skipped the way libsndfile / aubio_source walk a RIFF file
+    size_t f = 12;
+    if (strict) { if (memcmp(p + f, "fmt ", 4)) return SJ_EINVAL; }
+    else {
+        while (f + 8 <= n && memcmp(p + f, "fmt ", 4)) f += 8 + (size_t)u32(f + 4) + (u32(f + 4) & 1);
+        if (f + 24 > n) return SJ_EINVAL;
+    }
+    const size_t fmt_size = u32(f + 4);
+    info->audio_format = (int32_t)u16(f + 8);
+    info->channels = (int32_t)u16(f + 10);
+    info->sample_rate = (int32_t)u32(f + 12);
+    info->bits_per_sample = (int32_t)u16(f + 22);
     if (info->audio_format != 1 || info->channels < 1 || info->bits_per_sample < 8) return SJ_EINVAL;
     // the reference reads 16 bytes of fmt and expects the next chunk header right after them; a longer fmt
     // chunk (fmt_size > 16) would make it misparse -- here the declared size is honoured
-    size_t o = 20 + (fmt_size < 16 ? 16 : fmt_size);
+    size_t o = f + 8 + (fmt_size < 16 ? 16 : fmt_size);
     o += fmt_size & 1;
     while (o + 8 <= n && memcmp(p + o, "data", 4)) o += 8 + (size_t)u32(o + 4) + (u32(o + 4) & 1);
     if (o + 8 > n) return SJ_EINVAL;

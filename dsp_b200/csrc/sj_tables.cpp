@@ -76,7 +76,9 @@ void sj_default_cepstrum_params(scrubjay_cepstrum_params *p)
 }
 
 // `wscale`: factor folded into the weights -- the untangling step leaves |X| doubled (0.5), |X|^2 quadrupled (0.25)
-static int build_mel(SjTables *t, unsigned samplerate, float wscale, char *err)
+// `allow_fast`: false forces the generic partial-sum layout (the specialised 16 kHz instantiation hard-codes the
+// in-register periodic Hann, |X| and the 2e-42 floor, so non-default parameters must not get its layout)
+static int build_mel(SjTables *t, unsigned samplerate, float wscale, bool allow_fast, char *err)
 {
     std::vector<float> fb((size_t)SJ_NFILT * SJ_NBINS);
     sj_dense_slaney(fb.data(), samplerate);
@@ -113,7 +115,7 @@ static int build_mel(SjTables *t, unsigned samplerate, float wscale, char *err)
     int ch = (hi - base + 1 + 31) / 32;
     ch = (ch + 3) & ~3;
     if (ch > SJ_MAX_CH) return fail(err, "filterbank support too wide");
-    bool fast = ch <= SJ_MEL_FAST_CH;
+    bool fast = allow_fast && ch <= SJ_MEL_FAST_CH;
     if (fast) ch = SJ_MEL_FAST_CH;
     int lo_al = base;
     if (lo_al + 32 * ch > 1152) lo_al = (1152 - 32 * ch) & ~3; // stay inside the per-warp magnitude buffer
@@ -268,12 +270,11 @@ int sj_build_tables(SjTables *t, const void *blob, size_t blob_bytes, unsigned s
         t->tp4[0][b].w = 0.f;
     }
     const bool power = prm.spectrum == SJ_SPECTRUM_POWER;
-    if (build_mel(t, samplerate, power ? 0.25f : 0.5f, err)) return -1;
-    t->gen_flags = (power ? SJ_GEN_POWER : 0) | (prm.window != SJ_WINDOW_HANN_PERIODIC ? SJ_GEN_WINDOW_TABLE : 0);
+    const int gen_flags = (power ? SJ_GEN_POWER : 0) | (prm.window != SJ_WINDOW_HANN_PERIODIC ? SJ_GEN_WINDOW_TABLE : 0);
+    if (build_mel(t, samplerate, power ? 0.25f : 0.5f, !gen_flags && prm.log_floor == 2.e-42f, err)) return -1;
+    t->gen_flags = gen_flags;
     t->log_floor = prm.log_floor;
     t->label_rule = prm.label_rule;
-    // the specialised 16 kHz instantiation hard-codes the in-register periodic Hann, |X| and the 2e-42 floor
-    if (t->gen_flags || prm.log_floor != 2.e-42f) t->mel_fast = 0;
     for (int i = 0; i < SJ_WIN; ++i) {
         const double den = prm.window == SJ_WINDOW_HANN_SYMMETRIC ? (double)(SJ_WIN - 1) : (double)SJ_WIN;
         t->window[i] = (float)(0.5 * (1.0 - cos(two_pi * (double)i / den)));

@@ -167,6 +167,10 @@ typedef struct scrubjay_wav_info {
     int64_t data_offset, data_bytes, frames;
 } scrubjay_wav_info;
 SJ_API int scrubjay_wav_parse(const void *bytes, size_t n_bytes, scrubjay_wav_info *info);
+/* strict = 1: the rules above (read_wav_file, the donut path's reader).  strict = 0: chunks in front of "fmt " (JUNK,
+ * bext, LIST ...) are skipped, the way libsndfile -- the reader behind aubio_source (cepstrum/scrubjay_infer.c:21) --
+ * walks a RIFF file; cepstrum/testing/P_1363v2-sj-short.WAV starts with a JUNK chunk. */
+SJ_API int scrubjay_wav_parse_ex(const void *bytes, size_t n_bytes, scrubjay_wav_info *info, int strict);
 /* Device decode of interleaved int16 frames to mono float: policy SJ_MIX_FIRST = channel 0 / 32768
  * (classifier.c:293-297, 56-60), SJ_MIX_MEAN = mean over channels of s / 32768 (aubio_source_do's down-mix,
  * the input of mfcc_stats).  d_out[frames]. */

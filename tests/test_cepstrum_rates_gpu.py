@@ -51,10 +51,10 @@ def _run_dev(sj, clips_np, pcm16=False):
     return labels.cpu().numpy(), conf.cpu().numpy(), score.cpu().numpy(), feats.cpu().numpy()
 
 
-def _check(gpu, ora, what=""):
+def _check(gpu, ora, what="", atol_scale=1.0):
     gl, gc, gs, gf = gpu
     ol, oc, os_, of = ora
-    err = np.abs(gf - of) / (FEAT_RTOL * np.abs(of) + FEAT_ATOL)
+    err = np.abs(gf - of) / (FEAT_RTOL * np.abs(of) + FEAT_ATOL * atol_scale)
     assert err.max() <= 1.0, "%s: feature error %.3g x tolerance at %s" % (what, err.max(), np.unravel_index(err.argmax(), err.shape))
     assert np.allclose(gs, os_, rtol=1e-4, atol=1e-6), (what, np.abs(gs - os_).max())
     decided = np.abs(os_) >= 1e-6
@@ -142,7 +142,9 @@ def test_each_parameter_switch_matches_the_oracle_with_the_same_switch(idx, sr):
     sj.set_latency_mode(False)
     clips = _clips(sr, 64, sr, seed=100 + idx)
     g, o = _run_dev(sj, clips), ora.infer_batch(clips)
-    _check(g, o, "%s @ %d" % (name, sr))
+    # the unnormalised DCT is 2 / sqrt(2 / 40) = 8.9 times the orthonormal one: the absolute part of the tolerance
+    # (which covers coefficients near zero) scales with it
+    _check(g, o, "%s @ %d" % (name, sr), atol_scale=9.0 if "dct_norm" in kw else 1.0)
     base = _run_dev(_ctx(sr), clips)
     loud = np.abs(clips).max(axis=1) > 0
     changed = np.abs(g[3][loud] - base[3][loud]).max()

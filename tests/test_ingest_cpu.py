@@ -68,3 +68,19 @@ def test_reference_fixtures_parse_like_python_wave():
         assert (info.channels, info.sample_rate, info.bits_per_sample, info.frames) == ref, f
         seen += 1
     assert seen > 0
+
+
+def test_lenient_parse_skips_chunks_in_front_of_fmt():
+    """cepstrum/testing/P_1363v2-sj-short.WAV opens with a JUNK chunk: read_wav_file (classifier.c:248-253) would refuse
+    it, libsndfile (behind aubio_source, scrubjay_infer.c:21) reads it.  strict=False follows the latter."""
+    pcm = (np.arange(500) % 97 - 40).astype(np.int16)
+    w = _wav(pcm, 96000, 2)
+    junk = b"JUNK" + struct.pack("<I", 28) + b"\0" * 28
+    w2 = w[:12] + junk + w[12:]
+    assert dsp_b200.wav_parse(w2) is None
+    info = dsp_b200.wav_parse(w2, strict=False)
+    assert info is not None and (info.channels, info.sample_rate, info.frames) == (2, 96000, 250)
+    got = np.frombuffer(w2, "<i2", count=500, offset=info.data_offset)
+    assert np.array_equal(got, pcm)
+    a, b = dsp_b200.wav_parse(w), dsp_b200.wav_parse(w, strict=False)
+    assert (a.frames, a.data_offset) == (b.frames, b.data_offset)
