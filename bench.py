@@ -105,35 +105,39 @@ def cpu_baseline(clips_np, target_seconds=12.0):
                       % (n, dt)}
 
 
-def donut_cpu_reference(clips_np, n=4096):
-    """the UNMODIFIED reference classify() (sync/lib/classifier.cpp built into oracle/_ref by oracle/Makefile) on one
-    host thread -- it keeps static buffers, so it is not thread-safe -- over a bounded sample of the same clips"""
-    import ctypes
-    path = os.path.join(ROOT, "oracle", "_ref", "libdonut_ref_f32.so")
-    if not os.path.exists(path):
+def donut_cpu_reference(clips_np, per_proc=384):
+    """the UNMODIFIED reference classify() (sync/lib/classifier.cpp built into oracle/_ref by oracle/Makefile) on ALL host
+    cores: it keeps static buffers (classifier.cpp:230-232), so it is not thread-safe -- one worker PROCESS per core
+    (tools/donut_cpu_worker.py: no torch, no CUDA), each over its own slice of a bounded sample of the step's clips
+    (BASELINE.md section 4).  Throughput = clips / the slowest worker's classify() loop (start-up excluded)."""
+    import subprocess
+    import tempfile
+    import numpy as np
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdonut_ref_f32.so")):
         return None
-    L = ctypes.CDLL(path)
-    fn = getattr(L, "_Z8classifyPfi")
-    fn.argtypes = [ctypes.c_void_p, ctypes.c_int]
-    n = min(n, clips_np.shape[0])
-    x = clips_np[:n].copy()
-    labels = []
-    sys.stdout.flush()
-    saved, null = os.dup(1), os.open(os.devnull, os.O_WRONLY)  # the reference prints from inside classify()
-    os.dup2(null, 1)
-    try:
+    procs = host_threads()
+    n = min(clips_np.shape[0], procs * per_proc)
+    per = n // procs
+    if per < 1:
+        return None
+    n = per * procs
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "clips.npy")
+        np.save(path, clips_np[:n])
+        worker = os.path.join(ROOT, "tools", "donut_cpu_worker.py")
         t0 = time.perf_counter()
-        for i in range(n):
-            labels.append(int(fn(x[i].ctypes.data, x.shape[1])))
-        dt = time.perf_counter() - t0
-    finally:
-        ctypes.CDLL(None).fflush(None)
-        os.dup2(saved, 1)
-        os.close(null)
-        os.close(saved)
-    return {"value": n / dt, "unit": "clips/s", "cores": 1, "kind": "reference",
-            "sample": "%d of the step's clips, %.1f s wall, unmodified sync/lib/classifier.cpp + PlainFFT.cpp -O3, one thread "
-                      "(static buffers: not thread-safe)" % (n, dt)}, labels
+        ps = [subprocess.Popen([sys.executable, worker, path, str(i * per), str(per)], stdout=subprocess.PIPE)
+              for i in range(procs)]
+        outs = [json.loads(p.communicate()[0].decode().strip().splitlines()[-1]) for p in ps]
+        wall = time.perf_counter() - t0
+    outs.sort(key=lambda o: o["first"])
+    labels = [l for o in outs for l in o["labels"]]
+    slow = max(o["seconds"] for o in outs)
+    return {"value": n / slow, "unit": "clips/s", "cores": procs, "kind": "reference",
+            "one_process_value": per / statistics.median(o["seconds"] for o in outs),
+            "sample": "%d of the step's clips, %d worker processes x %d clips, slowest loop %.1f s (%.1f s wall with start-up), "
+                      "unmodified sync/lib/classifier.cpp + PlainFFT.cpp -O3 (static buffers: one process per core)"
+                      % (n, procs, per, slow, wall)}, labels
 
 
 # ---------------------------------------------------------------- clocks sampler
@@ -369,8 +373,14 @@ def run_ours(args, rank, local_rank, world):
         tp = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if dist is not None:
             dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        pgbs = (N_SAMPLES * 2 + 8) * Cp / (kp * 1e-3) / 1e9
+        ppk, ppk_src = measured_peak_gbs()
+        ptr = (ncu_traffic_bytes_per_clip() or {}).get("pcm16_dram_bytes_per_clip")
         pcm = {"clips_per_s_per_gpu_resident": Cp / (kp * 1e-3), "kernel_ms": kp, "clips": Cp,
-               "bytes_per_clip": N_SAMPLES * 2 + 8, "achieved_gbs": (N_SAMPLES * 2 + 8) * Cp / (kp * 1e-3) / 1e9,
+               "bytes_per_clip": N_SAMPLES * 2 + 8, "achieved_gbs": pgbs,
+               "roofline": {"bound": "hbm", "achieved": pgbs, "peak": ppk, "unit": "GB/s", "frac": pgbs / ppk,
+                            "traffic": ptr * Cp if ptr else None, "peak_source": ppk_src, "kernel_ms": kp,
+                            "kernel": "cepstrum_kernel<12 warps, TMA, fast-16k, PCM16>", "bytes_per_clip": N_SAMPLES * 2 + 8},
                "e2e": {"value": world * E * args.e2e_steps / float(tp.item()), "unit": "clips/s",
                        "h2d_bytes_per_step": E * N_SAMPLES * 2, "d2h_bytes_per_step": E * 12,
                        "api": "scrubjay_infer_batch_pcm16 (host int16 PCM, pinned)"},
@@ -390,18 +400,26 @@ def run_ours(args, rank, local_rank, world):
                 sj.donut_classify_batch_dev(clips, Cd, N_SAMPLES, variant, labels[:Cd], det)
                 kd.append(sj.last_kernel_ms())
             kd = min(kd[1:])
+            gbs = (N_SAMPLES * 4 + 4) * Cd / (kd * 1e-3) / 1e9
+            pk, pk_src = measured_peak_gbs()
+            tr = (ncu_traffic_bytes_per_clip() or {}).get("donut_" + name + "_dram_bytes_per_clip")
             donut[name] = {"kernel_ms": kd, "clips_per_s_per_gpu": Cd / (kd * 1e-3), "frames_per_s_per_gpu": 142 * Cd / (kd * 1e-3),
-                           "achieved_gbs": (N_SAMPLES * 4 + 4) * Cd / (kd * 1e-3) / 1e9,
+                           "achieved_gbs": gbs,
+                           "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk, "unit": "GB/s", "frac": gbs / pk,
+                                        "traffic": tr * Cd if tr else None, "peak_source": pk_src, "kernel_ms": kd,
+                                        "kernel": "donut_ws_kernel (4 filter + 8 transform warps)" if name == "sync_f32" else "donut_kernel<double>",
+                                        "bytes_per_clip": N_SAMPLES * 4 + 4,
+                                        "note": "FP32 / FP64 issue of the exact (no-FMA) recurrence and FFT binds, not HBM"},
                            "positives": int(labels[:Cd].sum().item())}
         if args.cpu_baseline and world == 1:
-            ref = donut_cpu_reference(host[:4096].numpy())
+            ref = donut_cpu_reference(host[:min(E, 32768)].numpy())
             if ref is not None:
                 nr = len(ref[1])
                 sj.donut_classify_batch_dev(clips, nr, N_SAMPLES, dsp_b200.DONUT_SYNC_F32, labels[:nr], det[:nr])
                 same = int((labels[:nr].cpu().numpy() == np.array(ref[1], dtype=np.int32)).sum())
                 donut["cpu_reference"] = dict(ref[0], labels_equal_to_gpu="%d of %d" % (same, len(ref[1])))
-        donut["note"] = ("fused donut_kernel (IIR x2 bit-exact, spectrogram x2, band sums, verdict); instruction-bound "
-                         "(exact no-FMA replay of the reference FFT), see DESIGN.md section 6")
+        donut["note"] = ("fused donut kernels (IIR x2 bit-exact, spectrogram x2, band sums, verdict); instruction-bound "
+                         "(exact no-FMA replay of the reference recurrence and FFT), see DESIGN.md section 6")
         del det
 
     # ---- BASELINE config 1 (single-clip inference): latency of one 1 s clip through the host-pointer call
