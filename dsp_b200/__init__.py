@@ -34,6 +34,7 @@ IIR_EXACT, IIR_SCAN = 0, 1       # one recurrence per lane (bit-identical) / blo
 BUTTER_16K, BUTTER_48K_DESIGN = 0, 1
 DONUT_MAX_MID = 8
 MAX_PEERS = 8
+NOALLOC_MAX_TOTAL_FRAMES = 16384
 PEER_HANDLE_BYTES = 64
 
 
@@ -67,6 +68,7 @@ def load_library():
     L.scrubjay_predict_batch_dev.argtypes = [vp, vp, c_long, vp, vp, vp]
     L.scrubjay_infer_batch_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_infer_batch_pcm16_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
+    L.scrubjay_infer_batch_noalloc_dev.argtypes = [vp, vp, c_long, c_int, vp, vp, vp, vp]
     L.scrubjay_peer_alloc.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp), vp]
     L.scrubjay_peer_free.argtypes = [vp, vp]
     L.scrubjay_peer_open.argtypes = [vp, vp, ctypes.POINTER(vp)]
@@ -236,6 +238,12 @@ class ScrubJay:
     def infer_batch_dev(self, d_clips, n_clips, n_samples, d_labels, d_conf=None, d_score=None, d_feats=None):
         self._check(self._L.scrubjay_infer_batch_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_labels),
                                                      _ptr(d_conf), _ptr(d_score), _ptr(d_feats)))
+
+    def infer_batch_noalloc_dev(self, d_clips, n_clips, n_samples, d_labels, d_conf=None, d_score=None, d_feats=None):
+        """scrubjay_infer_batch_noalloc_dev: small batches, scratch in the library's static device array, no allocation
+        (n_clips * ceil(n_samples / 1024) <= NOALLOC_MAX_TOTAL_FRAMES)"""
+        self._check(self._L.scrubjay_infer_batch_noalloc_dev(self._h, _ptr(d_clips), n_clips, n_samples, _ptr(d_labels),
+                                                             _ptr(d_conf), _ptr(d_score), _ptr(d_feats)))
 
     # ---- fused multi-GPU gather (peer stores over NVLink instead of a collective after the kernel)
     def peer_alloc(self, nbytes, want_handle=True):

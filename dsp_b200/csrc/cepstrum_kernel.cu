@@ -697,6 +697,33 @@ __global__ void __launch_bounds__(128) clip_stats_kernel(const SjCepstrumArgs a,
     }
 }
 
+// ---- allocation-free variant (scrubjay_infer_batch_noalloc_dev; no counterpart in the reference).
+// The frame scratch [clip][frame][40] of the frame-parallel clip mode lives in a file-scope
+// static array instead of a cudaMalloc'd buffer: SJ_NOALLOC_MAX_FRAMES frames x 40 floats = 2.5 MiB that every GPU
+// which loads the library holds until exit.  Every call on a device shares the array, and it keeps the last call's
+// contents; nothing in it has to start at zero (the first kernel writes all 40 floats of every (clip, frame) entry the
+// second kernel reads), but two calls that overlap on one GPU race on it.
+static __device__ __align__(256) float g_noalloc_frames[size_t(SJ_NOALLOC_MAX_FRAMES) * SJ_FEAT];
+
+// clip_stats_kernel with the frames read from the static array, named directly by device code
+__global__ void __launch_bounds__(128) clip_stats_static_kernel(const SjCepstrumArgs a, int F)
+{
+    __shared__ float z[4][SJ_FEAT];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long i = (long)blockIdx.x * 4 + warp; i < a.n_clips; i += (long)gridDim.x * 4) {
+        double sum = 0.0, sq = 0.0;
+        if (lane < SJ_NCOEF) {
+            const float *p = g_noalloc_frames + i * F * SJ_FEAT + lane;
+            for (int f = 0; f < F; ++f) {
+                const double dv = (double)p[(long)f * SJ_FEAT];
+                sum += dv;
+                sq += dv * dv;
+            }
+        }
+        sj_emit(a, z[warp], lane, i, sum, sq, F);
+    }
+}
+
 template <int WARPS> size_t smem_bytes(int maxseg, bool stream, bool pcm16)
 {
     size_t off = (kHotBytes + 127) & ~size_t(127);
@@ -786,6 +813,34 @@ cudaError_t sj_launch_clip_stats(const SjCepstrumArgs &a, const float *frames, i
     long blocks = (a.n_clips + 3) / 4;
     if (blocks > 148 * 8) blocks = 148 * 8;
     clip_stats_kernel<<<(unsigned)blocks, 128, 0, stream>>>(a, frames, n_frames);
+    return cudaGetLastError();
+}
+
+// Device address of the static frame scratch on `device`, which the caller has made current.  In host code the array's
+// name is only a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, looked up once
+// per device (set-up) and cached.  No allocation.
+cudaError_t sj_noalloc_frame_scratch(int device, float **ptr)
+{
+    constexpr int kMaxDev = 64;
+    static float *cache[kMaxDev] = {nullptr};
+    if (!ptr || device < 0 || device >= kMaxDev) return cudaErrorInvalidDevice;
+    if (!cache[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_frames);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        cache[device] = static_cast<float *>(p);
+    }
+    *ptr = cache[device];
+    return cudaSuccess;
+}
+
+cudaError_t sj_launch_clip_stats_static(const SjCepstrumArgs &a, int n_frames, cudaStream_t stream)
+{
+    if (a.n_clips <= 0) return cudaSuccess;
+    long blocks = (a.n_clips + 3) / 4;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    clip_stats_static_kernel<<<(unsigned)blocks, 128, 0, stream>>>(a, n_frames);
     return cudaGetLastError();
 }
 

@@ -46,6 +46,10 @@ cudaError_t sj_launch_cepstrum(const SjCepstrumArgs &a, const SjTables *host_tab
 // frame-parallel clip mode, second kernel: per-clip statistics over frames[clip][n_frames][40] (+ Scaler + SVM, outputs
 // as named by `a`; a.clips / stream fields are not used)
 cudaError_t sj_launch_clip_stats(const SjCepstrumArgs &a, const float *frames, int n_frames, cudaStream_t stream);
+// allocation-free variant: the frame scratch is a static device array of SJ_NOALLOC_MAX_FRAMES x 40 floats (2.5 MiB)
+#define SJ_NOALLOC_MAX_FRAMES 16384
+cudaError_t sj_noalloc_frame_scratch(int device, float **ptr); // device must be current; looked up once per device
+cudaError_t sj_launch_clip_stats_static(const SjCepstrumArgs &a, int n_frames, cudaStream_t stream);
 // warps the persistent grid keeps resident (work-item sizing of the stream mode)
 int sj_cepstrum_resident_warps(int num_sms);
 // one-time attribute set-up (max dynamic shared memory); returns cudaError_t

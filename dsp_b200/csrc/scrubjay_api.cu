@@ -361,6 +361,53 @@ int scrubjay_infer_batch_pcm16_dev(scrubjay_ctx *c, const int16_t *d_clips, long
                            d_score, d_feats, 1, true, 1);
 }
 
+/* Allocation-free fused mfcc_stats + ort_predict for small batches (no counterpart in the reference).
+ * Always the frame-parallel form: the STREAM instantiation with one-frame windows
+ * writes every frame's MFCC vector into the library's static device array (address from cudaGetSymbolAddress, looked
+ * up once per device in cepstrum_kernel.cu), then clip_stats_static_kernel forms the per-clip statistics in frame
+ * order -- the arithmetic and the order of the double sums of scrubjay_infer_batch_dev, so the outputs are the same
+ * bits.  Two kernel launches; no cudaMalloc / cudaFree / event or stream creation, nothing else that allocates. */
+int scrubjay_infer_batch_noalloc_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int32_t *d_labels,
+                                     float *d_conf, float *d_score, float *d_feats)
+{
+    static_assert(SJ_NOALLOC_MAX_FRAMES == SJ_NOALLOC_MAX_TOTAL_FRAMES, "public and internal limits");
+    if (!c) return SJ_EINVAL;
+    if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
+    if (n_samples <= 0) return set_err(c, SJ_EINVAL, "empty clip");
+    if (n_clips == 0) return SJ_OK;
+    const long F = ((long)n_samples + SJ_HOP - 1) / SJ_HOP;
+    if (n_clips > SJ_NOALLOC_MAX_FRAMES || n_clips * F > SJ_NOALLOC_MAX_FRAMES) {
+        snprintf(c->err, sizeof c->err,
+                 "scrubjay_infer_batch_noalloc_dev: %ld clips x %ld frames = %ld frames exceed the static scratch of %d frames "
+                 "(SJ_NOALLOC_MAX_TOTAL_FRAMES); use scrubjay_infer_batch_dev", n_clips, F, n_clips * F, SJ_NOALLOC_MAX_FRAMES);
+        return SJ_EINVAL;
+    }
+    SJ_CUDA(c, cudaSetDevice(c->device));
+    float *scratch = nullptr;
+    SJ_CUDA(c, sj_noalloc_frame_scratch(c->device, &scratch));
+    SjCepstrumArgs a;
+    a.pcm16 = 0;
+    a.peers = nullptr;
+    a.clips = d_clips; a.n_clips = n_clips; a.n_samples = n_samples; a.tables = c->d_tables;
+    a.labels = d_labels; a.conf = d_conf; a.score = d_score; a.feats = d_feats; a.do_svm = 1;
+    a.chan_stride = 0; a.prev_hop = nullptr; a.n_windows = 0; a.win_frames = a.step_frames = 0;
+    a.chunk_windows = 0; a.chunks_per_chan = 0;
+    SjCepstrumArgs f = a; // first kernel: every frame's MFCC vector -> scratch[clip][frame][40]
+    f.labels = nullptr; f.conf = nullptr; f.score = nullptr; f.do_svm = 0;
+    f.feats = scratch;
+    f.chan_stride = n_samples; f.n_windows = F; f.win_frames = f.step_frames = 1;
+    const long resident = sj_cepstrum_resident_warps(c->num_sms);
+    long k = (n_clips * F + resident - 1) / resident; // frames per work item: about one item per resident warp
+    if (k < 1) k = 1;
+    if (k > F) k = F;
+    f.chunk_windows = (int)k;
+    f.chunks_per_chan = (F + k - 1) / k;
+    SJ_CUDA(c, sj_launch_cepstrum(f, c->h_tables, c->num_sms, c->stream));
+    SJ_CUDA(c, sj_launch_clip_stats_static(a, (int)F, c->stream));
+    c->launches += 2;
+    return SJ_OK;
+}
+
 int scrubjay_peer_alloc(scrubjay_ctx *c, size_t bytes, void **d_ptr, unsigned char handle[SJ_PEER_HANDLE_BYTES])
 {
     static_assert(sizeof(cudaIpcMemHandle_t) == SJ_PEER_HANDLE_BYTES, "handle size");

@@ -120,6 +120,21 @@ SJ_API int scrubjay_predict_batch_dev(scrubjay_ctx *ctx, const float *d_feats, l
 SJ_API int scrubjay_infer_batch_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
                              int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  scrubjay_infer_batch_dev
+ * for SMALL batches that allocates nothing: its frame scratch ([clip][frame][40] floats) is a static device array
+ * inside the library -- SJ_NOALLOC_MAX_TOTAL_FRAMES frames = 2.5 MiB that every GPU which loads the library holds
+ * until exit.  Limit: n_clips * ceil(n_samples / 1024) <= SJ_NOALLOC_MAX_TOTAL_FRAMES (1024 one-second 16 kHz clips);
+ * beyond it the call returns SJ_EINVAL with a message and does nothing.  Inputs and outputs are the caller's device
+ * arrays as in scrubjay_infer_batch_dev (d_conf, d_score, d_feats may be NULL); the outputs are bit-identical to that
+ * call.  Work is enqueued on the context's stream (two kernels); the call itself makes no cudaMalloc / cudaFree and
+ * creates no stream or event.  ALL calls on a GPU share the one array, which keeps the last call's contents (nothing
+ * in it needs to start at zero: every entry read is written first): calls that overlap on the GPU -- two contexts or
+ * two streams on one device -- race on it; serialise them. */
+#define SJ_NOALLOC_MAX_TOTAL_FRAMES 16384
+SJ_API int scrubjay_infer_batch_noalloc_dev(scrubjay_ctx *ctx, const float *d_clips, long n_clips, int n_samples,
+                                            int32_t *d_labels, float *d_conf, float *d_score, float *d_feats);
+
 /* ---- multi-GPU result gather fused into the kernel (clips are sharded by contiguous ranges, the path's
  * only exchange is the final gather of label int32 + score fp32 = 8 B per clip).  The reference has no counterpart:
  * its main loop prints every file's label as it goes (cepstrum/scrubjay_infer.c:166-176).  Instead of a collective
