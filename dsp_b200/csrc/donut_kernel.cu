@@ -910,6 +910,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
             for (int t = 0; t < tb; ++t) {
                 if (t > 0) bar_sync(kBarEmpty + g, kPair); // the transform warps are done with frame t - 1
                 const int nnew = t == 0 ? DN_WIN : DN_HOP;
+#pragma unroll 1
                 for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) {
 #pragma unroll
                     for (int j = 0; j < kPre; ++j) {
