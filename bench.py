@@ -458,7 +458,11 @@ def run_ours(args, rank, local_rank, world):
                        "timing": "CUDA events on the launching stream, max over ranks"},
             "frames_per_s": value * FRAMES_PER_CLIP,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": (traffic or {}).get("dram_bytes_per_launch_1M_clips"),
+                         "traffic": (traffic or {}).get("dram_bytes_per_clip", 0) * C or None,
+                         "traffic_source": "ncu dram bytes per clip (%.0f B, profiles/roofline_traffic.json: a 200 k-clip --set full capture) "
+                                           "x the %d clips of this launch" % ((traffic or {}).get("dram_bytes_per_clip", 0), C),
+                         "fp32_note": "binding resources are the FP32 pipe (58 %), instruction issue (56 %) and the shared-memory LSU (72 %), "
+                                      "all per profiles/r2f_ncu_full_cepstrum.txt; HBM is at 29 %",
                          "peak_source": peak_src, "kernel": "cepstrum_kernel<12 warps, TMA, fast-16k>",
                          "kernel_ms": kernel_ms, "bytes_per_clip": BYTES_PER_CLIP,
                          "note": "shared-memory bandwidth and instruction issue of the FFT, not HBM, bind this kernel (see DESIGN.md): frac is of the HBM roofline"},
