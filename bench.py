@@ -262,13 +262,13 @@ def run_ours(args, rank, local_rank, world):
     # weak scaling: rank r owns global clips [r*C, (r+1)*C) of the counter-based synthetic set
     sj.synth_clips_dev(clips, rank * C, C, N_SAMPLES, SEED)
     # the path's only exchange: the final label/score gather, 8 B per clip.  Default: fused into the kernel (every
-    # result is stored into every rank's arrays through NVLink peer mappings, dsp_b200.sharded.PeerGather);
+    # result is stored into every rank's arrays through NVLink peer mappings, tools/sharded_torch.py: PeerGather);
     # --gather nccl (or a box without CUDA IPC / peer access) runs two NCCL all-gathers after the kernel instead.
     peer, gather_mode = None, "none (1 GPU)"
     if dist is not None:
         gather_mode = "nccl all-gather after the kernel"
         if args.gather == "p2p":
-            from dsp_b200.sharded import PeerGather
+            from sharded_torch import PeerGather
             ok = torch.ones(1, dtype=torch.int32, device=dev)
             try:
                 peer = PeerGather(sj, C, dist)

@@ -1,4 +1,4 @@
-"""Host logic of the fused multi-GPU gather (dsp_b200.sharded.PeerGather) on CPU, world_size 2 over gloo.
+"""Host logic of the fused multi-GPU gather (tools/sharded_torch.py: PeerGather) on CPU, world_size 2 over gloo.
 The CUDA side (peer allocations, IPC mapping, the kernel's stores) is replaced by a recording stand-in that
 "stores" through /dev/shm files, so what is under test is the handle exchange, the rank order of the target
 list, the slot layout and the close protocol.  The kernel side is tests/test_gather_gpu.py."""
@@ -57,7 +57,7 @@ def _worker(rank, world, port, shm):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from dsp_b200.sharded import PeerGather
+    from sharded_torch import PeerGather
     ctx = FakeCtx(rank, shm)
     g = PeerGather(ctx, N_PER_RANK, dist)
     assert (g.total, g.base) == (N_PER_RANK * world, N_PER_RANK * rank)
@@ -87,7 +87,7 @@ def _worker_fail(rank, world, port, shm):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from dsp_b200.sharded import PeerGather
+    from sharded_torch import PeerGather
 
     class Broken(FakeCtx):
         def peer_alloc(self, nbytes, want_handle=True):
@@ -121,7 +121,7 @@ def test_two_rank_peer_gather_host_logic(tmp_path):
 
 
 def test_gather_layout():
-    from dsp_b200.sharded import gather_layout
+    from sharded_torch import gather_layout
     assert gather_layout(1000, 0, 1) == (1000, 0)
     assert gather_layout(1000, 3, 8) == (8000, 3000)
     with pytest.raises(ValueError):

@@ -70,7 +70,7 @@ def test_bind_errors(sj):
 def test_peer_alloc_round_trip(sj):
     addr, h = sj.peer_alloc(4096)
     assert addr and len(h) == dsp_b200.PEER_HANDLE_BYTES and any(h)
-    from dsp_b200.sharded import _DevView
+    from sharded_torch import _DevView
     v = torch.as_tensor(_DevView(addr, 1024, "<i4"), device="cuda")
     v.fill_(3)
     assert int(v.sum().item()) == 3072

@@ -25,7 +25,7 @@ def _worker(rank, world, port, out_dir):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     import dsp_b200
-    from dsp_b200.sharded import gather_clip_results
+    from sharded_torch import gather_clip_results
     from oracle_lib import CepstrumOracle
     lo, hi = dsp_b200.shard_range(N_TOTAL, rank, world)
     labels, _, score, _ = CepstrumOracle(16000).infer_batch(_clips()[lo:hi])

@@ -2,7 +2,7 @@
 """BASELINE config 5 at its named size: long continuous 16 kHz streams (1 h per channel, 4096 channels) through the
 sliding-frame cepstrum + SVM, channels sharded over the GPUs of one box (512 channels = 118 GB per GPU at 8 GPUs), no
 data-path collective, the per-window labels and scores gathered by the kernel itself (peer stores over NVLink,
-dsp_b200.sharded.PeerGather; SJ_GATHER=nccl runs two NCCL all-gathers after the kernel instead).
+tools/sharded_torch.py: PeerGather; SJ_GATHER=nccl runs two NCCL all-gathers after the kernel instead).
 usage (one rank per GPU): python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
           tools/bench_stream_multi.py [channels=4096] [seconds=3600] [win=16] [step=16] [reps=3]"""
 import json, os, sys
@@ -36,7 +36,7 @@ sc = torch.empty((nch, nw), dtype=torch.float32, device=dev)
 torch.cuda.synchronize()
 peer = None
 if world > 1 and os.environ.get("SJ_GATHER", "p2p") == "p2p":
-    from dsp_b200.sharded import PeerGather
+    from sharded_torch import PeerGather
     assert nch_total % world == 0, "fused gather: equal channel counts per rank"
     peer = PeerGather(sj, nch * nw, dist)
 best = None

@@ -10,7 +10,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 import dsp_b200
-from dsp_b200.sharded import PeerGather
+from sharded_torch import PeerGather
 
 C = int(sys.argv[1]) if len(sys.argv) > 1 else 200000
 NS, STEPS = 16000, 5

@@ -2,8 +2,10 @@
 of W processes the contiguous range shard_range(n, r, W) with no data-path collective; the only
 exchange is the final gather of (label int32, score fp32) = 8 B per clip.
 
-`torch.distributed` is plumbing here (NCCL on GPUs, gloo in the CPU tests)."""
-from . import shard_range
+`torch.distributed` is plumbing here (NCCL on GPUs, gloo in the CPU tests).  This module is bench / test
+infrastructure and lives outside the product package on purpose: the product (libscrubjay_cuda + the ctypes mirror
+dsp_b200) has no torch in it; a C host exchanges the 64-byte handles itself (examples/multi_gpu_gather.c)."""
+from dsp_b200 import shard_range
 
 
 def gather_clip_results(labels, score, n_total, dist=None):
