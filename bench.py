@@ -63,6 +63,31 @@ def ncu_traffic_bytes_per_clip():
         return None
 
 
+def bind_to_gpu_numa_node(index):
+    """Bind this rank to the CPUs of its GPU's NUMA node BEFORE any pinned host allocation, so that the staging buffers
+    of the host-pointer path are first-touched next to the GPU's PCIe root (all eight ranks sat on
+    node 0).  Returns the node, or None where sysfs names none (single-socket boxes, VMs: nothing to bind)."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(index).pci_bus_id
+        dom = torch.cuda.get_device_properties(index).pci_domain_id
+        dev = torch.cuda.get_device_properties(index).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 # ---------------------------------------------------------------- CPU path (oracle) timing
 def cpu_run(oracle, clips, threads):
     """oracle.infer_batch over `clips`, split across `threads` OS threads (ctypes releases the GIL;
@@ -225,6 +250,105 @@ def run_reference(args, rank):
     return 0
 
 
+# ---------------------------------------------------------------- BASELINE configs 3, 4, 5 at their named sizes
+def run_config3(sj, clips, labels, C, dev):
+    """config 3: donut Butterworth IIR + FFT band-energy path on 16 384 synthetic streams x 60 s, one B200: every full
+    second of every stream classified from zero state, like the firmware (sync/sync.cpp:190-212) -> decision tracks"""
+    import torch
+    import dsp_b200
+    streams, secs = 16384, 60
+    if streams * secs > C:
+        secs = C // streams
+    if secs < 1:
+        return None
+    n = streams * secs
+    track = torch.empty((streams, secs), dtype=torch.int8, device=dev)
+    out = {"streams": streams, "seconds_per_stream": secs, "clips": n, "bytes": n * N_SAMPLES * 4,
+           "api": "scrubjay_donut_classify_streams_dev (per-second decision tracks)"}
+    for name, variant in (("sync_f32", dsp_b200.DONUT_SYNC_F32), ("desktop_f64", dsp_b200.DONUT_DESKTOP_F64)):
+        ms = []
+        for _ in range(3):
+            sj.donut_classify_streams_dev(clips, streams, secs * N_SAMPLES, secs * N_SAMPLES, variant, track)
+            ms.append(sj.last_kernel_ms())
+        ms = min(ms[1:])
+        out[name] = {"ms": ms, "clips_per_s": n / ms * 1e3, "frames_per_s": 142 * n / ms * 1e3,
+                     "audio_seconds_per_s": n / ms * 1e3, "scrub_jay_seconds": int((track == 2).sum().item())}
+    return out
+
+
+def run_config4(sj, clips, C, conf, dist, dev, rank, world, barrier, total=10_000_000):
+    """config 4: clip-sharded cepstrum + SVM on 10 M clips over N GPUs with the label / score gather: every rank walks its
+    10 M / N clips in resident passes of <= C clips (the resident batch is reused for every pass: inputs >> L2, so reuse
+    buys nothing), results stored straight into every rank's complete 10 M-entry arrays by the kernel (peer stores)."""
+    import torch
+    from sharded_torch import PeerGather
+    per = total // world
+    g = PeerGather(sj, per, dist)
+    passes = [(o, min(C, per - o)) for o in range(0, per, C)]
+
+    def step():
+        for o, n in passes:
+            sj.gather_bind(g.peer_labels, g.peer_score, g.base + o)
+            sj.infer_batch_gather_dev(clips, n, N_SAMPLES, conf)
+
+    step()
+    barrier()
+    best = None
+    for _ in range(2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        best = float(t.item()) if best is None else min(best, float(t.item()))
+    filled = int((g.labels >= 0).sum().item())
+    out = {"total_clips": per * world, "clips_per_gpu": per, "passes_per_gpu": len(passes), "ms": best,
+           "clips_per_s": per * world / best * 1e3, "frames_per_s": per * world * FRAMES_PER_CLIP / best * 1e3,
+           "gathered_entries_on_rank0": filled, "gather": "fused peer stores into every rank's 10 M-entry arrays",
+           "timing": "CUDA events around all passes of one 10 M-clip step, max over ranks"}
+    torch.cuda.synchronize()
+    g.close()
+    sj.gather_bind([], None, 0)
+    return out
+
+
+def run_config5(sj, dist, dev, rank, world, barrier, channels=4096, secs=3600, W=16, S=16):
+    """config 5: 4096 channels x 1 h of continuous 16 kHz audio, sliding-frame cepstrum + SVM (tumbling 1 s windows),
+    channels sharded over the GPUs (512 channels = 118 GB per GPU at N = 8), per-window labels / scores gathered by the
+    kernel itself"""
+    import torch
+    from sharded_torch import PeerGather
+    nch = channels // world
+    ns = secs * N_SAMPLES
+    d = torch.empty((nch * secs, N_SAMPLES), dtype=torch.float32, device=dev)
+    sj.synth_clips_dev(d, rank * nch * secs, nch * secs, N_SAMPLES, SEED)
+    nw = sj.stream_windows(ns, W, S)
+    g = PeerGather(sj, nch * nw, dist)
+    best = None
+    for i in range(3):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sj.stream_infer_gather_dev(d, nch, ns, ns, win_frames=W, step_frames=S)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if i > 0:
+            best = float(t.item()) if best is None else min(best, float(t.item()))
+    hops = (ns + 1023) // 1024
+    out = {"channels": nch * world, "seconds_per_channel": secs, "channels_per_gpu": nch, "bytes_per_gpu": nch * ns * 4, "ms": best,
+           "windows_per_s": nch * world * nw / best * 1e3, "frames_per_s": nch * world * hops / best * 1e3,
+           "audio_hours_per_s": nch * world * secs / 3600.0 / best * 1e3, "positive_windows_rank0_view": int(g.labels.sum().item()),
+           "gather": "fused peer stores", "timing": "CUDA events incl. the gather, max over ranks"}
+    torch.cuda.synchronize()
+    g.close()
+    del d
+    return out
+
+
 # ---------------------------------------------------------------- our arm
 def run_ours(args, rank, local_rank, world):
     import numpy as np
@@ -235,6 +359,7 @@ def run_ours(args, rank, local_rank, world):
         raise SystemExit("bench.py: no GPU (libscrubjay_cuda has no CPU fallback; use --impl reference for the CPU path)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_node = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     dist = None
     # libraries (NCCL's version banner) write to stdout; the contract is ONE JSON line there, so fd 1 points at
     # stderr until the line is printed
@@ -310,14 +435,34 @@ def run_ours(args, rank, local_rank, world):
         barrier()
     total_ms = ev[0].elapsed_time(ev[args.steps])
     launches = sj.launch_count - launches0
-    if peer is not None:  # the gathered arrays must hold this rank's results at its slots and be complete
+    gather_check = None
+    if peer is not None:
+        # The fused gather has no completion signal of its own: a consumer needs the cross-rank barrier that follows the
+        # step.  Check it the hard way: poison every rank's arrays, barrier, ONE gather step, barrier, then
+        # compare the complete arrays with an NCCL all-gather of the plain call's outputs.
+        peer.labels.fill_(-7)
+        peer.score.fill_(float("nan"))
+        barrier()
+        sj.infer_batch_gather_dev(clips, C, N_SAMPLES, conf)
+        barrier()
         sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
+        ref_l = torch.empty(world * C, dtype=torch.int32, device=dev)
+        ref_s = torch.empty(world * C, dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(ref_l, labels)
+        dist.all_gather_into_tensor(ref_s, score)
         torch.cuda.synchronize()
-        assert torch.equal(peer.labels[rank * C:(rank + 1) * C], labels), "fused gather: own slots differ"
-        assert torch.equal(peer.score[rank * C:(rank + 1) * C], score), "fused gather: own slots differ"
-        cnt = torch.tensor([int(labels.sum().item())], dtype=torch.int64, device=dev)
-        dist.all_reduce(cnt)
-        assert int(peer.labels.sum().item()) == int(cnt.item()), "fused gather: arrays incomplete"
+        assert torch.equal(peer.labels, ref_l), "fused gather: labels differ from the NCCL all-gather of the plain outputs"
+        assert torch.equal(peer.score, ref_s), "fused gather: scores differ from the NCCL all-gather of the plain outputs"
+        # per-step time WITH the barrier a consumer needs (the headline loop has one barrier after K steps)
+        tb0 = time.perf_counter()
+        for _ in range(5):
+            sj.infer_batch_gather_dev(clips, C, N_SAMPLES, conf)
+            barrier()
+        tb = torch.tensor([(time.perf_counter() - tb0) / 5 * 1e3], dtype=torch.float64, device=dev)
+        dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        gather_check = {"verified": "poisoned arrays, one gather step, full labels + score arrays equal to an NCCL all-gather of the plain call on every rank",
+                        "ms_per_step_with_barrier_each_step": float(tb.item()),
+                        "headline_timing": "K steps back to back, one barrier + synchronize after the last (the per-step barrier is excluded)"}
     # kernel-only time, measured live: events bracketing the kernel alone (no gather), same stream
     for i in range(min(args.steps, 5)):
         sj.infer_batch_dev(clips, C, N_SAMPLES, labels, conf, score, None)
@@ -422,6 +567,10 @@ def run_ours(args, rank, local_rank, world):
                          "(exact no-FMA replay of the reference recurrence and FFT), see DESIGN.md section 6")
         del det
 
+    # ---- BASELINE configs 3 / 4 at their named sizes (config 5 runs last: it needs the clips' memory)
+    config3 = run_config3(sj, clips, labels, C, dev) if (args.configs and world == 1) else None
+    config4 = run_config4(sj, clips, C, conf, dist, dev, rank, world, barrier) if (args.configs and world >= 2 and peer is not None) else None
+
     # ---- BASELINE config 1 (single-clip inference): latency of one 1 s clip through the host-pointer call
     single = None
     if rank == 0:
@@ -439,11 +588,20 @@ def run_ours(args, rank, local_rank, world):
         single = {"host_call_us": statistics.median(ws[4:]), "kernels_us": statistics.median(ks[2:]),
                   "api": "scrubjay_infer_batch, 1 clip (H2D 64 KB + 2 kernels + D2H); frame-parallel small-batch path"}
 
+    config5 = None
+    if args.configs and world >= 8 and peer is not None:
+        peer.close()
+        peer = None
+        del clips, host
+        torch.cuda.empty_cache()
+        config5 = run_config5(sj, dist, dev, rank, world, barrier)
+        clips = None
+
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         achieved = BYTES_PER_CLIP * C / (kernel_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_clip()
-        cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if (args.cpu_baseline and world == 1) else None  # N = 1 only
+        cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if (args.cpu_baseline and world == 1) else None  # N = 1 only (host is kept at N = 1)
         if cpu and single and cpu.get("one_thread_value"):
             single["cpu_port_us"] = 1e6 / cpu["one_thread_value"]
         line = {
@@ -454,6 +612,7 @@ def run_ours(args, rank, local_rank, world):
                        "clips_per_gpu": C, "n_samples": N_SAMPLES, "frames_per_clip": FRAMES_PER_CLIP,
                        "sharding": "clip-sharded x%d, label/score gather (8 B/clip) inside each step" % world,
                        "gather": gather_mode,
+                       "numa": "rank bound to NUMA node %s of its GPU" % numa_node if numa_node is not None else "no NUMA node reported for the GPU (nothing bound)",
                        "l2": "inputs (%.0f GB/GPU) >> L2, no flush needed" % (C * N_SAMPLES * 4 / 1e9),
                        "timing": "CUDA events on the launching stream, max over ranks"},
             "frames_per_s": value * FRAMES_PER_CLIP,
@@ -472,6 +631,8 @@ def run_ours(args, rank, local_rank, world):
                     "api": "scrubjay_infer_batch (host pointers, pinned)"},
             "pcm16": pcm,
             "donut": donut,
+            "config3": config3, "config4": config4, "config5": config5,
+            "gather_check": gather_check,
             "single_clip": single,
             "gpu_launches": launches,
             "clocks": clk.summary(),
@@ -506,6 +667,8 @@ def main():
     ap.add_argument("--no-donut", dest="donut", action="store_false", help="skip the donut-path measurement")
     ap.add_argument("--donut-clips", type=int, default=500000)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--no-configs", dest="configs", action="store_false",
+                    help="skip BASELINE configs 3 (N = 1), 4 (N >= 2) and 5 (N = 8) at their named sizes")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 1)
