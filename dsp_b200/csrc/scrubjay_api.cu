@@ -941,7 +941,18 @@ extern "C" {
 
 // signals longer than the fused kernel's 96 frames, and the 64-sample-window variant, take the staged pipeline
 static bool donut_needs_staged(int variant, long n_samples) { return variant == SJ_DONUT_INO_F32 || n_samples > DN_WIN + (long)DN_HOP * (DN_MAX_TB - 1); }
-constexpr int kStagedMaxMid = 64;
+// Midpoints the staged classifier keeps per signal.  The reference evaluates EVERY midpoint (classifier.cpp:92-115), so the
+// capacity follows the signal: a cluster spans >= 0.15 s (>= 11 frames of hop 224, >= 43 of hop 56) and is followed by a
+// gap > 0.05 s, hence fewer than frames / 12 + 1 clusters; 4096 (the entry point's limit) covers 3 hours of audio.
+static int staged_max_mid(int variant, long n_samples)
+{
+    const long win = variant == SJ_DONUT_INO_F32 ? 64 : DN_WIN, hop = win - win / 8;
+    const long frames = n_samples >= win ? (n_samples - win) / hop + 1 : 1;
+    long mm = frames / 12 + 1;
+    if (mm < 8) mm = 8;
+    if (mm > 4096) mm = 4096;
+    return (int)mm;
+}
 
 int scrubjay_donut_classify_batch_dev(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samples, int variant,
                                       int32_t *d_labels, float *d_detail)
@@ -950,7 +961,7 @@ int scrubjay_donut_classify_batch_dev(scrubjay_ctx *c, const float *d_clips, lon
     if (!d_clips || !d_labels || n_clips < 0) return set_err(c, SJ_EINVAL, "NULL pointer or negative count");
     SJ_CUDA(c, cudaSetDevice(c->device));
     if (donut_needs_staged(variant, n_samples))
-        return scrubjay_donut_classify_long_dev(c, d_clips, n_clips, n_samples, variant, d_labels, d_detail, nullptr, kStagedMaxMid);
+        return scrubjay_donut_classify_long_dev(c, d_clips, n_clips, n_samples, variant, d_labels, d_detail, nullptr, staged_max_mid(variant, n_samples));
     int tb = 0, rc = donut_prepare(c, variant, n_samples, &tb);
     if (rc != SJ_OK) return rc;
     return donut_launch(c, d_clips, n_clips, n_samples, variant, tb, d_labels, d_detail);
@@ -985,7 +996,7 @@ int scrubjay_donut_classify_batch(scrubjay_ctx *c, const float *clips, long n_cl
         SJ_CUDA(c, cudaMemcpyAsync(c->d_donut_clips, clips + done * (long)n_samples, (size_t)n * n_samples * 4,
                                    cudaMemcpyHostToDevice, c->stream));
         rc = staged ? scrubjay_donut_classify_long_dev(c, c->d_donut_clips, n, n_samples, variant, c->d_donut_labels,
-                                                       c->d_donut_detail, nullptr, kStagedMaxMid)
+                                                       c->d_donut_detail, nullptr, staged_max_mid(variant, n_samples))
                     : donut_launch(c, c->d_donut_clips, n, n_samples, variant, tb, c->d_donut_labels, c->d_donut_detail);
         if (rc != SJ_OK) return rc;
         SJ_CUDA(c, cudaMemcpyAsync(labels + done, c->d_donut_labels, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));

@@ -329,3 +329,34 @@ def test_long_signals_match_unmodified_reference(secs):
     lh, dh = sj.donut_classify_batch(x, dsp_b200.DONUT_SYNC_F32)
     assert np.array_equal(lh, l32) and np.array_equal(dh, d32)
     assert dsp_b200.classify(x[0]) == l32[0]
+
+
+def test_long_recording_with_more_than_64_clusters_matches_the_unmodified_reference():
+    """the staged path used to keep 64 midpoints at most, and the drop-in find_midpoints() refused inputs above
+    21 536 samples although classify() takes them.  A 60 s recording with 100 bursts in the 1000-3000 Hz band (0.25 s on,
+    0.35 s off): every midpoint of the unmodified find_midpoints (sync/lib/classifier.cpp:433-598) must come back, through
+    the reference's own symbol names, and classify() must agree with the unmodified classify()."""
+    import dsp_b200
+    from donut_lib import DonutRef32, have_ref
+    assert have_ref(), "oracle/_ref not shipped"
+    fs, secs = 16000, 60
+    rng = np.random.default_rng(64)
+    t = np.arange(fs * secs) / fs
+    x = 0.002 * rng.uniform(-1, 1, t.size)
+    for k in range(100):
+        t0 = 0.1 + 0.6 * k
+        m = (t >= t0) & (t < t0 + 0.25)
+        f = 1400.0 + 12.0 * k
+        x[m] += 0.4 * np.sin(2 * np.pi * f * (t[m] - t0)) + 0.1 * np.sin(2 * np.pi * (f + 4200.0) * (t[m] - t0))
+    x = x.astype(np.float32)
+    ref = DonutRef32()
+    want = ref.midpoints(x)
+    assert len(want) > 64, "the test signal must have more clusters than the old cap (%d)" % len(want)
+    got = dsp_b200.find_midpoints(x)
+    assert got is not None and len(got) == len(want), (None if got is None else len(got), len(want))
+    assert np.allclose(got, want, rtol=0, atol=1e-6)
+    assert dsp_b200.classify(x) == ref.classify(x)
+    # the batched host entry point takes the same route (two copies of the recording)
+    sj = dsp_b200.ScrubJay(device=0, samplerate=16000)
+    labels, detail = sj.donut_classify_batch(np.stack([x, x]), dsp_b200.DONUT_SYNC_F32)
+    assert labels.tolist() == [ref.classify(x)] * 2 and detail[:, 0].tolist() == [float(len(want))] * 2
