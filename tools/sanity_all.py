@@ -40,3 +40,22 @@ for sr in (8000, 22050, 44100):
     lab = torch.empty(n, dtype=torch.int32, device="cuda")
     s2.infer_batch_dev(d, n, 16000, lab, None, None, None); torch.cuda.synchronize(); s2.close()
 print("generic ok")
+# round 2 paths: allocation-free entry point, non-default cepstrum parameters, donut groups of several clips in the
+# warp-specialised float kernel (and its unaligned form), the call-flavoured generator, the staged long-signal classifier
+lab = torch.empty(n, dtype=torch.int32, device="cuda"); ft = torch.empty((n, 40), device="cuda")
+sj.infer_batch_noalloc_dev(d, n, 16000, lab, None, None, ft)
+sj.infer_batch_noalloc_dev(d, 7, 5000, lab, None, None, ft)
+torch.cuda.synchronize(); print("noalloc ok")
+prm = dsp_b200.CepstrumParams(window=dsp_b200.WINDOW_HANN_SYMMETRIC, spectrum=dsp_b200.SPECTRUM_POWER, log_floor=1e-20)
+s3 = dsp_b200.ScrubJay(0, 16000, params=prm); s3.set_stream(torch.cuda.current_stream().cuda_stream)
+s3.infer_batch_dev(d, n, 16000, lab, None, None, ft); torch.cuda.synchronize(); s3.close(); print("params ok")
+m = 2500
+big = torch.empty((m, 16000), dtype=torch.float32, device="cuda")
+sj.synth_clips_dev(big, 0, m, 16000, flavour=dsp_b200.SYNTH_CALLS)
+lab = torch.empty(m, dtype=torch.int32, device="cuda"); det = torch.empty((m, 4), device="cuda")
+sj.donut_classify_batch_dev(big, m, 16000, 1, lab, det)
+odd = big.view(-1)[1:1 + 300 * 16001].view(300, 16001)  # unaligned rows
+sj.donut_classify_batch_dev(odd, 300, 16001, 1, lab, det)
+torch.cuda.synchronize(); print("donut ws ok", lab[:300].sum().item())
+long_sig = big.view(-1)[:2 * 200000].view(2, 200000).contiguous()
+sj.donut_classify_batch_dev(long_sig, 2, 200000, 1, lab, det); torch.cuda.synchronize(); print("donut long ok", det[:2, 0].tolist())
