@@ -734,7 +734,8 @@ constexpr size_t kSmem = kTabBytes + sizeof(float) * kIir * 2 * kGroup * kRS + s
 // spectrogram_column_exact_f32
 template <bool BAND>
 __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
-                                               GroupState *st, FftWarpState *fw, float *scratch, int lane, int c0)
+                                               GroupState *st, FftWarpState *fw, float *scratch, int lane, int c0,
+                                               const float2 (&tw)[15])
 {
     const int half = lane >> 4, h = lane & 15;
     const int clip = c0 + 8 * half, r = (BAND ? kGroup : 0) + clip;
@@ -779,12 +780,14 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
     __syncwarp();
 #pragma unroll
     for (int l = 4; l < 8; ++l) {
-        const int l1h = 1 << (l - 4), l1 = 16 << (l - 4);
+        const int l1h = 1 << (l - 4);
 #pragma unroll
         for (int i = 0; i < 16; ++i)
             if ((i & l1h) == 0) {
-                const int m = (i & (l1h - 1)) * 16 + h;
-                bfly(v[i], v[i + l1h], tab->bourke[l1 - 1 + m][0], tab->bourke[l1 - 1 + m][1]);
+                // twiddle (l1 - 1) + (i & (l1h - 1)) * 16 + h of PlainFFT's table: the same 15 pairs for every pass of this
+                // lane, held in registers for the whole kernel (they were 32 per-lane shared-memory loads per pass)
+                const float2 u = tw[(l1h - 1) + (i & (l1h - 1))];
+                bfly(v[i], v[i + l1h], u.x, u.y);
             }
     }
     // a = re^2 + im^2 of bins k = 16 hh + h <= 128 with the reference's operations (classifier.cpp:349-364); "/ U" and "* 2"
@@ -910,8 +913,13 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
             for (int t = 0; t < tb; ++t) {
                 if (t > 0) bar_sync(kBarEmpty + g, kPair); // the transform warps are done with frame t - 1
                 const int nnew = t == 0 ? DN_WIN : DN_HOP;
+#ifdef SJ_DONUT_SKIP_FILTER /* timing experiment only (results are wrong): the filter warps run the barrier protocol alone */
+                if (t == 0) for (int i = 0; i < 256; ++i) myrow[i] = 0.001f * (float)((i * 37 + lane * 11) & 63);
+                for (int i0 = 0; i0 < 0; i0 += 8 * kPre) {
+#else
 #pragma unroll 1
                 for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) {
+#endif
 #pragma unroll
                     for (int j = 0; j < kPre; ++j) {
                         const int i = i0 + 8 * j;
@@ -960,6 +968,16 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
         // ------------------------------------------------------------------ transform warps
         const int w = warp;
         FftWarpState *fw = fw_all + w;
+        float2 tw[15]; // this lane's twiddles of FFT stages 4..7 (lane & 15 = the low index digit after the transpose)
+        {
+            const int hh = lane & 15;
+            auto twid = [&](int l1, int q) { const int m = q * 16 + hh; return make_float2(tab->bourke[l1 - 1 + m][0], tab->bourke[l1 - 1 + m][1]); };
+            tw[0] = twid(16, 0);
+            tw[1] = twid(32, 0); tw[2] = twid(32, 1);
+            tw[3] = twid(64, 0); tw[4] = twid(64, 1); tw[5] = twid(64, 2); tw[6] = twid(64, 3);
+            tw[7] = twid(128, 0); tw[8] = twid(128, 1); tw[9] = twid(128, 2); tw[10] = twid(128, 3);
+            tw[11] = twid(128, 4); tw[12] = twid(128, 5); tw[13] = twid(128, 6); tw[14] = twid(128, 7);
+        }
         const float U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
         for (long r = 0;; ++r) {
             if (blockIdx.x + r * kIir * gridDim.x >= n_groups) break;
@@ -987,8 +1005,8 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
                         continue;
 #endif
-                        if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0);
-                        else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0);
+                        if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
+                        else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
                     }
                     if (t < tb - 1) {
                         __threadfence_block();
