@@ -698,43 +698,71 @@ namespace ws {
 #ifndef SJ_DONUT_IIR_WARPS
 #define SJ_DONUT_IIR_WARPS 4
 #endif
-constexpr int kIir = SJ_DONUT_IIR_WARPS; // filter warps = clip groups in flight per CTA
 #ifndef SJ_DONUT_FFT_WARPS
 #define SJ_DONUT_FFT_WARPS 8 /* measured (100 k clips): 8 warps 6.21 M clips/s (168 registers, no spill), 10: 6.04 M, 12: 6.03 M (128 registers) */
 #endif
-constexpr int kFft = SJ_DONUT_FFT_WARPS; // transform / epilogue warps
+// double: 255 registers allow 8 warps per SM, and a group's 32 rows of doubles take 66 KB of shared memory
+#ifndef SJ_DONUT_IIR_WARPS_F64
+#define SJ_DONUT_IIR_WARPS_F64 3
+#endif
+#ifndef SJ_DONUT_FFT_WARPS_F64
+#define SJ_DONUT_FFT_WARPS_F64 4 /* measured (100 k clips): 3 + 4 warps 2.83 M clips/s, 3 + 5: 2.70 M, 2 + 6: 2.39 M, 2 + 4: 2.43 M; round-1 kernel 2.70 M */
+#endif
 constexpr int kGroup = 16;         // clips per group (32 rows: lane = filter * 16 + clip)
-constexpr int kPasses = 2 * kGroup / 2; // passes per group frame: two rows each
-constexpr int kRS = 258;           // row stride in floats
-constexpr int kThreads = (kIir + kFft) * 32;
-constexpr int kBarFull = 1, kBarEmpty = 1 + kIir, kBarFft = 1 + 2 * kIir; // named barriers (0 = __syncthreads)
-static_assert(kBarFft < 16, "named barriers");
-
-struct GroupState {
-    float mean[2 * kGroup];                                       // per row: frame mean, summed sequentially like the reference
-    float min_in[kGroup], max_in[kGroup], min_ed[kGroup], max_ed[kGroup]; // band rows: min / max of a over the cells with Sxx > 0
-    uint32_t flags[kGroup][3];                                    // flag rows: frames with any cell above the dB threshold
-    int next_pass;                                                // passes of the current frame handed out so far (transform warps grab them)
-    int n_mid[kGroup];
-    float mids[kGroup][DN_MAX_MID];
+constexpr int kRS = 258;           // row stride in elements
+template <typename T> struct Cfg;
+template <> struct Cfg<float> {
+    static constexpr int kIir = SJ_DONUT_IIR_WARPS; // filter warps = clip groups in flight per CTA
+    static constexpr int kFft = SJ_DONUT_FFT_WARPS; // transform / epilogue warps
+    static constexpr int kPasses = 2 * kGroup / 2;  // passes per group frame: two rows each (16 lanes per row)
+    static constexpr int kStage = 2 * 16 * 17 * 2 / 32 * 32; // epilogue staging area = the transpose buffers
 };
-struct FftWarpState {
+template <> struct Cfg<double> {
+    static constexpr int kIir = SJ_DONUT_IIR_WARPS_F64;
+    static constexpr int kFft = SJ_DONUT_FFT_WARPS_F64;
+    static constexpr int kPasses = 2 * kGroup / 8;  // eight rows each (4 lanes per row)
+    static constexpr int kStage = 192;
+};
+template <typename T> constexpr int kThreadsT = (Cfg<T>::kIir + Cfg<T>::kFft) * 32;
+// named barriers (0 = __syncthreads): full[g] = 1 + g, empty[g] = 1 + kIir + g, transform warps = 1 + 2 kIir
+constexpr int kBarFull = 1;
+static_assert(1 + 2 * Cfg<float>::kIir < 16 && 1 + 2 * Cfg<double>::kIir < 16, "named barriers");
+
+template <typename T> struct GroupState {
+    T mean[2 * kGroup];                                       // per row: frame mean, summed sequentially like the reference
+    T min_in[kGroup], max_in[kGroup], min_ed[kGroup], max_ed[kGroup]; // band rows: min / max of a over the cells with Sxx > 0
+    uint32_t flags[kGroup][3];                                // flag rows: frames with any cell above the dB threshold
+    int next_pass;                                            // passes of the current frame handed out so far (transform warps grab them)
+    int n_mid[kGroup];
+    T mids[kGroup][DN_MAX_MID];
+};
+template <typename T> struct FftWarpState;
+template <> struct FftWarpState<float> {
     float2 xbuf[2][16 * 17]; // 16x16 transpose buffers of the exact float FFT (two frames per pass)
     float queue[64];         // band-sum epilogue: a values of the cells that passed the level test
+    __device__ float *stage() { return reinterpret_cast<float *>(xbuf); } // the transpose buffers are idle in the epilogue
+};
+template <> struct FftWarpState<double> {
+    double stage_buf[Cfg<double>::kStage]; // band-sum epilogue: staging area of the box cells
+    double queue[64];
+    __device__ double *stage() { return stage_buf; }
 };
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-constexpr size_t kTabBytes = (sizeof(SjDonutTables<float>) + 15) & ~size_t(15);
-constexpr size_t kSmem = kTabBytes + sizeof(float) * kIir * 2 * kGroup * kRS + sizeof(GroupState) * kIir + sizeof(FftWarpState) * kFft;
+template <typename T> constexpr size_t kTabBytesT = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
+template <typename T>
+constexpr size_t kSmemT = kTabBytesT<T> + sizeof(T) * Cfg<T>::kIir * 2 * kGroup * kRS + sizeof(GroupState<T>) * Cfg<T>::kIir +
+                          sizeof(FftWarpState<T>) * Cfg<T>::kFft;
+static_assert(kSmemT<float> <= 232448 && kSmemT<double> <= 232448, "shared memory per CTA");
 
 // one pass = spectrogram column t of two rows of one kind (BAND: 3000-7500 Hz rows whose cells are kept; otherwise the
 // 1000-3000 Hz rows that only flag frames), the clips c0 and c0 + 8 of the group; PlainFFT replayed as in
 // spectrogram_column_exact_f32
 template <bool BAND>
 __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
-                                               GroupState *st, FftWarpState *fw, float *scratch, int lane, int c0,
+                                               GroupState<float> *st, FftWarpState<float> *fw, float *scratch, int lane, int c0,
                                                const float2 (&tw)[15])
 {
     const int half = lane >> 4, h = lane & 15;
@@ -845,20 +873,133 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
     }
 }
 
-template <bool ALIGNED>
-__global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs a)
+// double: one pass = spectrogram column t of eight rows of one kind, 4 lanes per row (no bit-exact FFT to follow: FFTW's
+// order is unknown): 256-point real FFT as a 128-point complex FFT split 32 (register FFT per lane) x 4 (two shuffle
+// butterflies across the lane quad), untangling with the partner lane -- the arithmetic of donut_kernel<double>
+// (BAND is a run-time flag here, not a template parameter as in the float pass: the pass is ~3000 straight-line
+// instructions = 50 KB of code, and two copies streaming through the 32 KB L1.5 instruction cache at the same time starved
+// every warp of the SM of instructions -- 3.3 "no instruction" stall cycles per issued instruction, profiles/r2l)
+__device__ __forceinline__ void pass_f64(const bool BAND, const double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
+                                         GroupState<double> *st, double *scratch, int lane, int c0)
 {
-    typedef float T;
+    typedef double T;
+    typedef double2 T2;
+    const int q = lane >> 2, g = lane & 3;
+    const int k2 = ((g & 1) << 1) | (g >> 1); // which quarter of the 128-point spectrum this lane ends up holding
+    // the eight clips of a pass are dealt to the lane quads so that the two rows of a quarter-warp lie four rows apart:
+    // with the odd row stride (129 16-byte units) their 8 x 16-byte reads fall on eight distinct bank groups
+    const int clip = c0 + 4 * (q & 1) + (q >> 1), r = (BAND ? kGroup : 0) + clip;
+    const T *rowp = rows + r * kRS;
+    T2 v[32];
+    const T mean = st->mean[r];
+#pragma unroll
+    for (int n = 0; n < 32; ++n) {
+        v[n] = *reinterpret_cast<const T2 *>(rowp + ((pos + 8 * n + 2 * g) & 255));
+        const T2 wv = *reinterpret_cast<const T2 *>(&tab->window[8 * n + 2 * g]);
+        v[n].x = mul_rn(sub_rn(v[n].x, mean), wv.x);
+        v[n].y = mul_rn(sub_rn(v[n].y, mean), wv.y);
+    }
+    fft32(v); // over n: Y_g[k1] in v[SJ_BREV32(k1)]
+#pragma unroll
+    for (int k1 = 1; k1 < 32; ++k1) {
+        const T wr = tab->tw128[k1][g][0], wi = tab->tw128[k1][g][1];
+        T2 &y = v[SJ_BREV32(k1)];
+        const T yr = y.x * wr - y.y * wi;
+        y.y = y.x * wi + y.y * wr;
+        y.x = yr;
+    }
+    // 4-point DFT across the lane quad (g = n mod 4): afterwards this lane holds Z[k1 + 32*k2]
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        T ox = __shfl_xor_sync(kFull, v[i].x, 2), oy = __shfl_xor_sync(kFull, v[i].y, 2);
+        if (g & 2) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
+        if (g == 3) { const T tx = v[i].y; v[i].y = -v[i].x; v[i].x = tx; } // times -i
+        ox = __shfl_xor_sync(kFull, v[i].x, 1); oy = __shfl_xor_sync(kFull, v[i].y, 1);
+        if (g & 1) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
+    }
+    // untangle the real FFT; a = re^2 + im^2 ("/ U" and "* 2" are applied later, only where a value is needed)
+    const T a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
+    T *cell = scratch + (size_t(clip) * tb + t) * DN_BINS;
+    T lmin = (T)INFINITY, lmax = 0, emin = (T)INFINITY, emax = 0;
+    bool any = false;
+    auto emit = [&](int bin, T x2, T y2) { // (x2, y2) = 2 X[bin]
+        const T re = (T)0.5 * x2, im = (T)0.5 * y2;
+        const T av = add_rn(mul_rn(re, re), mul_rn(im, im));
+        const bool edge = bin == 0 || bin == DN_BINS - 1;
+        if (BAND) {
+            cell[bin] = av;
+            if (av >= a_pos) {
+                if (edge) { emin = av < emin ? av : emin; emax = av > emax ? av : emax; }
+                else { lmin = av < lmin ? av : lmin; lmax = av > lmax ? av : lmax; }
+            }
+        } else any = any || (av >= (edge ? a_thr_e : a_thr_i));
+    };
+    auto pair = [&](T2 A, T bx, T by, int k, T &xa, T &ya, T &xb, T &yb) {
+        // A = Z[k], (bx, by) = Z[128 - k]; returns 2 X[k] and 2 conj-partner for bin 128 - k
+        const T ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
+        const T wr = tab->tw256[k][0], wi = tab->tw256[k][1];
+        const T tx = wr * dy + wi * dx, ty = wi * dy - wr * dx;
+        xa = ex + tx; ya = ey + ty; xb = ex - tx; yb = ey - ty;
+    };
+#pragma unroll
+    for (int k1 = 1; k1 < 16; ++k1) {
+        const T2 S = v[SJ_BREV32(32 - k1)];
+        const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
+        const int k = k1 + 32 * k2;
+        T xa, ya, xb, yb;
+        pair(v[SJ_BREV32(k1)], bx, by, k, xa, ya, xb, yb);
+        emit(k, xa, ya);
+        emit(DN_WIN / 2 - k, xb, yb);
+    }
+    {   // k1 = 16: partner Z[16 + 32 (3 - k2)] sits in the mirror lane, same register
+        const T2 S = v[SJ_BREV32(16)];
+        const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
+        T xa, ya, xb, yb;
+        pair(S, bx, by, 16 + 32 * k2, xa, ya, xb, yb);
+        emit(16 + 32 * k2, xa, ya);
+    }
+    {   // k1 = 0: bins 0, 32, 64, 96 (and 128 from the k2 = 0 lane)
+        const T2 S = v[0];
+        T bx = __shfl_xor_sync(kFull, S.x, 1), by = __shfl_xor_sync(kFull, S.y, 1);
+        if (g < 2) { bx = S.x; by = S.y; } // k2 = 0 and k2 = 2 are their own partners
+        T xa, ya, xb, yb;
+        pair(S, bx, by, 32 * k2, xa, ya, xb, yb);
+        emit(32 * k2, xa, ya);
+        if (k2 == 0) emit(DN_WIN / 2, xb, yb);
+    }
+    if (BAND) { // combine the quad's partial results; the quad leader updates the clip's state
+        lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 1)); lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 2));
+        lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 1)); lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 2));
+        emin = fmin(emin, __shfl_xor_sync(kFull, emin, 1)); emin = fmin(emin, __shfl_xor_sync(kFull, emin, 2));
+        emax = fmax(emax, __shfl_xor_sync(kFull, emax, 1)); emax = fmax(emax, __shfl_xor_sync(kFull, emax, 2));
+        if (g == 0) {
+            st->min_in[clip] = fmin(st->min_in[clip], lmin);
+            st->max_in[clip] = fmax(st->max_in[clip], lmax);
+            st->min_ed[clip] = fmin(st->min_ed[clip], emin);
+            st->max_ed[clip] = fmax(st->max_ed[clip], emax);
+        }
+    } else {
+        const unsigned ballot = __ballot_sync(kFull, any);
+        if (g == 0 && ((ballot >> (4 * q)) & 0xFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
+    }
+}
+
+template <typename T, bool ALIGNED>
+__global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonutArgs a)
+{
+    typedef typename V2<T>::type T2;
+    constexpr int kIir = Cfg<T>::kIir, kFft = Cfg<T>::kFft, kPasses = Cfg<T>::kPasses, kThreads = kThreadsT<T>;
+    constexpr int kBarEmpty = 1 + kIir, kBarFft = 1 + 2 * kIir;
     extern __shared__ __align__(16) unsigned char smem[];
-    SjDonutTables<float> *tab = reinterpret_cast<SjDonutTables<float> *>(smem);
-    float *rows_all = reinterpret_cast<float *>(smem + kTabBytes);
-    GroupState *gs_all = reinterpret_cast<GroupState *>(rows_all + kIir * 2 * kGroup * kRS);
-    FftWarpState *fw_all = reinterpret_cast<FftWarpState *>(gs_all + kIir);
+    SjDonutTables<T> *tab = reinterpret_cast<SjDonutTables<T> *>(smem);
+    T *rows_all = reinterpret_cast<T *>(smem + kTabBytesT<T>);
+    GroupState<T> *gs_all = reinterpret_cast<GroupState<T> *>(rows_all + kIir * 2 * kGroup * kRS);
+    FftWarpState<T> *fw_all = reinterpret_cast<FftWarpState<T> *>(gs_all + kIir);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
-        for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<float>) / 4); i += kThreads) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kThreads) dst[i] = __ldg(src + i);
     }
     __syncthreads();
 
@@ -871,13 +1012,13 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
     if (warp >= kFft) {
         // ------------------------------------------------------------------ filter warp: group q = g, g + kIir, ...
         const int g = warp - kFft;
-        float *rows = rows_all + g * 2 * kGroup * kRS;
-        GroupState *st = gs_all + g;
+        T *rows = rows_all + g * 2 * kGroup * kRS;
+        GroupState<T> *st = gs_all + g;
         const int f = lane >> 4, ci = lane & 15; // row = lane = filter * 16 + clip
-        float ca[9], cb[9];
+        T ca[9], cb[9];
 #pragma unroll
         for (int j = 0; j < 9; ++j) { ca[j] = tab->a[f][j]; cb[j] = tab->b[f][j]; }
-        float *myrow = rows + lane * kRS;
+        T *myrow = rows + lane * kRS;
         for (long q = g;; q += kIir) {
             const long gid = blockIdx.x + q * gridDim.x;
             if (gid >= n_groups) break;
@@ -887,12 +1028,12 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
             const float *src = a.clips_per_row > 0
                                    ? a.clips + (clip / a.clips_per_row) * a.row_stride + (clip % a.clips_per_row) * (long)n_samples
                                    : a.clips + clip * (long)n_samples;
-            float w[8];
+            T w[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) w[j] = 0.f;
+            for (int j = 0; j < 8; ++j) w[j] = 0;
             if (lane < kGroup) {
-                st->min_in[lane] = st->min_ed[lane] = INFINITY;
-                st->max_in[lane] = st->max_ed[lane] = 0.f;
+                st->min_in[lane] = st->min_ed[lane] = (T)INFINITY;
+                st->max_in[lane] = st->max_ed[lane] = 0;
                 st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
             }
 #ifndef SJ_DONUT_PRE
@@ -908,13 +1049,13 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                     ring[j][1] = __ldg(reinterpret_cast<const float4 *>(src + 8 * j + 4));
                 }
             }
-            float acc_cur = 0.f, acc_next = 0.f;
+            T acc_cur = 0, acc_next = 0;
             int pos = 0, sample = 0;
             for (int t = 0; t < tb; ++t) {
                 if (t > 0) bar_sync(kBarEmpty + g, kPair); // the transform warps are done with frame t - 1
                 const int nnew = t == 0 ? DN_WIN : DN_HOP;
 #ifdef SJ_DONUT_SKIP_FILTER /* timing experiment only (results are wrong): the filter warps run the barrier protocol alone */
-                if (t == 0) for (int i = 0; i < 256; ++i) myrow[i] = 0.001f * (float)((i * 37 + lane * 11) & 63);
+                if (t == 0) for (int i = 0; i < 256; ++i) myrow[i] = (T)0.001 * (T)((i * 37 + lane * 11) & 63);
                 for (int i0 = 0; i0 < 0; i0 += 8 * kPre) {
 #else
 #pragma unroll 1
@@ -923,7 +1064,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 #pragma unroll
                     for (int j = 0; j < kPre; ++j) {
                         const int i = i0 + 8 * j;
-                        float x[8], y[8];
+                        T x[8], y[8];
                         if (ALIGNED) {
                             const float4 u0 = ring[j][0], u1 = ring[j][1];
                             x[0] = u0.x; x[1] = u0.y; x[2] = u0.z; x[3] = u0.w; x[4] = u1.x; x[5] = u1.y; x[6] = u1.z; x[7] = u1.w;
@@ -939,7 +1080,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 #pragma unroll
                         for (int k = 0; k < 8; ++k) y[k] = x[k];
 #else
-                        iir8(x, w, ca, cb, y); // the packed overload: (a[j] w, b[j] w) from one FMUL2 for even j
+                        iir8(x, w, ca, cb, y); // float: the packed overload, (a[j] w, b[j] w) from one FMUL2 for even j
 #endif
                         // frame mean: "sum += vReal[i]" in sample order (classifier.cpp:320-324), kept exact
                         const bool tail = i >= nnew - 32; // the last 32 samples of a frame open the next frame
@@ -948,17 +1089,17 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                             acc_cur = add_rn(acc_cur, y[k]);
                             if (tail) acc_next = add_rn(acc_next, y[k]);
                         }
-                        float *dst = myrow + ((pos + i) & 255);
+                        T *dst = myrow + ((pos + i) & 255);
 #pragma unroll
-                        for (int k = 0; k < 8; k += 2) *reinterpret_cast<float2 *>(dst + k) = make_float2(y[k], y[k + 1]);
+                        for (int k = 0; k < 8; k += 2) *reinterpret_cast<T2 *>(dst + k) = T2{y[k], y[k + 1]};
                     }
                 }
                 sample += nnew;
                 pos = (pos + nnew) & 255;
-                st->mean[lane] = div_rn(acc_cur, (float)DN_WIN);
+                st->mean[lane] = div_rn(acc_cur, (T)DN_WIN);
                 if (lane == 0) st->next_pass = 0;
                 acc_cur = acc_next;
-                acc_next = 0.f;
+                acc_next = 0;
                 __threadfence_block();
                 bar_arrive(kBarFull + g, kPair);
             }
@@ -967,9 +1108,9 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
     } else {
         // ------------------------------------------------------------------ transform warps
         const int w = warp;
-        FftWarpState *fw = fw_all + w;
-        float2 tw[15]; // this lane's twiddles of FFT stages 4..7 (lane & 15 = the low index digit after the transpose)
-        {
+        FftWarpState<T> *fw = fw_all + w;
+        float2 tw[15]; // float: this lane's twiddles of FFT stages 4..7 (lane & 15 = the low index digit after the transpose)
+        if constexpr (sizeof(T) == 4) {
             const int hh = lane & 15;
             auto twid = [&](int l1, int q) { const int m = q * 16 + hh; return make_float2(tab->bourke[l1 - 1 + m][0], tab->bourke[l1 - 1 + m][1]); };
             tw[0] = twid(16, 0);
@@ -978,7 +1119,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
             tw[7] = twid(128, 0); tw[8] = twid(128, 1); tw[9] = twid(128, 2); tw[10] = twid(128, 3);
             tw[11] = twid(128, 4); tw[12] = twid(128, 5); tw[13] = twid(128, 6); tw[14] = twid(128, 7);
         }
-        const float U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
+        const T U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
         for (long r = 0;; ++r) {
             if (blockIdx.x + r * kIir * gridDim.x >= n_groups) break;
             for (int t = 0; t < tb; ++t) {
@@ -989,24 +1130,29 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                     if (gid >= n_groups) break;
                     const long base = gid * cpg;
                     const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
-                    const float *rows = rows_all + g * 2 * kGroup * kRS;
-                    GroupState *st = gs_all + g;
-                    float *scratch = reinterpret_cast<float *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
+                    const T *rows = rows_all + g * 2 * kGroup * kRS;
+                    GroupState<T> *st = gs_all + g;
+                    T *scratch = reinterpret_cast<T *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
                     bar_sync(kBarFull + g, kPair);
-                    // 16 passes: p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8
+                    // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
+                    // double: 4 passes, p < 2 the flag rows; pass j of a kind holds the clips 8 j .. 8 j + 7.
                     // (handed out through a counter, so any number of transform warps shares them evenly)
                     for (;;) {
                         int p = 0;
                         if (lane == 0) p = atomicAdd(&st->next_pass, 1);
                         p = __shfl_sync(kFull, p, 0);
                         if (p >= kPasses) break;
-                        const int c0 = p & 7;
+                        const int c0 = sizeof(T) == 4 ? (p & 7) : 8 * (p & 1);
                         if (c0 >= nact) continue;
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
                         continue;
 #endif
-                        if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
-                        else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
+                        if constexpr (sizeof(T) == 4) {
+                            if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
+                            else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
+                        } else {
+                            pass_f64(p >= 2, rows, pos, t, tb, tab, st, scratch, lane, c0);
+                        }
                     }
                     if (t < tb - 1) {
                         __threadfence_block();
@@ -1089,8 +1235,8 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                             }
                             const T *scr = scratch + size_t(c2) * tb * DN_BINS;
                             T *qu = fw->queue;
-                            T *stage = reinterpret_cast<T *>(fw->xbuf); // the warp's transpose buffers are idle in the epilogue
-                            constexpr int kStage = (int)(sizeof(fw->xbuf) / sizeof(T)) / 32 * 32;
+                            T *stage = fw->stage();
+                            constexpr int kStage = Cfg<T>::kStage;
                             auto box = [&](int band, T halfw, T midpoint) -> T {
                                 const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
                                 const T tlo = sub_rn(midpoint, halfw), thi = add_rn(midpoint, halfw);
@@ -1184,12 +1330,20 @@ template <typename T> size_t smem_total()
 
 } // namespace
 
-// A/B switch: SCRUBJAY_DONUT_LEGACY=1 keeps the round-1 float kernel (CTA-wide barriers, warp 0 filters alone)
-bool sj_donut_legacy_f32()
+// A/B switch: SCRUBJAY_DONUT_LEGACY=1 keeps the round-1 kernels (CTA-wide barriers, warp 0 filters alone) for both
+// precisions, =f32 / =f64 for one of them
+static int donut_legacy_mask()
 {
-    static const bool legacy = [] { const char *e = getenv("SCRUBJAY_DONUT_LEGACY"); return e && e[0] == '1'; }();
-    return legacy;
+    static const int mask = [] {
+        const char *e = getenv("SCRUBJAY_DONUT_LEGACY");
+        if (!e || !e[0] || e[0] == '0') return 0;
+        if (e[0] == 'f') return e[1] == '6' ? 2 : 1;
+        return 3;
+    }();
+    return mask;
 }
+bool sj_donut_legacy_f32() { return donut_legacy_mask() & 1; }
+bool sj_donut_legacy(bool f64) { return donut_legacy_mask() & (f64 ? 2 : 1); }
 
 cudaError_t sj_donut_setup()
 {
@@ -1200,14 +1354,17 @@ cudaError_t sj_donut_setup()
     SJ_DN_ATTR(float, true, false); SJ_DN_ATTR(float, false, false); SJ_DN_ATTR(float, true, true); SJ_DN_ATTR(float, false, true);
     SJ_DN_ATTR(double, true, false); SJ_DN_ATTR(double, false, false); SJ_DN_ATTR(double, true, true); SJ_DN_ATTR(double, false, true);
 #undef SJ_DN_ATTR
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::donut_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::kSmem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ws::donut_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::kSmem);
+#define SJ_WS_ATTR(T, AL)                                                                                              \
+    if (e == cudaSuccess)                                                                                              \
+    e = cudaFuncSetAttribute(ws::donut_ws_kernel<T, AL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws::kSmemT<T>)
+    SJ_WS_ATTR(float, true); SJ_WS_ATTR(float, false); SJ_WS_ATTR(double, true); SJ_WS_ATTR(double, false);
+#undef SJ_WS_ATTR
     return e;
 }
 
 int sj_donut_grid(int num_sms, bool f64)
 {
-    if (!f64 && !sj_donut_legacy_f32()) return num_sms; // warp-specialised float kernel: one persistent CTA per SM
+    if (!sj_donut_legacy(f64)) return num_sms; // warp-specialised kernels: one persistent CTA per SM
     int per_sm = 0;
     if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true, false>, DnWarps<double>::value * 32, smem_total<double>());
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true, false>, DnWarps<float>::value * 32, smem_total<float>());
@@ -1217,28 +1374,33 @@ int sj_donut_grid(int num_sms, bool f64)
 
 size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
 {
-    if (!f64 && !sj_donut_legacy_f32()) return size_t(ws::kIir) * ws::kGroup * tb * DN_BINS * 4;
+    if (!sj_donut_legacy(f64))
+        return size_t(f64 ? ws::Cfg<double>::kIir : ws::Cfg<float>::kIir) * ws::kGroup * tb * DN_BINS * (f64 ? 8 : 4);
     return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
+}
+
+template <typename T> static cudaError_t launch_ws(SjDonutArgs a, int grid, cudaStream_t stream)
+{
+    // groups of up to 16 clips, kIir in flight per CTA; small batches are spread over the CTAs in smaller groups
+    constexpr int kIir = ws::Cfg<T>::kIir;
+    long cpg = (a.n_clips + (long)grid * kIir - 1) / ((long)grid * kIir);
+    if (cpg > ws::kGroup) cpg = ws::kGroup;
+    if (cpg < 1) cpg = 1;
+    a.clips_per_cta = (int)cpg;
+    const long groups = (a.n_clips + cpg - 1) / cpg;
+    if (groups < grid) grid = (int)groups;
+    const bool al = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
+                    (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
+    if (al) ws::donut_ws_kernel<T, true><<<grid, ws::kThreadsT<T>, ws::kSmemT<T>, stream>>>(a);
+    else ws::donut_ws_kernel<T, false><<<grid, ws::kThreadsT<T>, ws::kSmemT<T>, stream>>>(a);
+    return cudaGetLastError();
 }
 
 cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int grid, cudaStream_t stream)
 {
     if (a_in.n_clips <= 0) return cudaSuccess;
     SjDonutArgs a = a_in;
-    if (!f64 && !sj_donut_legacy_f32()) {
-        // groups of up to 32 clips, two in flight per CTA; small batches are spread over the CTAs in smaller groups
-        long cpg = (a.n_clips + (long)grid * ws::kIir - 1) / ((long)grid * ws::kIir);
-        if (cpg > ws::kGroup) cpg = ws::kGroup;
-        if (cpg < 1) cpg = 1;
-        a.clips_per_cta = (int)cpg;
-        const long groups = (a.n_clips + cpg - 1) / cpg;
-        if (groups < grid) grid = (int)groups;
-        const bool al = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
-                        (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
-        if (al) ws::donut_ws_kernel<true><<<grid, ws::kThreads, ws::kSmem, stream>>>(a);
-        else ws::donut_ws_kernel<false><<<grid, ws::kThreads, ws::kSmem, stream>>>(a);
-        return cudaGetLastError();
-    }
+    if (!sj_donut_legacy(f64)) return f64 ? launch_ws<double>(a, grid, stream) : launch_ws<float>(a, grid, stream);
     long cpc = (a.n_clips + grid - 1) / grid; // spread small batches over the resident CTAs
     if (cpc > DN_CLIPS_PER_WARP) cpc = DN_CLIPS_PER_WARP;
     if (cpc < 1) cpc = 1;

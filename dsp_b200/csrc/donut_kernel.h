@@ -67,5 +67,6 @@ void sj_donut_default_params(SjDonutParams *p, int variant); // 0: classifier.c 
 int sj_donut_grid(int num_sms, bool f64);
 size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64);
 cudaError_t sj_donut_setup();
-bool sj_donut_legacy_f32(); // SCRUBJAY_DONUT_LEGACY=1: the round-1 float kernel instead of the warp-specialised one
+bool sj_donut_legacy_f32(); // SCRUBJAY_DONUT_LEGACY=1 (both precisions), =f32, =f64: the round-1 kernels instead of the warp-specialised ones
+bool sj_donut_legacy(bool f64);
 cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream_t stream);
