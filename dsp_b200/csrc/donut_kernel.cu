@@ -701,12 +701,12 @@ namespace ws {
 #ifndef SJ_DONUT_FFT_WARPS
 #define SJ_DONUT_FFT_WARPS 8 /* measured (100 k clips): 8 warps 6.21 M clips/s (168 registers, no spill), 10: 6.04 M, 12: 6.03 M (128 registers) */
 #endif
-// double: 255 registers allow 8 warps per SM, and a group's 32 rows of doubles take 66 KB of shared memory
+// double: a group's 32 rows of doubles take 66 KB of shared memory, so three groups are in flight
 #ifndef SJ_DONUT_IIR_WARPS_F64
 #define SJ_DONUT_IIR_WARPS_F64 3
 #endif
 #ifndef SJ_DONUT_FFT_WARPS_F64
-#define SJ_DONUT_FFT_WARPS_F64 4 /* measured (100 k clips): 3 + 4 warps 2.83 M clips/s, 3 + 5: 2.70 M, 2 + 6: 2.39 M, 2 + 4: 2.43 M; round-1 kernel 2.70 M */
+#define SJ_DONUT_FFT_WARPS_F64 9 /* measured (100 k clips, 8 lanes per row): 3 + 4 warps 3.26 M clips/s (254 registers), 3 + 5: 3.20 M, 3 + 9: 3.70 M (168), 3 + 13: 3.42 M (128, spills); round-1 kernel 2.70 M */
 #endif
 constexpr int kGroup = 16;         // clips per group (32 rows: lane = filter * 16 + clip)
 constexpr int kRS = 258;           // row stride in elements
@@ -720,9 +720,10 @@ template <> struct Cfg<float> {
 template <> struct Cfg<double> {
     static constexpr int kIir = SJ_DONUT_IIR_WARPS_F64;
     static constexpr int kFft = SJ_DONUT_FFT_WARPS_F64;
-    static constexpr int kPasses = 2 * kGroup / 8;  // eight rows each (4 lanes per row)
-    static constexpr int kStage = 192;
+    static constexpr int kPasses = 2 * kGroup / 4;  // four rows each (8 lanes per row)
+    static constexpr int kStage = 512;              // epilogue staging area: a slice of the group's idle rows, per transform warp
 };
+static_assert((64 + Cfg<double>::kStage) * Cfg<double>::kFft <= 2 * kGroup * kRS, "epilogue slices of the rows");
 template <typename T> constexpr int kThreadsT = (Cfg<T>::kIir + Cfg<T>::kFft) * 32;
 // named barriers (0 = __syncthreads): full[g] = 1 + g, empty[g] = 1 + kIir + g, transform warps = 1 + 2 kIir
 constexpr int kBarFull = 1;
@@ -742,10 +743,8 @@ template <> struct FftWarpState<float> {
     float queue[64];         // band-sum epilogue: a values of the cells that passed the level test
     __device__ float *stage() { return reinterpret_cast<float *>(xbuf); } // the transpose buffers are idle in the epilogue
 };
-template <> struct FftWarpState<double> {
-    double stage_buf[Cfg<double>::kStage]; // band-sum epilogue: staging area of the box cells
-    double queue[64];
-    __device__ double *stage() { return stage_buf; }
+template <> struct FftWarpState<double> { // nothing: the double pass transposes through the rows, and the epilogue's queue
+    double pad[2];                        // and staging area are slices of the group's rows, idle after the last frame
 };
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -873,59 +872,76 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
     }
 }
 
-// double: one pass = spectrogram column t of eight rows of one kind, 4 lanes per row (no bit-exact FFT to follow: FFTW's
-// order is unknown): 256-point real FFT as a 128-point complex FFT split 32 (register FFT per lane) x 4 (two shuffle
-// butterflies across the lane quad), untangling with the partner lane -- the arithmetic of donut_kernel<double>
-// (BAND is a run-time flag here, not a template parameter as in the float pass: the pass is ~3000 straight-line
-// instructions = 50 KB of code, and two copies streaming through the 32 KB L1.5 instruction cache at the same time starved
-// every warp of the SM of instructions -- 3.3 "no instruction" stall cycles per issued instruction, profiles/r2l)
-__device__ __forceinline__ void pass_f64(const bool BAND, const double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
+// double: one pass = spectrogram column t of four rows of one kind, 8 lanes per row (no bit-exact FFT to follow: FFTW's
+// order is unknown).  The 256-point real FFT is a 128-point complex FFT of z[n] = x[2n] + i x[2n+1], split 16 x 8:
+//   lane l of a row holds z[l + 8m], m = 0..15: FFT16 over m in registers -> Y_l[k1]; times W128^(l k1);
+//   an 8 x 16 transpose (in two halves of 8 x 8) -> lane j holds T_l[j] and T_l[j + 8] for l = 0..7; two FFT8 over l ->
+//   Z[k], k = j + 8c, c = 0..15, in lane j; the real-FFT untangling pairs Z[k] with Z[128 - k] = element 15 - c of lane 8 - j.
+// The transposes go through the part of the row's own circular buffer that the next hop overwrites anyway (224 of the
+// 256 samples; the transform warps own the rows until they signal "empty"): no shared memory besides the rows.
+// A pass is ~900 instructions (14 KB of code) against the ~3100 (50 KB) of the round-1 scheme (4 lanes per row, FFT32 per
+// lane, two shuffle butterflies across the lane quad), which did not fit the 32 KB instruction cache: 3.3 "no instruction"
+// stall cycles per issued instruction with warps at different places of the pass (profiles/r2l_*).
+// (BAND is a run-time flag, not a template parameter as in the float pass: one copy of the code.)
+__device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
                                          GroupState<double> *st, double *scratch, int lane, int c0)
 {
     typedef double T;
     typedef double2 T2;
-    const int q = lane >> 2, g = lane & 3;
-    const int k2 = ((g & 1) << 1) | (g >> 1); // which quarter of the 128-point spectrum this lane ends up holding
-    // the eight clips of a pass are dealt to the lane quads so that the two rows of a quarter-warp lie four rows apart:
-    // with the odd row stride (129 16-byte units) their 8 x 16-byte reads fall on eight distinct bank groups
-    const int clip = c0 + 4 * (q & 1) + (q >> 1), r = (BAND ? kGroup : 0) + clip;
-    const T *rowp = rows + r * kRS;
-    T2 v[32];
+    const int q = lane >> 3, l = lane & 7;
+    const int clip = c0 + q, r = (BAND ? kGroup : 0) + clip;
+    T *rowp = rows + r * kRS;
+    T2 v[16];
     const T mean = st->mean[r];
 #pragma unroll
-    for (int n = 0; n < 32; ++n) {
-        v[n] = *reinterpret_cast<const T2 *>(rowp + ((pos + 8 * n + 2 * g) & 255));
-        const T2 wv = *reinterpret_cast<const T2 *>(&tab->window[8 * n + 2 * g]);
-        v[n].x = mul_rn(sub_rn(v[n].x, mean), wv.x);
-        v[n].y = mul_rn(sub_rn(v[n].y, mean), wv.y);
+    for (int m = 0; m < 16; ++m) { // the 8 lanes of a row read 8 consecutive 16-byte units: conflict-free
+        v[m] = *reinterpret_cast<const T2 *>(rowp + ((pos + 2 * l + 16 * m) & 255));
+        const T2 wv = *reinterpret_cast<const T2 *>(&tab->window[2 * l + 16 * m]);
+        v[m].x = mul_rn(sub_rn(v[m].x, mean), wv.x);
+        v[m].y = mul_rn(sub_rn(v[m].y, mean), wv.y);
     }
-    fft32(v); // over n: Y_g[k1] in v[SJ_BREV32(k1)]
+    __syncwarp(); // every lane has its samples: the row's first 224 positions are free from here on
+    sj_fft16d(v); // over m: Y_l[k1] in v[SJ_BREV16(k1)]
 #pragma unroll
-    for (int k1 = 1; k1 < 32; ++k1) {
-        const T wr = tab->tw128[k1][g][0], wi = tab->tw128[k1][g][1];
-        T2 &y = v[SJ_BREV32(k1)];
+    for (int k1 = 1; k1 < 16; ++k1) { // W128^(l k1) = W256^(2 e) for e = l k1 < 64, minus that of e - 64 otherwise
+        const int e = l * k1;
+        const T2 w0 = *reinterpret_cast<const T2 *>(tab->tw256[2 * (e & 63)]);
+        const int flip = (e & 64) << 25; // sign bit of the high word
+        const T wr = __hiloint2double(__double2hiint(w0.x) ^ flip, __double2loint(w0.x));
+        const T wi = __hiloint2double(__double2hiint(w0.y) ^ flip, __double2loint(w0.y));
+        T2 &y = v[SJ_BREV16(k1)];
         const T yr = y.x * wr - y.y * wi;
         y.y = y.x * wi + y.y * wr;
         y.x = yr;
     }
-    // 4-point DFT across the lane quad (g = n mod 4): afterwards this lane holds Z[k1 + 32*k2]
+    // transpose, half by half: element (l, k1) at unit 9 l + (k1 & 7) of the row's free part (16-byte units; the odd
+    // stride keeps the column writes of the 8 lanes and their row reads on distinct bank groups)
+    T2 w[16]; // w[8 h + l'] = T_l'[j + 8 h]
+    const int sbase = pos + 18 * l, lbase = pos + 2 * l;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-        T ox = __shfl_xor_sync(kFull, v[i].x, 2), oy = __shfl_xor_sync(kFull, v[i].y, 2);
-        if (g & 2) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
-        if (g == 3) { const T tx = v[i].y; v[i].y = -v[i].x; v[i].x = tx; } // times -i
-        ox = __shfl_xor_sync(kFull, v[i].x, 1); oy = __shfl_xor_sync(kFull, v[i].y, 1);
-        if (g & 1) { v[i].x = ox - v[i].x; v[i].y = oy - v[i].y; } else { v[i].x += ox; v[i].y += oy; }
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) *reinterpret_cast<T2 *>(rowp + ((sbase + 2 * k) & 255)) = v[SJ_BREV16(8 * h + k)];
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) w[8 * h + k] = *reinterpret_cast<const T2 *>(rowp + ((lbase + 18 * k) & 255));
+        __syncwarp();
     }
-    // untangle the real FFT; a = re^2 + im^2 ("/ U" and "* 2" are applied later, only where a value is needed)
+    {
+        T2(&u0)[8] = *reinterpret_cast<T2(*)[8]>(&w[0]);
+        T2(&u1)[8] = *reinterpret_cast<T2(*)[8]>(&w[8]);
+        sj_fft8d(u0); // over l: Z[j + 16 k2] in w[SJ_BREV8(k2)]
+        sj_fft8d(u1); // Z[j + 8 + 16 k2] in w[8 + SJ_BREV8(k2)]
+    }
+    // Z[j + 8 c] = w[ZI(c)]
+#define SJ_ZI(c) ((((c) & 1) << 3) + SJ_BREV8((c) >> 1))
     const T a_thr_e = tab->a_thr[0], a_thr_i = tab->a_thr[1], a_pos = tab->a_pos;
     T *cell = scratch + (size_t(clip) * tb + t) * DN_BINS;
     T lmin = (T)INFINITY, lmax = 0, emin = (T)INFINITY, emax = 0;
     bool any = false;
-    auto emit = [&](int bin, T x2, T y2) { // (x2, y2) = 2 X[bin]
+    auto emit = [&](int bin, bool edge, T x2, T y2) { // (x2, y2) = 2 X[bin]; a = re^2 + im^2 ("/ U", "* 2" applied later)
         const T re = (T)0.5 * x2, im = (T)0.5 * y2;
         const T av = add_rn(mul_rn(re, re), mul_rn(im, im));
-        const bool edge = bin == 0 || bin == DN_BINS - 1;
         if (BAND) {
             cell[bin] = av;
             if (av >= a_pos) {
@@ -935,44 +951,39 @@ __device__ __forceinline__ void pass_f64(const bool BAND, const double *rows, in
         } else any = any || (av >= (edge ? a_thr_e : a_thr_i));
     };
     auto pair = [&](T2 A, T bx, T by, int k, T &xa, T &ya, T &xb, T &yb) {
-        // A = Z[k], (bx, by) = Z[128 - k]; returns 2 X[k] and 2 conj-partner for bin 128 - k
+        // A = Z[k], (bx, by) = Z[128 - k]; returns 2 X[k] and twice the conjugate partner for bin 128 - k
         const T ex = A.x + bx, ey = A.y - by, dx = A.x - bx, dy = A.y + by;
-        const T wr = tab->tw256[k][0], wi = tab->tw256[k][1];
-        const T tx = wr * dy + wi * dx, ty = wi * dy - wr * dx;
+        const T2 tw = *reinterpret_cast<const T2 *>(tab->tw256[k]);
+        const T tx = tw.x * dy + tw.y * dx, ty = tw.y * dy - tw.x * dx;
         xa = ex + tx; ya = ey + ty; xb = ex - tx; yb = ey - ty;
     };
+    const int src = (lane & 24) | ((8 - l) & 7); // the lane that holds Z[128 - k] for this lane's k (lane 0 and 4: itself)
 #pragma unroll
-    for (int k1 = 1; k1 < 16; ++k1) {
-        const T2 S = v[SJ_BREV32(32 - k1)];
-        const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
-        const int k = k1 + 32 * k2;
+    for (int c = 0; c < 8; ++c) {
+        // partner element: 15 - c of lane 8 - j; lane 0 pairs with itself, element (16 - c) mod 16
+        const T2 S = w[SJ_ZI(15 - c)], O = w[SJ_ZI((16 - c) & 15)];
+        T bx = __shfl_sync(kFull, S.x, src), by = __shfl_sync(kFull, S.y, src);
+        if (l == 0) { bx = O.x; by = O.y; }
+        const int k = l + 8 * c;
         T xa, ya, xb, yb;
-        pair(v[SJ_BREV32(k1)], bx, by, k, xa, ya, xb, yb);
-        emit(k, xa, ya);
-        emit(DN_WIN / 2 - k, xb, yb);
+        pair(w[SJ_ZI(c)], bx, by, k, xa, ya, xb, yb);
+        emit(k, c == 0 && l == 0, xa, ya);           // bin 0 is an edge cell
+        emit(DN_WIN / 2 - k, c == 0 && l == 0, xb, yb); // ... and so is bin 128 = 128 - 0
     }
-    {   // k1 = 16: partner Z[16 + 32 (3 - k2)] sits in the mirror lane, same register
-        const T2 S = v[SJ_BREV32(16)];
-        const T bx = __shfl_xor_sync(kFull, S.x, 3), by = __shfl_xor_sync(kFull, S.y, 3);
+    if (l == 0) { // bin 64 pairs with itself
+        const T2 A = w[SJ_ZI(8)];
         T xa, ya, xb, yb;
-        pair(S, bx, by, 16 + 32 * k2, xa, ya, xb, yb);
-        emit(16 + 32 * k2, xa, ya);
+        pair(A, A.x, A.y, 64, xa, ya, xb, yb);
+        emit(64, false, xa, ya);
     }
-    {   // k1 = 0: bins 0, 32, 64, 96 (and 128 from the k2 = 0 lane)
-        const T2 S = v[0];
-        T bx = __shfl_xor_sync(kFull, S.x, 1), by = __shfl_xor_sync(kFull, S.y, 1);
-        if (g < 2) { bx = S.x; by = S.y; } // k2 = 0 and k2 = 2 are their own partners
-        T xa, ya, xb, yb;
-        pair(S, bx, by, 32 * k2, xa, ya, xb, yb);
-        emit(32 * k2, xa, ya);
-        if (k2 == 0) emit(DN_WIN / 2, xb, yb);
-    }
-    if (BAND) { // combine the quad's partial results; the quad leader updates the clip's state
-        lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 1)); lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, 2));
-        lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 1)); lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, 2));
-        emin = fmin(emin, __shfl_xor_sync(kFull, emin, 1)); emin = fmin(emin, __shfl_xor_sync(kFull, emin, 2));
-        emax = fmax(emax, __shfl_xor_sync(kFull, emax, 1)); emax = fmax(emax, __shfl_xor_sync(kFull, emax, 2));
-        if (g == 0) {
+#undef SJ_ZI
+    if (BAND) { // combine the partial results of the row's 8 lanes; lane 0 of the row (which alone saw the edge cells) updates the clip's state
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            lmin = fmin(lmin, __shfl_xor_sync(kFull, lmin, o));
+            lmax = fmax(lmax, __shfl_xor_sync(kFull, lmax, o));
+        }
+        if (l == 0) {
             st->min_in[clip] = fmin(st->min_in[clip], lmin);
             st->max_in[clip] = fmax(st->max_in[clip], lmax);
             st->min_ed[clip] = fmin(st->min_ed[clip], emin);
@@ -980,7 +991,7 @@ __device__ __forceinline__ void pass_f64(const bool BAND, const double *rows, in
         }
     } else {
         const unsigned ballot = __ballot_sync(kFull, any);
-        if (g == 0 && ((ballot >> (4 * q)) & 0xFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
+        if (l == 0 && ((ballot >> (8 * q)) & 0xFFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
     }
 }
 
@@ -1130,19 +1141,19 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                     if (gid >= n_groups) break;
                     const long base = gid * cpg;
                     const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
-                    const T *rows = rows_all + g * 2 * kGroup * kRS;
+                    T *rows = rows_all + g * 2 * kGroup * kRS;
                     GroupState<T> *st = gs_all + g;
                     T *scratch = reinterpret_cast<T *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
                     bar_sync(kBarFull + g, kPair);
                     // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
-                    // double: 4 passes, p < 2 the flag rows; pass j of a kind holds the clips 8 j .. 8 j + 7.
+                    // double: 8 passes, p < 4 the flag rows; pass j of a kind holds the clips 4 j .. 4 j + 3.
                     // (handed out through a counter, so any number of transform warps shares them evenly)
                     for (;;) {
                         int p = 0;
                         if (lane == 0) p = atomicAdd(&st->next_pass, 1);
                         p = __shfl_sync(kFull, p, 0);
                         if (p >= kPasses) break;
-                        const int c0 = sizeof(T) == 4 ? (p & 7) : 8 * (p & 1);
+                        const int c0 = sizeof(T) == 4 ? (p & 7) : 4 * (p & 3);
                         if (c0 >= nact) continue;
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
                         continue;
@@ -1151,7 +1162,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                             if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
                             else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
                         } else {
-                            pass_f64(p >= 2, rows, pos, t, tb, tab, st, scratch, lane, c0);
+                            pass_f64(p >= 4, rows, pos, t, tb, tab, st, scratch, lane, c0);
                         }
                     }
                     if (t < tb - 1) {
@@ -1234,8 +1245,9 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                                 a_hi = first_true([&](T av) { return !(level(av) < hi); });
                             }
                             const T *scr = scratch + size_t(c2) * tb * DN_BINS;
-                            T *qu = fw->queue;
-                            T *stage = fw->stage();
+                            T *qu, *stage;
+                            if constexpr (sizeof(T) == 4) { qu = fw->queue; stage = fw->stage(); }
+                            else { qu = rows + w * (64 + Cfg<T>::kStage); stage = qu + 64; } // the rows are idle after the last frame
                             constexpr int kStage = Cfg<T>::kStage;
                             auto box = [&](int band, T halfw, T midpoint) -> T {
                                 const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
