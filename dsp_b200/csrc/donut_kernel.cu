@@ -674,7 +674,8 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 
 // ================================================================================================
 // Warp-specialised float kernel (round 2).  One persistent CTA per SM: kIir "filter" warps and kFft
-// "transform" warps, coupled by named barriers only -- no CTA-wide barrier in the steady state.
+// "transform" warps, coupled by one named barrier ("full") and one mbarrier ("empty") per group -- no CTA-wide barrier
+// in the steady state.
 //   * A filter warp owns a group of 16 clips = 32 (clip, filter) rows, one direct-form-II recurrence per
 //     lane in the reference's exact operation order (iir8: bit-identical samples, classifier.cpp:193-219).
 //     One filter warp sits on each of the SM's four schedulers: measured on B200, a lone warp issues FP32
@@ -686,12 +687,13 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 //   * The warp writes one spectrogram hop (224 new samples per row) into circular 256-sample rows
 //     (row = filter * 16 + clip, stride 258 floats: the warp's 64-bit column stores and the 16-float row
 //     reads of two half-warps eight rows apart are bank-conflict-free), signals "full", and waits for
-//     "empty" before the next hop; the four groups drift out of phase, so the transform warps always have a
-//     frame to work on and a filter warp's idle time is the transform time of its own frame only.
+//     "empty" before the next hop: one mbarrier arrival per pass, made as soon as the pass has its rows in registers,
+//     so the next hop is filtered while the frame is transformed; the groups drift out of phase, so the transform
+//     warps always have a frame to work on.
 //   * The transform warps replay PlainFFT's butterfly network on 2 rows per pass (16 lanes per frame,
 //     exactly the arithmetic of spectrogram_column_exact_f32); a pass holds two rows of the SAME kind
 //     (two flag rows or two band rows), so the per-cell bookkeeping is specialised per kind instead of
-//     carried twice with selects; passes are handed out through a shared-memory counter.  After a group's
+//     carried twice with selects; warp w takes the passes w, w + kFft, ...  After a group's
 //     last frame the transform warps run the clustering / band-sum epilogue for its clips and release it.
 namespace ws {
 
@@ -706,7 +708,7 @@ namespace ws {
 #define SJ_DONUT_IIR_WARPS_F64 3
 #endif
 #ifndef SJ_DONUT_FFT_WARPS_F64
-#define SJ_DONUT_FFT_WARPS_F64 9 /* measured (100 k clips, 8 lanes per row): 3 + 4 warps 3.26 M clips/s (254 registers), 3 + 5: 3.20 M, 3 + 9: 3.70 M (168), 3 + 13: 3.42 M (128, spills); round-1 kernel 2.70 M */
+#define SJ_DONUT_FFT_WARPS_F64 8 /* measured (100 k clips, 8 lanes per row, one pass per warp and frame): 3 + 8 warps 4.18 M clips/s, 3 + 4: 3.41 M; round-1 kernel 2.70 M */
 #endif
 constexpr int kGroup = 16;         // clips per group (32 rows: lane = filter * 16 + clip)
 constexpr int kRS = 258;           // row stride in elements
@@ -733,8 +735,8 @@ template <typename T> struct GroupState {
     T mean[2 * kGroup];                                       // per row: frame mean, summed sequentially like the reference
     T min_in[kGroup], max_in[kGroup], min_ed[kGroup], max_ed[kGroup]; // band rows: min / max of a over the cells with Sxx > 0
     uint32_t flags[kGroup][3];                                // flag rows: frames with any cell above the dB threshold
-    int next_pass;                                            // passes of the current frame handed out so far (transform warps grab them)
     int n_mid[kGroup];
+    unsigned long long empty_bar;                             // mbarrier: one arrival per pass whose rows have been read (phase = frame)
     T mids[kGroup][DN_MAX_MID];
 };
 template <typename T> struct FftWarpState;
@@ -749,6 +751,27 @@ template <> struct FftWarpState<double> { // nothing: the double pass transposes
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+#ifndef SJ_DONUT_POLL_NS
+#define SJ_DONUT_POLL_NS 100
+#endif
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar, int count)
+{
+    asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.shared::cta.b64 st, [%0], %1;\n}" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    // a failed try_wait comes back at once and a bare retry loop costs the scheduler one issue slot in three (measured:
+    // +80 k warp instructions per clip from three waiting filter warps); sleep between the polls instead
+    for (;;) {
+        uint32_t done;
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(SJ_DONUT_POLL_NS);
+    }
+}
 
 template <typename T> constexpr size_t kTabBytesT = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
 template <typename T>
@@ -762,7 +785,7 @@ static_assert(kSmemT<float> <= 232448 && kSmemT<double> <= 232448, "shared memor
 template <bool BAND>
 __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
                                                GroupState<float> *st, FftWarpState<float> *fw, float *scratch, int lane, int c0,
-                                               const float2 (&tw)[15])
+                                               const float2 (&tw)[15], uint32_t release)
 {
     const int half = lane >> 4, h = lane & 15;
     const int clip = c0 + 8 * half, r = (BAND ? kGroup : 0) + clip;
@@ -777,6 +800,11 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
         const float x = rowp[(pos + n) & 255];
         v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
     }
+    // the two rows are in registers: the filter warp may overwrite them with the next hop (one arrival per pass)
+#ifndef SJ_DONUT_F32_LATE_RELEASE
+    __syncwarp();
+    if (release && lane == 0) mbar_arrive(release, 1);
+#endif
 #pragma unroll
     for (int i = 0; i < 16; i += 2) {
         const float t1 = v[i + 1].x;
@@ -870,6 +898,10 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
         const unsigned ballot = __ballot_sync(kFull, any);
         if (h == 0 && ((ballot >> (16 * half)) & 0xFFFFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
     }
+#ifdef SJ_DONUT_F32_LATE_RELEASE
+    __syncwarp();
+    if (release && lane == 0) mbar_arrive(release, 1);
+#endif
 }
 
 // double: one pass = spectrogram column t of four rows of one kind, 8 lanes per row (no bit-exact FFT to follow: FFTW's
@@ -884,7 +916,7 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
 // stall cycles per issued instruction with warps at different places of the pass (profiles/r2l_*).
 // (BAND is a run-time flag, not a template parameter as in the float pass: one copy of the code.)
 __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
-                                         GroupState<double> *st, double *scratch, int lane, int c0)
+                                         GroupState<double> *st, double *scratch, int lane, int c0, uint32_t release)
 {
     typedef double T;
     typedef double2 T2;
@@ -927,6 +959,7 @@ __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos,
         for (int k = 0; k < 8; ++k) w[8 * h + k] = *reinterpret_cast<const T2 *>(rowp + ((lbase + 18 * k) & 255));
         __syncwarp();
     }
+    if (release && lane == 0) mbar_arrive(release, 1); // done with the rows: the filter warp may write the next hop
     {
         T2(&u0)[8] = *reinterpret_cast<T2(*)[8]>(&w[0]);
         T2(&u1)[8] = *reinterpret_cast<T2(*)[8]>(&w[8]);
@@ -1000,7 +1033,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
 {
     typedef typename V2<T>::type T2;
     constexpr int kIir = Cfg<T>::kIir, kFft = Cfg<T>::kFft, kPasses = Cfg<T>::kPasses, kThreads = kThreadsT<T>;
-    constexpr int kBarEmpty = 1 + kIir, kBarFft = 1 + 2 * kIir;
+    constexpr int kBarFft = 1 + kIir;
     extern __shared__ __align__(16) unsigned char smem[];
     SjDonutTables<T> *tab = reinterpret_cast<SjDonutTables<T> *>(smem);
     T *rows_all = reinterpret_cast<T *>(smem + kTabBytesT<T>);
@@ -1011,6 +1044,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
         for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kThreads) dst[i] = __ldg(src + i);
+        if (threadIdx.x < kIir) mbar_init(smem_u32(&gs_all[threadIdx.x].empty_bar), kPasses);
     }
     __syncthreads();
 
@@ -1030,6 +1064,8 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
 #pragma unroll
         for (int j = 0; j < 9; ++j) { ca[j] = tab->a[f][j]; cb[j] = tab->b[f][j]; }
         T *myrow = rows + lane * kRS;
+        const uint32_t empty_bar = smem_u32(&st->empty_bar);
+        uint32_t empty_phase = 0; // parity of the next phase to wait for: one phase per frame, all groups of this warp in a row
         for (long q = g;; q += kIir) {
             const long gid = blockIdx.x + q * gridDim.x;
             if (gid >= n_groups) break;
@@ -1063,7 +1099,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
             T acc_cur = 0, acc_next = 0;
             int pos = 0, sample = 0;
             for (int t = 0; t < tb; ++t) {
-                if (t > 0) bar_sync(kBarEmpty + g, kPair); // the transform warps are done with frame t - 1
+                if (t > 0) { mbar_wait(empty_bar, empty_phase); empty_phase ^= 1; } // every pass of frame t - 1 has read its rows
                 const int nnew = t == 0 ? DN_WIN : DN_HOP;
 #ifdef SJ_DONUT_SKIP_FILTER /* timing experiment only (results are wrong): the filter warps run the barrier protocol alone */
                 if (t == 0) for (int i = 0; i < 256; ++i) myrow[i] = (T)0.001 * (T)((i * 37 + lane * 11) & 63);
@@ -1108,13 +1144,13 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                 sample += nnew;
                 pos = (pos + nnew) & 255;
                 st->mean[lane] = div_rn(acc_cur, (T)DN_WIN);
-                if (lane == 0) st->next_pass = 0;
                 acc_cur = acc_next;
                 acc_next = 0;
                 __threadfence_block();
                 bar_arrive(kBarFull + g, kPair);
             }
-            bar_sync(kBarEmpty + g, kPair); // the group's epilogue is done: rows and state are free again
+            mbar_wait(empty_bar, empty_phase); // the group's epilogue is done: rows and state are free again
+            empty_phase ^= 1;
         }
     } else {
         // ------------------------------------------------------------------ transform warps
@@ -1144,32 +1180,32 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                     T *rows = rows_all + g * 2 * kGroup * kRS;
                     GroupState<T> *st = gs_all + g;
                     T *scratch = reinterpret_cast<T *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
+                    const uint32_t empty_bar = smem_u32(&st->empty_bar);
+                    const uint32_t release = t < tb - 1 ? empty_bar : 0u; // the last frame's phase is completed after the epilogue
                     bar_sync(kBarFull + g, kPair);
                     // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
                     // double: 8 passes, p < 4 the flag rows; pass j of a kind holds the clips 4 j .. 4 j + 3.
-                    // (handed out through a counter, so any number of transform warps shares them evenly)
-                    for (;;) {
-                        int p = 0;
-                        if (lane == 0) p = atomicAdd(&st->next_pass, 1);
-                        p = __shfl_sync(kFull, p, 0);
-                        if (p >= kPasses) break;
+                    // warp w takes the passes w, w + kFft, ...  (A shared-memory ticket counter -- atomicAdd, later a
+                    // compare-and-swap that never claims beyond the frame -- cost 6 % of the float kernel's throughput:
+                    // 6.68 M clips/s with the fixed deal against 6.27 M / 6.15 M.)
+                    for (int p = w; p < kPasses; p += kFft) {
                         const int c0 = sizeof(T) == 4 ? (p & 7) : 4 * (p & 3);
-                        if (c0 >= nact) continue;
+                        bool skip = c0 >= nact;
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
-                        continue;
+                        skip = true;
 #endif
+                        if (skip) {
+                            if (release && lane == 0) mbar_arrive(release, 1);
+                            continue;
+                        }
                         if constexpr (sizeof(T) == 4) {
-                            if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
-                            else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw);
+                            if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw, release);
+                            else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw, release);
                         } else {
-                            pass_f64(p >= 4, rows, pos, t, tb, tab, st, scratch, lane, c0);
+                            pass_f64(p >= 4, rows, pos, t, tb, tab, st, scratch, lane, c0, release);
                         }
                     }
-                    if (t < tb - 1) {
-                        __threadfence_block();
-                        bar_arrive(kBarEmpty + g, kPair);
-                        continue;
-                    }
+                    if (t < tb - 1) continue;
                     // ---- the group's last frame: epilogue for its clips, then release the group
                     __threadfence_block();
                     bar_sync(kBarFft, 32 * kFft); // every pass of the frame has been accounted for
@@ -1325,8 +1361,12 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                         if (a.mids && lane < DN_MAX_MID)
                             a.mids[(base + c2) * DN_MAX_MID + lane] = lane < nm ? (float)st->mids[c2][lane] : __int_as_float(0x7fc00000);
                     }
-                    __threadfence_block();
-                    bar_arrive(kBarEmpty + g, kPair);
+                    // the last frame's phase: the kPasses arrivals are shared out over the transform warps
+                    __syncwarp();
+                    if (lane == 0) {
+                        const int share = kPasses / kFft + (w < kPasses % kFft ? 1 : 0);
+                        if (share > 0) mbar_arrive(empty_bar, share);
+                    }
                 }
             }
         }
