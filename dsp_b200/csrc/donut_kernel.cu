@@ -776,7 +776,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 template <typename T> constexpr size_t kTabBytesT = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
 template <typename T>
 constexpr size_t kSmemT = kTabBytesT<T> + sizeof(T) * Cfg<T>::kIir * 2 * kGroup * kRS + sizeof(GroupState<T>) * Cfg<T>::kIir +
-                          sizeof(FftWarpState<T>) * Cfg<T>::kFft;
+                          sizeof(FftWarpState<T>) * Cfg<T>::kFft + sizeof(T) * DN_MAX_TB;
 static_assert(kSmemT<float> <= 232448 && kSmemT<double> <= 232448, "shared memory per CTA");
 
 // one pass = spectrogram column t of two rows of one kind (BAND: 3000-7500 Hz rows whose cells are kept; otherwise the
@@ -1039,6 +1039,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
     T *rows_all = reinterpret_cast<T *>(smem + kTabBytesT<T>);
     GroupState<T> *gs_all = reinterpret_cast<GroupState<T> *>(rows_all + kIir * 2 * kGroup * kRS);
     FftWarpState<T> *fw_all = reinterpret_cast<FftWarpState<T> *>(gs_all + kIir);
+    T *frame_time = reinterpret_cast<T *>(fw_all + kFft); // centre time of frame j with the reference's operations (classifier.c:586-590)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
@@ -1046,6 +1047,8 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
         for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kThreads) dst[i] = __ldg(src + i);
         if (threadIdx.x < kIir) mbar_init(smem_u32(&gs_all[threadIdx.x].empty_bar), kPasses);
     }
+    __syncthreads();
+    if (threadIdx.x < DN_MAX_TB) frame_time[threadIdx.x] = div_rn((T)(threadIdx.x * DN_HOP + DN_WIN / 2), tab->fs);
     __syncthreads();
 
     const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 32, fewer for small batches
@@ -1219,7 +1222,7 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                             T first = 0, last = 0, tsum = 0;
                             for (int j = 0; j <= tb; ++j) {
                                 const bool on = j < tb && ((fl[j >> 5] >> (j & 31)) & 1u);
-                                const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                                const T tj = frame_time[j < DN_MAX_TB ? j : DN_MAX_TB - 1]; // (j == tb only closes the last cluster)
                                 const bool joins = on && size > 0 && sub_rn(tj, last) <= tol;
                                 if (size > 0 && (!on ? j == tb : !joins)) {
                                     if (sub_rn(last, first) >= mind) {
@@ -1244,7 +1247,24 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                         const int nm = st->n_mid[c2];
                         int label = 0;
                         T s_above = 0, s_mid = 0, s_below = 0;
+#ifdef SJ_DONUT_SKIP_EPILOGUE /* timing experiment only: results are wrong */
+                        if (false) {
+#else
                         if (nm > 0) {
+#endif
+                            const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
+                            const T *scr = scratch + size_t(c2) * tb * DN_BINS;
+                            // The boxes' cells went to L2 up to 71 frames ago and most have been evicted to DRAM since (64 clips
+                            // in flight per SM x 148 SMs do not fit L2): ask for the frames around every midpoint now, one 128-byte
+                            // line per lane and instruction, so that they arrive while the thresholds are searched.
+                            for (int m = 0; m < cap; ++m) {
+                                const T mp = st->mids[c2][m];
+                                int f_lo = (int)((mp - (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP - 1, f_hi = (int)((mp + (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP + 2;
+                                f_lo = f_lo < 0 ? 0 : f_lo;
+                                f_hi = f_hi > tb ? tb : f_hi;
+                                const char *p0 = reinterpret_cast<const char *>(scr + f_lo * DN_BINS), *p1 = reinterpret_cast<const char *>(scr + f_hi * DN_BINS);
+                                for (const char *q = p0 + 128 * lane; q < p1; q += 128 * 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                            }
                             T smin = (T)INFINITY, smax = 0;
                             if (st->max_in[c2] > 0) { smin = mul_rn(div_rn(st->min_in[c2], U), (T)2); smax = mul_rn(div_rn(st->max_in[c2], U), (T)2); }
                             if (st->max_ed[c2] > 0) {
@@ -1259,10 +1279,21 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                                 return div_rn(sub_rn(to_db<T>(sv), mn), range);
                             };
                             const T amax = st->max_in[c2];
-                            auto first_true = [&](auto pred) -> T {
+                            // smallest a in [a_pos, amax] with pred true (pred monotone); "none" = +inf.  `seed` is where the
+                            // threshold should lie if level() were evaluated without rounding: the search starts in a window of
+                            // +-2^10 bit patterns around it when the predicate brackets there (two rounds instead of seven / thirteen),
+                            // and in the whole range otherwise -- the result is the exact threshold either way.
+                            auto first_true = [&](auto pred, T seed) -> T {
                                 typedef typename Bits<T>::type UI;
                                 UI blo = Bits<T>::of(a_pos), bhi = Bits<T>::of(amax);
                                 if (!(amax >= a_pos) || !pred(amax)) return (T)INFINITY;
+                                if (seed > a_pos && seed < amax) {
+                                    const UI sb = Bits<T>::of(seed), wlo = sb - 1024 > blo ? sb - 1024 : blo, whi = sb + 1024 < bhi ? sb + 1024 : bhi;
+                                    // lane 0 tests the pattern below the window (must be false), lane 1 its top (must be true)
+                                    const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(lane == 0 ? wlo - 1 : whi)));
+                                    if (wlo > blo && !(bal & 1u)) blo = wlo;
+                                    if (bal & 2u) bhi = whi;
+                                }
                                 while (blo < bhi) {
                                     const UI step = (bhi - blo) / 32 + 1;
                                     UI cand = blo + step * (UI)(lane + 1) - 1;
@@ -1277,27 +1308,32 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                             };
                             T a_lo = (T)INFINITY, a_hi = (T)INFINITY;
                             if (range > 0) {
-                                a_lo = first_true([&](T av) { return level(av) > lo; });
-                                a_hi = first_true([&](T av) { return !(level(av) < hi); });
+                                // level(a) = (10 log10(2 a / U / 1e-12) - mn) / range = x  <=>  a = U / 2 * 1e-12 * 10^((x range + mn) / 10)
+                                const double k = 0.5e-12 * (double)U;
+                                a_lo = first_true([&](T av) { return level(av) > lo; }, (T)(k * exp10(((double)lo * (double)range + (double)mn) * 0.1)));
+                                a_hi = first_true([&](T av) { return !(level(av) < hi); }, (T)(k * exp10(((double)hi * (double)range + (double)mn) * 0.1)));
                             }
-                            const T *scr = scratch + size_t(c2) * tb * DN_BINS;
                             T *qu, *stage;
                             if constexpr (sizeof(T) == 4) { qu = fw->queue; stage = fw->stage(); }
                             else { qu = rows + w * (64 + Cfg<T>::kStage); stage = qu + 64; } // the rows are idle after the last frame
                             constexpr int kStage = Cfg<T>::kStage;
-                            auto box = [&](int band, T halfw, T midpoint) -> T {
-                                const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
+                            // time index search exactly as sum_intense (classifier.c:619-640), lane-parallel over the frame-time
+                            // table: times are increasing, so the loops count the frames before / after the window
+                            auto window = [&](T halfw, T midpoint, int &t0, int &t1) {
                                 const T tlo = sub_rn(midpoint, halfw), thi = add_rn(midpoint, halfw);
                                 int nb = 0, na = 0;
                                 for (int j = lane; j < DN_MAX_TB; j += 32) {
-                                    const T tj = div_rn((T)(j * DN_HOP + DN_WIN / 2), fs);
+                                    const T tj = frame_time[j];
                                     nb += __popc(__ballot_sync(kFull, j < tb && tj < tlo));
                                     na += __popc(__ballot_sync(kFull, j < tb && tj > thi));
                                 }
-                                int t0 = nb, t1 = tb - 1 - na;
+                                t0 = nb; t1 = tb - 1 - na;
                                 if (t0 >= tb) t0 = tb - 1;
                                 if (t1 < 0) t1 = 0;
                                 if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
+                            };
+                            auto box = [&](int band, int t0, int t1) -> T {
+                                const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
                                 double acc = 0.0;
                                 const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
                                 int nq = 0;
@@ -1309,7 +1345,11 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                                         __syncwarp();
                                         int sj = cj, si = ci;
                                         for (int c = cc + lane; c < ncell && c < cc + kStage; c += 32) {
+#ifdef SJ_DONUT_EXP_NOSTAGE /* timing experiment only: results are wrong */
+                                            stage[c - cc] = (T)(c & 1023);
+#else
                                             cp_async_elem(stage + (c - cc), scr + (t0 + sj) * DN_BINS + f0 + si);
+#endif
                                             si += r32;
                                             sj += q32;
                                             if (si >= nf) { si -= nf; ++sj; }
@@ -1328,7 +1368,11 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                                     nq += __popc(bal);
                                     __syncwarp();
                                     if (nq >= 32) {
+#ifdef SJ_DONUT_EXP_NOLEVEL /* timing experiment only: results are wrong */
+                                        acc += (double)qu[lane];
+#else
                                         acc += (double)level(qu[lane]);
+#endif
                                         nq -= 32;
                                         __syncwarp();
                                         if (lane < nq) qu[lane] = qu[32 + lane];
@@ -1341,12 +1385,14 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                                 for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
                                 return (T)acc;
                             };
-                            const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
                             for (int m = 0; m < cap; ++m) {
                                 const T mp = st->mids[c2][m];
-                                s_above = box(0, (T)0.18, mp);
-                                s_mid = box(1, (T)0.05, mp);
-                                s_below = box(2, (T)0.18, mp);
+                                int t0, t1, u0, u1;
+                                window((T)0.18, mp, t0, t1); // the above and below boxes share their time window
+                                window((T)0.05, mp, u0, u1);
+                                s_above = box(0, t0, t1);
+                                s_mid = box(1, u0, u1);
+                                s_below = box(2, t0, t1);
                                 if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
                             }
                         }
