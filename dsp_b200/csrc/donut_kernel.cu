@@ -700,53 +700,70 @@ namespace ws {
 #ifndef SJ_DONUT_IIR_WARPS
 #define SJ_DONUT_IIR_WARPS 4
 #endif
-#ifndef SJ_DONUT_FFT_WARPS
-#define SJ_DONUT_FFT_WARPS 8 /* measured (100 k clips): 8 warps 6.21 M clips/s (168 registers, no spill), 10: 6.04 M, 12: 6.03 M (128 registers) */
-#endif
 // double: a group's 32 rows of doubles take 66 KB of shared memory, so three groups are in flight
 #ifndef SJ_DONUT_IIR_WARPS_F64
 #define SJ_DONUT_IIR_WARPS_F64 3
 #endif
-#ifndef SJ_DONUT_FFT_WARPS_F64
-#define SJ_DONUT_FFT_WARPS_F64 8 /* measured (100 k clips, 8 lanes per row, one pass per warp and frame): 3 + 8 warps 4.18 M clips/s, 3 + 4: 3.41 M; round-1 kernel 2.70 M */
+// registers per thread of the transform / filter / epilogue warpgroups (multiples of 8; 8 T + 4 F + 4 E <= 2048)
+#ifndef SJ_DONUT_REG_T_F32
+#define SJ_DONUT_REG_T_F32 128
+#define SJ_DONUT_REG_F_F32 104
+#define SJ_DONUT_REG_E_F32 152
+#endif
+#ifndef SJ_DONUT_REG_T_F64
+#define SJ_DONUT_REG_T_F64 144
+#define SJ_DONUT_REG_F_F64 136
+#define SJ_DONUT_REG_E_F64 80
 #endif
 constexpr int kGroup = 16;         // clips per group (32 rows: lane = filter * 16 + clip)
 constexpr int kRS = 258;           // row stride in elements
+// Warp roles, by warpgroup (setmaxnreg moves registers between whole warpgroups): warps 0-7 transform, 8-11 epilogue,
+// 12-15 filter (the double kernel leaves warp 15 idle).  The kernel is compiled for 512 threads = 128 registers; the
+// warpgroups then grow or shrink to the Cfg<T>::kReg* of their role (8 T + 4 F + 4 E <= 2048 = 64 K registers / 32 lanes).
+constexpr int kFft = 8, kEpi = 4, kFilterWarp0 = kFft + kEpi, kThreads = 512;
 template <typename T> struct Cfg;
 template <> struct Cfg<float> {
     static constexpr int kIir = SJ_DONUT_IIR_WARPS; // filter warps = clip groups in flight per CTA
-    static constexpr int kFft = SJ_DONUT_FFT_WARPS; // transform / epilogue warps
     static constexpr int kPasses = 2 * kGroup / 2;  // passes per group frame: two rows each (16 lanes per row)
-    static constexpr int kStage = 2 * 16 * 17 * 2 / 32 * 32; // epilogue staging area = the transpose buffers
+    static constexpr int kStage = 512;              // epilogue staging area (cells) per epilogue warp
+    static constexpr int kRegT = SJ_DONUT_REG_T_F32, kRegF = SJ_DONUT_REG_F_F32, kRegE = SJ_DONUT_REG_E_F32;
 };
 template <> struct Cfg<double> {
     static constexpr int kIir = SJ_DONUT_IIR_WARPS_F64;
-    static constexpr int kFft = SJ_DONUT_FFT_WARPS_F64;
     static constexpr int kPasses = 2 * kGroup / 4;  // four rows each (8 lanes per row)
-    static constexpr int kStage = 512;              // epilogue staging area: a slice of the group's idle rows, per transform warp
+    static constexpr int kStage = 96;
+    static constexpr int kRegT = SJ_DONUT_REG_T_F64, kRegF = SJ_DONUT_REG_F_F64, kRegE = SJ_DONUT_REG_E_F64;
 };
-static_assert((64 + Cfg<double>::kStage) * Cfg<double>::kFft <= 2 * kGroup * kRS, "epilogue slices of the rows");
-template <typename T> constexpr int kThreadsT = (Cfg<T>::kIir + Cfg<T>::kFft) * 32;
-// named barriers (0 = __syncthreads): full[g] = 1 + g, empty[g] = 1 + kIir + g, transform warps = 1 + 2 kIir
-constexpr int kBarFull = 1;
-static_assert(1 + 2 * Cfg<float>::kIir < 16 && 1 + 2 * Cfg<double>::kIir < 16, "named barriers");
+static_assert(8 * Cfg<float>::kRegT + 4 * Cfg<float>::kRegE + 4 * Cfg<float>::kRegF <= 2048, "register file");
+static_assert(8 * Cfg<double>::kRegT + 4 * Cfg<double>::kRegE + 4 * Cfg<double>::kRegF <= 2048, "register file");
+static_assert(Cfg<float>::kIir <= 4 && Cfg<double>::kIir <= 4, "one warpgroup of filter warps");
+constexpr int kBarFull = 1; // named barriers (0 = __syncthreads): full[g] = 1 + g
 
-template <typename T> struct GroupState {
-    T mean[2 * kGroup];                                       // per row: frame mean, summed sequentially like the reference
+// per-clip results of a group's frames, read by the epilogue warps after the last frame: two copies per group slot, so
+// that the next group of the slot is filtered and transformed while the epilogue of the previous one runs
+template <typename T> struct ClipState {
     T min_in[kGroup], max_in[kGroup], min_ed[kGroup], max_ed[kGroup]; // band rows: min / max of a over the cells with Sxx > 0
     uint32_t flags[kGroup][3];                                // flag rows: frames with any cell above the dB threshold
     int n_mid[kGroup];
-    unsigned long long empty_bar;                             // mbarrier: one arrival per pass whose rows have been read (phase = frame)
     T mids[kGroup][DN_MAX_MID];
+};
+template <typename T> struct GroupState {
+    T mean[2 * kGroup];            // per row: frame mean, summed sequentially like the reference
+    ClipState<T> cs[2];
+    unsigned long long empty_bar;  // mbarrier: one arrival per pass whose rows have been read (phase = frame)
+    int frames_done;               // transform warps that have finished the last frame of a group, summed over the slot's groups
+    int epilogues_done;            // epilogue warps that have finished a group, summed over the slot's groups
 };
 template <typename T> struct FftWarpState;
 template <> struct FftWarpState<float> {
     float2 xbuf[2][16 * 17]; // 16x16 transpose buffers of the exact float FFT (two frames per pass)
-    float queue[64];         // band-sum epilogue: a values of the cells that passed the level test
-    __device__ float *stage() { return reinterpret_cast<float *>(xbuf); } // the transpose buffers are idle in the epilogue
 };
-template <> struct FftWarpState<double> { // nothing: the double pass transposes through the rows, and the epilogue's queue
-    double pad[2];                        // and staging area are slices of the group's rows, idle after the last frame
+template <> struct FftWarpState<double> { // nothing: the double pass transposes through the rows
+    double pad[2];
+};
+template <typename T> struct EpiWarpState {
+    T queue[64];                 // band-sum epilogue: a values of the cells that passed the level test
+    T stage[Cfg<T>::kStage];     // ... and the staging area of a box's cells
 };
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -776,22 +793,47 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 template <typename T> constexpr size_t kTabBytesT = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
 template <typename T>
 constexpr size_t kSmemT = kTabBytesT<T> + sizeof(T) * Cfg<T>::kIir * 2 * kGroup * kRS + sizeof(GroupState<T>) * Cfg<T>::kIir +
-                          sizeof(FftWarpState<T>) * Cfg<T>::kFft + sizeof(T) * DN_MAX_TB;
+                          sizeof(FftWarpState<T>) * kFft + sizeof(EpiWarpState<T>) * kEpi + sizeof(T) * DN_MAX_TB;
 static_assert(kSmemT<float> <= 232448 && kSmemT<double> <= 232448, "shared memory per CTA");
+
+// normalised dB level of an inner-bin cell with the reference's operations.  Out of line on purpose: the double-precision
+// log10 is ~150 instructions, and five inlined copies made the epilogue too large to share the 32 KB instruction cache
+// with the filter loop and the passes that run at the same time.
+template <typename T> __device__ __noinline__ T level_of(T av, T U, T mn, T range)
+{
+    const T sv = mul_rn(div_rn(av, U), (T)2);
+    return div_rn(sub_rn(to_db<T>(sv), mn), range);
+}
+
+// volatile poll of a shared-memory counter (the hand-overs to and from the epilogue warps: rare, never on the frame path)
+__device__ __forceinline__ void wait_count(const int *ctr, int at_least)
+{
+    while (*reinterpret_cast<const volatile int *>(ctr) < at_least) __nanosleep(200);
+    __threadfence_block();
+}
+template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 // one pass = spectrogram column t of two rows of one kind (BAND: 3000-7500 Hz rows whose cells are kept; otherwise the
 // 1000-3000 Hz rows that only flag frames), the clips c0 and c0 + 8 of the group; PlainFFT replayed as in
 // spectrogram_column_exact_f32
+// (SJ_DONUT_F32_ONE_PASS_BODY: BAND as a run-time flag = one copy of the FFT code for both row kinds, 9 KB less to keep in
+// the instruction cache next to the filter loop and the epilogue)
+#ifdef SJ_DONUT_F32_ONE_PASS_BODY
+template <bool UNUSED>
+__device__ __forceinline__ void pass_exact_f32(const bool BAND, const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
+#else
 template <bool BAND>
-__device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
-                                               GroupState<float> *st, FftWarpState<float> *fw, float *scratch, int lane, int c0,
-                                               const float2 (&tw)[15], uint32_t release)
+__device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
+#endif
+                                               const float *mean_tab, ClipState<float> *st, FftWarpState<float> *fw, float *scratch,
+                                               int lane, int c0, const float2 (&tw)[15], uint32_t release)
 {
     const int half = lane >> 4, h = lane & 15;
     const int clip = c0 + 8 * half, r = (BAND ? kGroup : 0) + clip;
     float2 *xb = fw->xbuf[half];
     const float *rowp = rows + r * kRS;
-    const float mean = st->mean[r];
+    const float mean = mean_tab[r];
     float2 v[16];
     const int hb = brev4(h);
 #pragma unroll
@@ -916,7 +958,7 @@ __device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t
 // stall cycles per issued instruction with warps at different places of the pass (profiles/r2l_*).
 // (BAND is a run-time flag, not a template parameter as in the float pass: one copy of the code.)
 __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
-                                         GroupState<double> *st, double *scratch, int lane, int c0, uint32_t release)
+                                         const double *mean_tab, ClipState<double> *st, double *scratch, int lane, int c0, uint32_t release)
 {
     typedef double T;
     typedef double2 T2;
@@ -924,7 +966,7 @@ __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos,
     const int clip = c0 + q, r = (BAND ? kGroup : 0) + clip;
     T *rowp = rows + r * kRS;
     T2 v[16];
-    const T mean = st->mean[r];
+    const T mean = mean_tab[r];
 #pragma unroll
     for (int m = 0; m < 16; ++m) { // the 8 lanes of a row read 8 consecutive 16-byte units: conflict-free
         v[m] = *reinterpret_cast<const T2 *>(rowp + ((pos + 2 * l + 16 * m) & 255));
@@ -1029,37 +1071,45 @@ __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos,
 }
 
 template <typename T, bool ALIGNED>
-__global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonutArgs a)
+__global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs a)
 {
     typedef typename V2<T>::type T2;
-    constexpr int kIir = Cfg<T>::kIir, kFft = Cfg<T>::kFft, kPasses = Cfg<T>::kPasses, kThreads = kThreadsT<T>;
-    constexpr int kBarFft = 1 + kIir;
+    constexpr int kIir = Cfg<T>::kIir, kPasses = Cfg<T>::kPasses;
     extern __shared__ __align__(16) unsigned char smem[];
     SjDonutTables<T> *tab = reinterpret_cast<SjDonutTables<T> *>(smem);
     T *rows_all = reinterpret_cast<T *>(smem + kTabBytesT<T>);
     GroupState<T> *gs_all = reinterpret_cast<GroupState<T> *>(rows_all + kIir * 2 * kGroup * kRS);
     FftWarpState<T> *fw_all = reinterpret_cast<FftWarpState<T> *>(gs_all + kIir);
-    T *frame_time = reinterpret_cast<T *>(fw_all + kFft); // centre time of frame j with the reference's operations (classifier.c:586-590)
+    EpiWarpState<T> *ew_all = reinterpret_cast<EpiWarpState<T> *>(fw_all + kFft);
+    T *frame_time = reinterpret_cast<T *>(ew_all + kEpi); // centre time of frame j with the reference's operations (classifier.c:586-590)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
         for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kThreads) dst[i] = __ldg(src + i);
-        if (threadIdx.x < kIir) mbar_init(smem_u32(&gs_all[threadIdx.x].empty_bar), kPasses);
+        if (threadIdx.x < kIir) {
+            mbar_init(smem_u32(&gs_all[threadIdx.x].empty_bar), kPasses);
+            gs_all[threadIdx.x].frames_done = gs_all[threadIdx.x].epilogues_done = 0;
+        }
     }
     __syncthreads();
     if (threadIdx.x < DN_MAX_TB) frame_time[threadIdx.x] = div_rn((T)(threadIdx.x * DN_HOP + DN_WIN / 2), tab->fs);
     __syncthreads();
 
-    const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 32, fewer for small batches
+    const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 16, fewer for small batches
     const long n_groups = (a.n_clips + cpg - 1) / cpg;
-    constexpr int kPair = 32 + 32 * kFft; // threads of a full / empty barrier: one filter warp + the transform warps
+    constexpr int kPair = 32 + 32 * kFft; // threads of a "full" barrier: one filter warp + the transform warps
+    // scratch of group slot g, buffer b: [16][tb][129] PSD cells of the band rows
+    auto scratch_of = [&](int g, int b) {
+        return reinterpret_cast<T *>(a.scratch) + ((size_t(blockIdx.x) * kIir + g) * 2 + b) * kGroup * tb * DN_BINS;
+    };
 
-    // the filter warps take the HIGHEST warp ids: the SM's warp arbiter favours high ids, and the recurrence is the
-    // latency-critical chain (a transform warp that loses a slot loses nothing)
-    if (warp >= kFft) {
-        // ------------------------------------------------------------------ filter warp: group q = g, g + kIir, ...
-        const int g = warp - kFft;
+    if (warp >= kFilterWarp0) {
+        // ------------------------------------------------------------------ filter warp: groups q = g, g + kIir, ... of this CTA
+        // (the highest warp ids: the SM's warp arbiter favours them, and the recurrence is the latency-critical chain)
+        if constexpr (Cfg<T>::kRegF < 128) reg_dealloc<Cfg<T>::kRegF>(); else if constexpr (Cfg<T>::kRegF > 128) reg_alloc<Cfg<T>::kRegF>();
+        const int g = warp - kFilterWarp0;
+        if (g >= kIir) return;
         T *rows = rows_all + g * 2 * kGroup * kRS;
         GroupState<T> *st = gs_all + g;
         const int f = lane >> 4, ci = lane & 15; // row = lane = filter * 16 + clip
@@ -1069,8 +1119,8 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
         T *myrow = rows + lane * kRS;
         const uint32_t empty_bar = smem_u32(&st->empty_bar);
         uint32_t empty_phase = 0; // parity of the next phase to wait for: one phase per frame, all groups of this warp in a row
-        for (long q = g;; q += kIir) {
-            const long gid = blockIdx.x + q * gridDim.x;
+        for (long r = 0;; ++r) {
+            const long gid = blockIdx.x + (r * kIir + g) * gridDim.x;
             if (gid >= n_groups) break;
             const long base = gid * cpg;
             const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
@@ -1081,13 +1131,23 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
             T w[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) w[j] = 0;
+            // the slot's state copy r & 1 was last used by group r - 2: its epilogue must be over
+            if (r >= 2) wait_count(&st->epilogues_done, kEpi * (int)(r - 1));
             if (lane < kGroup) {
-                st->min_in[lane] = st->min_ed[lane] = (T)INFINITY;
-                st->max_in[lane] = st->max_ed[lane] = 0;
-                st->flags[lane][0] = st->flags[lane][1] = st->flags[lane][2] = 0;
+                ClipState<T> *cs = &st->cs[r & 1];
+                cs->min_in[lane] = cs->min_ed[lane] = (T)INFINITY;
+                cs->max_in[lane] = cs->max_ed[lane] = 0;
+                cs->flags[lane][0] = cs->flags[lane][1] = cs->flags[lane][2] = 0;
             }
+// input samples: a register ring of kPre blocks of 8 samples, requested kPre blocks ahead, behind an L2 prefetch of one
+// 128-byte line per lane SJ_DONUT_L2_AHEAD samples ahead.  (Measured, float / double: ring of 4 alone 7.05 / 3.81 M clips/s;
+// ring of 2 + L2 prefetch 256 ahead 7.82 / 4.50 M -- the loop body is half as long, and the filter loop, the passes and the
+// epilogue must share the 32 KB instruction cache; ring of 1: 7.53 / 4.22 M; 128 / 512 ahead: 7.79 / 7.74 M.)
 #ifndef SJ_DONUT_PRE
-#define SJ_DONUT_PRE 4
+#define SJ_DONUT_PRE 2
+#endif
+#ifndef SJ_DONUT_L2_AHEAD
+#define SJ_DONUT_L2_AHEAD 256
 #endif
             constexpr int kPre = SJ_DONUT_PRE; // register ring of kPre blocks of 8 samples, requested kPre blocks ahead
             float4 ring[kPre][2];
@@ -1110,6 +1170,10 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
 #else
 #pragma unroll 1
                 for (int i0 = 0; i0 < nnew; i0 += 8 * kPre) {
+#endif
+#if SJ_DONUT_L2_AHEAD > 0
+                    if (ALIGNED && (i0 & 31) == 0 && sample + i0 + SJ_DONUT_L2_AHEAD < n_samples)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(src + sample + i0 + SJ_DONUT_L2_AHEAD));
 #endif
 #pragma unroll
                     for (int j = 0; j < kPre; ++j) {
@@ -1152,11 +1216,12 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                 __threadfence_block();
                 bar_arrive(kBarFull + g, kPair);
             }
-            mbar_wait(empty_bar, empty_phase); // the group's epilogue is done: rows and state are free again
+            mbar_wait(empty_bar, empty_phase); // every pass of the last frame has read its rows: they are free for the next group
             empty_phase ^= 1;
         }
-    } else {
+    } else if (warp < kFft) {
         // ------------------------------------------------------------------ transform warps
+        if constexpr (Cfg<T>::kRegT > 128) reg_alloc<Cfg<T>::kRegT>();
         const int w = warp;
         FftWarpState<T> *fw = fw_all + w;
         float2 tw[15]; // float: this lane's twiddles of FFT stages 4..7 (lane & 15 = the low index digit after the transpose)
@@ -1169,7 +1234,6 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
             tw[7] = twid(128, 0); tw[8] = twid(128, 1); tw[9] = twid(128, 2); tw[10] = twid(128, 3);
             tw[11] = twid(128, 4); tw[12] = twid(128, 5); tw[13] = twid(128, 6); tw[14] = twid(128, 7);
         }
-        const T U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
         for (long r = 0;; ++r) {
             if (blockIdx.x + r * kIir * gridDim.x >= n_groups) break;
             for (int t = 0; t < tb; ++t) {
@@ -1182,15 +1246,14 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                     const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
                     T *rows = rows_all + g * 2 * kGroup * kRS;
                     GroupState<T> *st = gs_all + g;
-                    T *scratch = reinterpret_cast<T *>(a.scratch) + (size_t(blockIdx.x) * kIir + g) * kGroup * tb * DN_BINS;
-                    const uint32_t empty_bar = smem_u32(&st->empty_bar);
-                    const uint32_t release = t < tb - 1 ? empty_bar : 0u; // the last frame's phase is completed after the epilogue
+                    ClipState<T> *cs = &st->cs[r & 1];
+                    T *scratch = scratch_of(g, (int)(r & 1));
+                    const uint32_t release = smem_u32(&st->empty_bar);
                     bar_sync(kBarFull + g, kPair);
                     // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
                     // double: 8 passes, p < 4 the flag rows; pass j of a kind holds the clips 4 j .. 4 j + 3.
-                    // warp w takes the passes w, w + kFft, ...  (A shared-memory ticket counter -- atomicAdd, later a
-                    // compare-and-swap that never claims beyond the frame -- cost 6 % of the float kernel's throughput:
-                    // 6.68 M clips/s with the fixed deal against 6.27 M / 6.15 M.)
+                    // Warp w takes the passes w, w + kFft, ...  (A shared-memory ticket counter -- atomicAdd, later a
+                    // compare-and-swap that never claims beyond the frame -- cost 6 % of the float kernel's throughput.)
                     for (int p = w; p < kPasses; p += kFft) {
                         const int c0 = sizeof(T) == 4 ? (p & 7) : 4 * (p & 3);
                         bool skip = c0 >= nact;
@@ -1198,222 +1261,238 @@ __global__ void __launch_bounds__(kThreadsT<T>, 1) donut_ws_kernel(const SjDonut
                         skip = true;
 #endif
                         if (skip) {
-                            if (release && lane == 0) mbar_arrive(release, 1);
+                            if (lane == 0) mbar_arrive(release, 1);
                             continue;
                         }
                         if constexpr (sizeof(T) == 4) {
-                            if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw, release);
-                            else pass_exact_f32<true>(rows, pos, t, tb, tab, st, fw, scratch, lane, c0, tw, release);
+#ifdef SJ_DONUT_F32_ONE_PASS_BODY
+                            pass_exact_f32<false>(p >= 8, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, release);
+#else
+                            if (p < 8) pass_exact_f32<false>(false, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, release);
+                            else pass_exact_f32<true>(true, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, release);
+#endif
                         } else {
-                            pass_f64(p >= 4, rows, pos, t, tb, tab, st, scratch, lane, c0, release);
+                            pass_f64(p >= 4, rows, pos, t, tb, tab, st->mean, cs, scratch, lane, c0, release);
                         }
                     }
-                    if (t < tb - 1) continue;
-                    // ---- the group's last frame: epilogue for its clips, then release the group
-                    __threadfence_block();
-                    bar_sync(kBarFft, 32 * kFft); // every pass of the frame has been accounted for
-                    // epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
-                    {
-                        const int c = w + kFft * lane;
-                        if (c < nact) {
-                            const uint32_t *fl = st->flags[c];
-                            const T tol = tab->gap_tol, mind = tab->min_dur;
-                            int count = 0, size = 0;
-                            T first = 0, last = 0, tsum = 0;
-                            for (int j = 0; j <= tb; ++j) {
-                                const bool on = j < tb && ((fl[j >> 5] >> (j & 31)) & 1u);
-                                const T tj = frame_time[j < DN_MAX_TB ? j : DN_MAX_TB - 1]; // (j == tb only closes the last cluster)
-                                const bool joins = on && size > 0 && sub_rn(tj, last) <= tol;
-                                if (size > 0 && (!on ? j == tb : !joins)) {
-                                    if (sub_rn(last, first) >= mind) {
-                                        if (count < DN_MAX_MID) st->mids[c][count] = div_rn(tsum, (T)size);
-                                        ++count;
-                                    }
-                                    size = 0;
-                                }
-                                if (on) {
-                                    if (size == 0) { first = tj; tsum = 0; }
-                                    tsum = add_rn(tsum, tj);
-                                    last = tj;
-                                    ++size;
-                                }
-                            }
-                            st->n_mid[c] = count;
-                        }
-                    }
-                    __syncwarp();
-                    // epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip (see donut_kernel)
-                    for (int c2 = w; c2 < nact; c2 += kFft) {
-                        const int nm = st->n_mid[c2];
-                        int label = 0;
-                        T s_above = 0, s_mid = 0, s_below = 0;
-#ifdef SJ_DONUT_SKIP_EPILOGUE /* timing experiment only: results are wrong */
-                        if (false) {
-#else
-                        if (nm > 0) {
-#endif
-                            const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
-                            const T *scr = scratch + size_t(c2) * tb * DN_BINS;
-                            // The boxes' cells went to L2 up to 71 frames ago and most have been evicted to DRAM since (64 clips
-                            // in flight per SM x 148 SMs do not fit L2): ask for the frames around every midpoint now, one 128-byte
-                            // line per lane and instruction, so that they arrive while the thresholds are searched.
-                            for (int m = 0; m < cap; ++m) {
-                                const T mp = st->mids[c2][m];
-                                int f_lo = (int)((mp - (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP - 1, f_hi = (int)((mp + (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP + 2;
-                                f_lo = f_lo < 0 ? 0 : f_lo;
-                                f_hi = f_hi > tb ? tb : f_hi;
-                                const char *p0 = reinterpret_cast<const char *>(scr + f_lo * DN_BINS), *p1 = reinterpret_cast<const char *>(scr + f_hi * DN_BINS);
-                                for (const char *q = p0 + 128 * lane; q < p1; q += 128 * 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-                            }
-                            T smin = (T)INFINITY, smax = 0;
-                            if (st->max_in[c2] > 0) { smin = mul_rn(div_rn(st->min_in[c2], U), (T)2); smax = mul_rn(div_rn(st->max_in[c2], U), (T)2); }
-                            if (st->max_ed[c2] > 0) {
-                                const T e0 = div_rn(st->min_ed[c2], U), e1 = div_rn(st->max_ed[c2], U);
-                                smin = e0 < smin ? e0 : smin;
-                                smax = e1 > smax ? e1 : smax;
-                            }
-                            const T mn = to_db<T>(smin), mx = to_db<T>(smax);
-                            const T range = sub_rn(mx, mn), lo = tab->lo_norm, hi = tab->hi_norm;
-                            auto level = [&](T av) -> T {
-                                const T sv = mul_rn(div_rn(av, U), (T)2);
-                                return div_rn(sub_rn(to_db<T>(sv), mn), range);
-                            };
-                            const T amax = st->max_in[c2];
-                            // smallest a in [a_pos, amax] with pred true (pred monotone); "none" = +inf.  `seed` is where the
-                            // threshold should lie if level() were evaluated without rounding: the search starts in a window of
-                            // +-2^10 bit patterns around it when the predicate brackets there (two rounds instead of seven / thirteen),
-                            // and in the whole range otherwise -- the result is the exact threshold either way.
-                            auto first_true = [&](auto pred, T seed) -> T {
-                                typedef typename Bits<T>::type UI;
-                                UI blo = Bits<T>::of(a_pos), bhi = Bits<T>::of(amax);
-                                if (!(amax >= a_pos) || !pred(amax)) return (T)INFINITY;
-                                if (seed > a_pos && seed < amax) {
-                                    const UI sb = Bits<T>::of(seed), wlo = sb - 1024 > blo ? sb - 1024 : blo, whi = sb + 1024 < bhi ? sb + 1024 : bhi;
-                                    // lane 0 tests the pattern below the window (must be false), lane 1 its top (must be true)
-                                    const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(lane == 0 ? wlo - 1 : whi)));
-                                    if (wlo > blo && !(bal & 1u)) blo = wlo;
-                                    if (bal & 2u) bhi = whi;
-                                }
-                                while (blo < bhi) {
-                                    const UI step = (bhi - blo) / 32 + 1;
-                                    UI cand = blo + step * (UI)(lane + 1) - 1;
-                                    if (cand > bhi || cand < blo) cand = bhi;
-                                    const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(cand)));
-                                    const int first = __ffs(bal) - 1;
-                                    const UI at = Bits<T>::shfl(cand, first), before = Bits<T>::shfl(cand, first > 0 ? first - 1 : 0);
-                                    bhi = at;
-                                    if (first > 0) blo = before + 1;
-                                }
-                                return Bits<T>::from(bhi);
-                            };
-                            T a_lo = (T)INFINITY, a_hi = (T)INFINITY;
-                            if (range > 0) {
-                                // level(a) = (10 log10(2 a / U / 1e-12) - mn) / range = x  <=>  a = U / 2 * 1e-12 * 10^((x range + mn) / 10)
-                                const double k = 0.5e-12 * (double)U;
-                                a_lo = first_true([&](T av) { return level(av) > lo; }, (T)(k * exp10(((double)lo * (double)range + (double)mn) * 0.1)));
-                                a_hi = first_true([&](T av) { return !(level(av) < hi); }, (T)(k * exp10(((double)hi * (double)range + (double)mn) * 0.1)));
-                            }
-                            T *qu, *stage;
-                            if constexpr (sizeof(T) == 4) { qu = fw->queue; stage = fw->stage(); }
-                            else { qu = rows + w * (64 + Cfg<T>::kStage); stage = qu + 64; } // the rows are idle after the last frame
-                            constexpr int kStage = Cfg<T>::kStage;
-                            // time index search exactly as sum_intense (classifier.c:619-640), lane-parallel over the frame-time
-                            // table: times are increasing, so the loops count the frames before / after the window
-                            auto window = [&](T halfw, T midpoint, int &t0, int &t1) {
-                                const T tlo = sub_rn(midpoint, halfw), thi = add_rn(midpoint, halfw);
-                                int nb = 0, na = 0;
-                                for (int j = lane; j < DN_MAX_TB; j += 32) {
-                                    const T tj = frame_time[j];
-                                    nb += __popc(__ballot_sync(kFull, j < tb && tj < tlo));
-                                    na += __popc(__ballot_sync(kFull, j < tb && tj > thi));
-                                }
-                                t0 = nb; t1 = tb - 1 - na;
-                                if (t0 >= tb) t0 = tb - 1;
-                                if (t1 < 0) t1 = 0;
-                                if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
-                            };
-                            auto box = [&](int band, int t0, int t1) -> T {
-                                const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
-                                double acc = 0.0;
-                                const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
-                                int nq = 0;
-                                // the box is staged in shared memory by asynchronous copies first (see donut_kernel)
-                                const int q32 = 32 / nf, r32 = 32 - q32 * nf;
-                                int cj = lane / nf, ci = lane - cj * nf;
-                                for (int cc = 0; cc < ncell; cc += 32) {
-                                    if (cc % kStage == 0) {
-                                        __syncwarp();
-                                        int sj = cj, si = ci;
-                                        for (int c = cc + lane; c < ncell && c < cc + kStage; c += 32) {
-#ifdef SJ_DONUT_EXP_NOSTAGE /* timing experiment only: results are wrong */
-                                            stage[c - cc] = (T)(c & 1023);
-#else
-                                            cp_async_elem(stage + (c - cc), scr + (t0 + sj) * DN_BINS + f0 + si);
-#endif
-                                            si += r32;
-                                            sj += q32;
-                                            if (si >= nf) { si -= nf; ++sj; }
-                                        }
-                                        cp_async_wait_all();
-                                        __syncwarp();
-                                    }
-                                    const int c = cc + lane;
-                                    const T av = c < ncell ? stage[c % kStage] : (T)0;
-                                    ci += r32;
-                                    cj += q32;
-                                    if (ci >= nf) { ci -= nf; ++cj; }
-                                    const bool pass = c < ncell && av >= a_lo && av < a_hi;
-                                    const unsigned bal = __ballot_sync(kFull, pass);
-                                    if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
-                                    nq += __popc(bal);
-                                    __syncwarp();
-                                    if (nq >= 32) {
-#ifdef SJ_DONUT_EXP_NOLEVEL /* timing experiment only: results are wrong */
-                                        acc += (double)qu[lane];
-#else
-                                        acc += (double)level(qu[lane]);
-#endif
-                                        nq -= 32;
-                                        __syncwarp();
-                                        if (lane < nq) qu[lane] = qu[32 + lane];
-                                        __syncwarp();
-                                    }
-                                }
-                                if (lane < nq) acc += (double)level(qu[lane]);
-                                __syncwarp();
-#pragma unroll
-                                for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
-                                return (T)acc;
-                            };
-                            for (int m = 0; m < cap; ++m) {
-                                const T mp = st->mids[c2][m];
-                                int t0, t1, u0, u1;
-                                window((T)0.18, mp, t0, t1); // the above and below boxes share their time window
-                                window((T)0.05, mp, u0, u1);
-                                s_above = box(0, t0, t1);
-                                s_mid = box(1, u0, u1);
-                                s_below = box(2, t0, t1);
-                                if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
-                            }
-                        }
-                        if (lane == 0) {
-                            if (a.labels) a.labels[base + c2] = label;
-                            if (a.track) a.track[base + c2] = (int8_t)(label + 1);
-                            if (a.detail) {
-                                float *d = a.detail + (base + c2) * 4;
-                                d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
-                            }
-                        }
-                        if (a.mids && lane < DN_MAX_MID)
-                            a.mids[(base + c2) * DN_MAX_MID + lane] = lane < nm ? (float)st->mids[c2][lane] : __int_as_float(0x7fc00000);
-                    }
-                    // the last frame's phase: the kPasses arrivals are shared out over the transform warps
-                    __syncwarp();
-                    if (lane == 0) {
-                        const int share = kPasses / kFft + (w < kPasses % kFft ? 1 : 0);
-                        if (share > 0) mbar_arrive(empty_bar, share);
+                    if (t == tb - 1) { // the group's last frame: hand its clips to the epilogue warps
+                        __syncwarp();
+                        if (lane == 0) { __threadfence_block(); atomicAdd(&st->frames_done, 1); }
                     }
                 }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue warps: clustering, band sums, verdict
+        if constexpr (Cfg<T>::kRegE < 128) reg_dealloc<Cfg<T>::kRegE>(); else if constexpr (Cfg<T>::kRegE > 128) reg_alloc<Cfg<T>::kRegE>();
+        const int e = warp - kFft;
+        EpiWarpState<T> *ew = ew_all + e;
+        const T U = tab->U, a_pos = tab->a_pos, fs = tab->fs;
+        for (long r = 0;; ++r) {
+            if (blockIdx.x + r * kIir * gridDim.x >= n_groups) break;
+#pragma unroll 1
+            for (int g = 0; g < kIir; ++g) {
+                const long gid = blockIdx.x + (r * kIir + g) * gridDim.x;
+                if (gid >= n_groups) break;
+                const long base = gid * cpg;
+                const int nact = a.n_clips - base < cpg ? (int)(a.n_clips - base) : cpg;
+                GroupState<T> *gs = gs_all + g;
+                ClipState<T> *st = &gs->cs[r & 1];
+                const T *scratch = scratch_of(g, (int)(r & 1));
+                wait_count(&gs->frames_done, kFft * (int)(r + 1)); // every pass of the group's last frame is done
+                // epilogue A: blob clustering -> midpoints, one lane per clip (find_midpoints, classifier.c:729-800)
+                {
+                    const int c = e + kEpi * lane;
+                    if (c < nact) {
+                        const uint32_t *fl = st->flags[c];
+                        const T tol = tab->gap_tol, mind = tab->min_dur;
+                        int count = 0, size = 0;
+                        T first = 0, last = 0, tsum = 0;
+                        for (int j = 0; j <= tb; ++j) {
+                            const bool on = j < tb && ((fl[j >> 5] >> (j & 31)) & 1u);
+                            const T tj = frame_time[j < DN_MAX_TB ? j : DN_MAX_TB - 1]; // (j == tb only closes the last cluster)
+                            const bool joins = on && size > 0 && sub_rn(tj, last) <= tol;
+                            if (size > 0 && (!on ? j == tb : !joins)) {
+                                if (sub_rn(last, first) >= mind) {
+                                    if (count < DN_MAX_MID) st->mids[c][count] = div_rn(tsum, (T)size);
+                                    ++count;
+                                }
+                                size = 0;
+                            }
+                            if (on) {
+                                if (size == 0) { first = tj; tsum = 0; }
+                                tsum = add_rn(tsum, tj);
+                                last = tj;
+                                ++size;
+                            }
+                        }
+                        st->n_mid[c] = count;
+                    }
+                }
+                __syncwarp();
+                // epilogue B: band sums around each midpoint and the verdict, the warp cooperating per clip (see donut_kernel)
+                for (int c2 = e; c2 < nact; c2 += kEpi) {
+                    const int nm = st->n_mid[c2];
+                    int label = 0;
+                    T s_above = 0, s_mid = 0, s_below = 0;
+#ifdef SJ_DONUT_SKIP_EPILOGUE /* timing experiment only: results are wrong */
+                    if (false) {
+#else
+                    if (nm > 0) {
+#endif
+                    const int cap = nm < DN_MAX_MID ? nm : DN_MAX_MID;
+                    const T *scr = scratch + size_t(c2) * tb * DN_BINS;
+                    // The boxes' cells went to L2 up to 71 frames ago and most have been evicted to DRAM since (64 clips
+                    // in flight per SM x 148 SMs do not fit L2): ask for the frames around every midpoint now, one 128-byte
+                    // line per lane and instruction, so that they arrive while the thresholds are searched.
+                    for (int m = 0; m < cap; ++m) {
+                        const T mp = st->mids[c2][m];
+                        int f_lo = (int)((mp - (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP - 1, f_hi = (int)((mp + (T)0.18) * fs - (T)(DN_WIN / 2)) / DN_HOP + 2;
+                        f_lo = f_lo < 0 ? 0 : f_lo;
+                        f_hi = f_hi > tb ? tb : f_hi;
+                        const char *p0 = reinterpret_cast<const char *>(scr + f_lo * DN_BINS), *p1 = reinterpret_cast<const char *>(scr + f_hi * DN_BINS);
+                        for (const char *q = p0 + 128 * lane; q < p1; q += 128 * 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                    }
+                    T smin = (T)INFINITY, smax = 0;
+                    if (st->max_in[c2] > 0) { smin = mul_rn(div_rn(st->min_in[c2], U), (T)2); smax = mul_rn(div_rn(st->max_in[c2], U), (T)2); }
+                    if (st->max_ed[c2] > 0) {
+                        const T e0 = div_rn(st->min_ed[c2], U), e1 = div_rn(st->max_ed[c2], U);
+                        smin = e0 < smin ? e0 : smin;
+                        smax = e1 > smax ? e1 : smax;
+                    }
+                    const T mn = to_db<T>(smin), mx = to_db<T>(smax);
+                    const T range = sub_rn(mx, mn), lo = tab->lo_norm, hi = tab->hi_norm;
+                    auto level = [&](T av) -> T { return level_of<T>(av, U, mn, range); };
+                    const T amax = st->max_in[c2];
+                    // smallest a in [a_pos, amax] with pred true (pred monotone); "none" = +inf.  `seed` is where the
+                    // threshold should lie if level() were evaluated without rounding: the search starts in a window of
+                    // +-2^10 bit patterns around it when the predicate brackets there (two rounds instead of seven / thirteen),
+                    // and in the whole range otherwise -- the result is the exact threshold either way.
+                    auto first_true = [&](const bool upper, T seed) -> T {
+                        auto pred = [&](T av) { const T lv = level(av); return upper ? !(lv < hi) : lv > lo; };
+                        typedef typename Bits<T>::type UI;
+                        UI blo = Bits<T>::of(a_pos), bhi = Bits<T>::of(amax);
+                        if (!(amax >= a_pos) || !pred(amax)) return (T)INFINITY;
+                        if (seed > a_pos && seed < amax) {
+                            const UI sb = Bits<T>::of(seed), wlo = sb - 1024 > blo ? sb - 1024 : blo, whi = sb + 1024 < bhi ? sb + 1024 : bhi;
+                            // lane 0 tests the pattern below the window (must be false), lane 1 its top (must be true)
+                            const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(lane == 0 ? wlo - 1 : whi)));
+                            if (wlo > blo && !(bal & 1u)) blo = wlo;
+                            if (bal & 2u) bhi = whi;
+                        }
+                        while (blo < bhi) {
+                            const UI step = (bhi - blo) / 32 + 1;
+                            UI cand = blo + step * (UI)(lane + 1) - 1;
+                            if (cand > bhi || cand < blo) cand = bhi;
+                            const unsigned bal = __ballot_sync(kFull, pred(Bits<T>::from(cand)));
+                            const int first = __ffs(bal) - 1;
+                            const UI at = Bits<T>::shfl(cand, first), before = Bits<T>::shfl(cand, first > 0 ? first - 1 : 0);
+                            bhi = at;
+                            if (first > 0) blo = before + 1;
+                        }
+                        return Bits<T>::from(bhi);
+                    };
+                    T a_lo = (T)INFINITY, a_hi = (T)INFINITY;
+                    if (range > 0) {
+                        // level(a) = (10 log10(2 a / U / 1e-12) - mn) / range = x  <=>  a = U / 2 * 1e-12 * 10^((x range + mn) / 10)
+                        const double k = 0.5e-12 * (double)U;
+                        a_lo = first_true(false, (T)(k * exp10(((double)lo * (double)range + (double)mn) * 0.1)));
+                        a_hi = first_true(true, (T)(k * exp10(((double)hi * (double)range + (double)mn) * 0.1)));
+                    }
+                    T *qu = ew->queue, *stage = ew->stage;
+                    constexpr int kStage = Cfg<T>::kStage;
+                    // time index search exactly as sum_intense (classifier.c:619-640), lane-parallel over the frame-time
+                    // table: times are increasing, so the loops count the frames before / after the window
+                    auto window = [&](T halfw, T midpoint, int &t0, int &t1) {
+                        const T tlo = sub_rn(midpoint, halfw), thi = add_rn(midpoint, halfw);
+                        int nb = 0, na = 0;
+                        for (int j = lane; j < DN_MAX_TB; j += 32) {
+                            const T tj = frame_time[j];
+                            nb += __popc(__ballot_sync(kFull, j < tb && tj < tlo));
+                            na += __popc(__ballot_sync(kFull, j < tb && tj > thi));
+                        }
+                        t0 = nb; t1 = tb - 1 - na;
+                        if (t0 >= tb) t0 = tb - 1;
+                        if (t1 < 0) t1 = 0;
+                        if (t0 > t1) { const int x = t0; t0 = t1; t1 = x; }
+                    };
+                    auto box = [&](int band, int t0, int t1) -> T {
+                        const int f0 = tab->box_f[band][0], f1 = tab->box_f[band][1];
+                        double acc = 0.0;
+                        const int nf = f1 - f0 + 1, ncell = nf * (t1 - t0 + 1);
+                        int nq = 0;
+                        // the box is staged in shared memory by asynchronous copies first (see donut_kernel)
+                        const int q32 = 32 / nf, r32 = 32 - q32 * nf;
+                        int cj = lane / nf, ci = lane - cj * nf;
+                        for (int cc = 0; cc < ncell; cc += 32) {
+                            if (cc % kStage == 0) {
+                                __syncwarp();
+                                int sj = cj, si = ci;
+                                for (int c = cc + lane; c < ncell && c < cc + kStage; c += 32) {
+#ifdef SJ_DONUT_EXP_NOSTAGE /* timing experiment only: results are wrong */
+                                    stage[c - cc] = (T)(c & 1023);
+#else
+                                    cp_async_elem(stage + (c - cc), scr + (t0 + sj) * DN_BINS + f0 + si);
+#endif
+                                    si += r32;
+                                    sj += q32;
+                                    if (si >= nf) { si -= nf; ++sj; }
+                                }
+                                cp_async_wait_all();
+                                __syncwarp();
+                            }
+                            const int c = cc + lane;
+                            const T av = c < ncell ? stage[c % kStage] : (T)0;
+                            ci += r32;
+                            cj += q32;
+                            if (ci >= nf) { ci -= nf; ++cj; }
+                            const bool pass = c < ncell && av >= a_lo && av < a_hi;
+                            const unsigned bal = __ballot_sync(kFull, pass);
+                            if (pass) qu[nq + __popc(bal & ((1u << lane) - 1u))] = av;
+                            nq += __popc(bal);
+                            __syncwarp();
+                            if (nq >= 32) {
+#ifdef SJ_DONUT_EXP_NOLEVEL /* timing experiment only: results are wrong */
+                                acc += (double)qu[lane];
+#else
+                                acc += (double)level(qu[lane]);
+#endif
+                                nq -= 32;
+                                __syncwarp();
+                                if (lane < nq) qu[lane] = qu[32 + lane];
+                                __syncwarp();
+                            }
+                        }
+                        if (lane < nq) acc += (double)level(qu[lane]);
+                        __syncwarp();
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+                        return (T)acc;
+                    };
+                    for (int m = 0; m < cap; ++m) {
+                        const T mp = st->mids[c2][m];
+                        int t0, t1, u0, u1;
+                        window((T)0.18, mp, t0, t1); // the above and below boxes share their time window
+                        window((T)0.05, mp, u0, u1);
+                        s_above = box(0, t0, t1);
+                        s_mid = box(1, u0, u1);
+                        s_below = box(2, t0, t1);
+                        if (s_mid < tab->thr_mid && s_above > tab->thr_above && s_below > tab->thr_below) { label = 1; break; }
+                    }
+                }
+                    if (lane == 0) {
+                        if (a.labels) a.labels[base + c2] = label;
+                        if (a.track) a.track[base + c2] = (int8_t)(label + 1);
+                        if (a.detail) {
+                            float *d = a.detail + (base + c2) * 4;
+                            d[0] = (float)nm; d[1] = (float)s_above; d[2] = (float)s_mid; d[3] = (float)s_below;
+                        }
+                    }
+                    if (a.mids && lane < DN_MAX_MID)
+                        a.mids[(base + c2) * DN_MAX_MID + lane] = lane < nm ? (float)st->mids[c2][lane] : __int_as_float(0x7fc00000);
+                }
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); atomicAdd(&gs->epilogues_done, 1); } // the slot's state copy and scratch buffer are free
             }
         }
     }
@@ -1472,8 +1551,8 @@ int sj_donut_grid(int num_sms, bool f64)
 
 size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
 {
-    if (!sj_donut_legacy(f64))
-        return size_t(f64 ? ws::Cfg<double>::kIir : ws::Cfg<float>::kIir) * ws::kGroup * tb * DN_BINS * (f64 ? 8 : 4);
+    if (!sj_donut_legacy(f64)) // two buffers per group slot: a group's epilogue runs while the slot's next group is transformed
+        return size_t(f64 ? ws::Cfg<double>::kIir : ws::Cfg<float>::kIir) * 2 * ws::kGroup * tb * DN_BINS * (f64 ? 8 : 4);
     return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
 }
 
@@ -1489,8 +1568,8 @@ template <typename T> static cudaError_t launch_ws(SjDonutArgs a, int grid, cuda
     if (groups < grid) grid = (int)groups;
     const bool al = (a.n_samples % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.clips) & 15) == 0) &&
                     (a.clips_per_row <= 0 || a.row_stride % 4 == 0);
-    if (al) ws::donut_ws_kernel<T, true><<<grid, ws::kThreadsT<T>, ws::kSmemT<T>, stream>>>(a);
-    else ws::donut_ws_kernel<T, false><<<grid, ws::kThreadsT<T>, ws::kSmemT<T>, stream>>>(a);
+    if (al) ws::donut_ws_kernel<T, true><<<grid, ws::kThreads, ws::kSmemT<T>, stream>>>(a);
+    else ws::donut_ws_kernel<T, false><<<grid, ws::kThreads, ws::kSmemT<T>, stream>>>(a);
     return cudaGetLastError();
 }
 
