@@ -552,7 +552,7 @@ def run_ours(args, rank, local_rank, world):
                            "achieved_gbs": gbs,
                            "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk, "unit": "GB/s", "frac": gbs / pk,
                                         "traffic": tr * Cd if tr else None, "peak_source": pk_src, "kernel_ms": kd,
-                                        "kernel": "donut_ws_kernel (4 filter + 8 transform warps)" if name == "sync_f32" else "donut_kernel<double>",
+                                        "kernel": "donut_ws_kernel<%s> (%d filter + 8 transform + 4 epilogue warps)" % (("float", 4) if name == "sync_f32" else ("double", 3)),
                                         "bytes_per_clip": N_SAMPLES * 4 + 4,
                                         "note": "FP32 / FP64 issue of the exact (no-FMA) recurrence and FFT binds, not HBM"},
                            "positives": int(labels[:Cd].sum().item())}

@@ -673,28 +673,34 @@ __global__ void __launch_bounds__(DnWarps<T>::value * 32) donut_kernel(const SjD
 
 
 // ================================================================================================
-// Warp-specialised float kernel (round 2).  One persistent CTA per SM: kIir "filter" warps and kFft
-// "transform" warps, coupled by one named barrier ("full") and one mbarrier ("empty") per group -- no CTA-wide barrier
-// in the steady state.
+// Warp-specialised kernels (round 2), float and double.  One persistent CTA of 16 warps per SM in three roles -- kIir
+// "filter" warps (4 float / 3 double), 8 "transform" warps, 4 "epilogue" warps -- coupled per clip group by two named
+// barriers ("full", "empty") and two shared-memory counters; no CTA-wide barrier in the steady state.  The roles live in
+// separate warpgroups and trade registers with setmaxnreg (filter ~100, transform 128-144, epilogue what is left).
 //   * A filter warp owns a group of 16 clips = 32 (clip, filter) rows, one direct-form-II recurrence per
 //     lane in the reference's exact operation order (iir8: bit-identical samples, classifier.cpp:193-219).
-//     One filter warp sits on each of the SM's four schedulers: measured on B200, a lone warp issues FP32
-//     instructions at one per 2 cycles (packed f32x2: one per 4), so a recurrence step costs ~50 cycles of
-//     its scheduler whatever it does -- four independent groups in flight is what fills the four FP32 pipes,
-//     and the other half of each pipe goes to the transform warps.  (A first version with both filters of
-//     a clip packed in one lane -- 13 cross-filter FMUL2 + two scalar chains -- needed 107 cycles per step
-//     on two warps and lost to the round-1 kernel: 4.85 M against 5.8 M clips/s.)
+//     One filter warp sits on each of the SM's four schedulers: the recurrence is a dependent chain (4 cycles per
+//     FP32, 8 per FP64 instruction), so a step costs its scheduler ~50 (float) / ~75 (double) cycles whatever it does;
+//     independent groups in flight are what fills the pipes, and the rest of each pipe goes to the other roles.
+//     (A first version with both filters of a clip packed in one lane -- 13 cross-filter FMUL2 + two scalar chains --
+//     needed 107 cycles per step on two warps and lost to the round-1 kernel: 4.85 M against 5.8 M clips/s.)
 //   * The warp writes one spectrogram hop (224 new samples per row) into circular 256-sample rows
-//     (row = filter * 16 + clip, stride 258 floats: the warp's 64-bit column stores and the 16-float row
-//     reads of two half-warps eight rows apart are bank-conflict-free), signals "full", and waits for
-//     "empty" before the next hop: one mbarrier arrival per pass, made as soon as the pass has its rows in registers,
-//     so the next hop is filtered while the frame is transformed; the groups drift out of phase, so the transform
-//     warps always have a frame to work on.
-//   * The transform warps replay PlainFFT's butterfly network on 2 rows per pass (16 lanes per frame,
-//     exactly the arithmetic of spectrogram_column_exact_f32); a pass holds two rows of the SAME kind
-//     (two flag rows or two band rows), so the per-cell bookkeeping is specialised per kind instead of
-//     carried twice with selects; warp w takes the passes w, w + kFft, ...  After a group's
-//     last frame the transform warps run the clustering / band-sum epilogue for its clips and release it.
+//     (row = filter * 16 + clip, stride 258 elements: the warp's column stores and the row reads of the passes are
+//     bank-conflict-free), signals "full", and waits for "empty" before the next hop.  A transform warp arrives at
+//     "empty" as soon as its last pass of the frame has its rows in registers, so the next hop is filtered while the
+//     frame is transformed; the groups drift out of phase, so the transform warps always have a frame to work on.
+//   * The transform warps compute the spectrogram column of the group's 32 rows: float = PlainFFT's butterfly network
+//     replayed exactly, 2 rows per pass (16 lanes per row, the arithmetic of spectrogram_column_exact_f32), a pass
+//     holding two rows of the SAME kind (flag rows or band rows) so that the per-cell bookkeeping is specialised per
+//     kind; double = 4 rows per pass, 8 lanes per row (pass_f64).  Warp w takes the passes w, w + 8, ...
+//   * After a group's last frame the epilogue warps cluster the flagged frames into midpoints, sum the three boxes around
+//     each and write the verdict, from the group's copy of the clip state and PSD scratch (two copies per group slot),
+//     while the filter and transform warps are already busy with the slot's next group.  With the epilogue on the
+//     transform warps every group end stalled the whole pipeline: 26 % of the float kernel's time for 8 % of its
+//     instructions.
+//   * The three code streams run at the same time and must share the 32 KB instruction cache: the double pass is one
+//     body for both row kinds, level() (double log10) is out of line, the filter loop handles 16 samples per trip behind
+//     an L2 prefetch.  (Two copies of a 50 KB pass body cost 3.3 "no instruction" stall cycles per issued instruction.)
 namespace ws {
 
 #ifndef SJ_DONUT_IIR_WARPS
@@ -737,7 +743,11 @@ template <> struct Cfg<double> {
 static_assert(8 * Cfg<float>::kRegT + 4 * Cfg<float>::kRegE + 4 * Cfg<float>::kRegF <= 2048, "register file");
 static_assert(8 * Cfg<double>::kRegT + 4 * Cfg<double>::kRegE + 4 * Cfg<double>::kRegF <= 2048, "register file");
 static_assert(Cfg<float>::kIir <= 4 && Cfg<double>::kIir <= 4, "one warpgroup of filter warps");
-constexpr int kBarFull = 1; // named barriers (0 = __syncthreads): full[g] = 1 + g
+// named barriers (0 = __syncthreads): full[g] = 1 + g, the filter warp arrives and the transform warps wait; empty[g] = 5 + g,
+// every transform warp arrives once per frame (when its last pass of the frame has its rows in registers) and the filter
+// warp waits.  (An mbarrier polled with naps did the same at equal speed but 15 % more issued instructions.)
+constexpr int kBarFull = 1, kBarEmpty = 5;
+constexpr int kPair = 32 + 32 * kFft; // threads of a full / empty barrier: one filter warp + the transform warps
 
 // per-clip results of a group's frames, read by the epilogue warps after the last frame: two copies per group slot, so
 // that the next group of the slot is filtered and transformed while the epilogue of the previous one runs
@@ -750,7 +760,6 @@ template <typename T> struct ClipState {
 template <typename T> struct GroupState {
     T mean[2 * kGroup];            // per row: frame mean, summed sequentially like the reference
     ClipState<T> cs[2];
-    unsigned long long empty_bar;  // mbarrier: one arrival per pass whose rows have been read (phase = frame)
     int frames_done;               // transform warps that have finished the last frame of a group, summed over the slot's groups
     int epilogues_done;            // epilogue warps that have finished a group, summed over the slot's groups
 };
@@ -768,28 +777,6 @@ template <typename T> struct EpiWarpState {
 
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-#ifndef SJ_DONUT_POLL_NS
-#define SJ_DONUT_POLL_NS 100
-#endif
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
-__device__ __forceinline__ void mbar_arrive(uint32_t bar, int count)
-{
-    asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.shared::cta.b64 st, [%0], %1;\n}" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
-{
-    // a failed try_wait comes back at once and a bare retry loop costs the scheduler one issue slot in three (measured:
-    // +80 k warp instructions per clip from three waiting filter warps); sleep between the polls instead
-    for (;;) {
-        uint32_t done;
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) break;
-        __nanosleep(SJ_DONUT_POLL_NS);
-    }
-}
-
 template <typename T> constexpr size_t kTabBytesT = (sizeof(SjDonutTables<T>) + 15) & ~size_t(15);
 template <typename T>
 constexpr size_t kSmemT = kTabBytesT<T> + sizeof(T) * Cfg<T>::kIir * 2 * kGroup * kRS + sizeof(GroupState<T>) * Cfg<T>::kIir +
@@ -827,7 +814,7 @@ template <bool BAND>
 __device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
 #endif
                                                const float *mean_tab, ClipState<float> *st, FftWarpState<float> *fw, float *scratch,
-                                               int lane, int c0, const float2 (&tw)[15], uint32_t release)
+                                               int lane, int c0, const float2 (&tw)[15], int release)
 {
     const int half = lane >> 4, h = lane & 15;
     const int clip = c0 + 8 * half, r = (BAND ? kGroup : 0) + clip;
@@ -842,11 +829,9 @@ __device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, in
         const float x = rowp[(pos + n) & 255];
         v[rr] = make_float2(mul_rn(sub_rn(x, mean), tab->window[n]), 0.f);
     }
-    // the two rows are in registers: the filter warp may overwrite them with the next hop (one arrival per pass)
-#ifndef SJ_DONUT_F32_LATE_RELEASE
-    __syncwarp();
-    if (release && lane == 0) mbar_arrive(release, 1);
-#endif
+    // the two rows are in registers: if this is the warp's last pass of the frame, the filter warp may overwrite the
+    // group's rows with the next hop as far as this warp is concerned
+    if (release) bar_arrive(release, kPair);
 #pragma unroll
     for (int i = 0; i < 16; i += 2) {
         const float t1 = v[i + 1].x;
@@ -940,10 +925,6 @@ __device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, in
         const unsigned ballot = __ballot_sync(kFull, any);
         if (h == 0 && ((ballot >> (16 * half)) & 0xFFFFu)) st->flags[clip][t >> 5] |= 1u << (t & 31);
     }
-#ifdef SJ_DONUT_F32_LATE_RELEASE
-    __syncwarp();
-    if (release && lane == 0) mbar_arrive(release, 1);
-#endif
 }
 
 // double: one pass = spectrogram column t of four rows of one kind, 8 lanes per row (no bit-exact FFT to follow: FFTW's
@@ -958,7 +939,7 @@ __device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, in
 // stall cycles per issued instruction with warps at different places of the pass (profiles/r2l_*).
 // (BAND is a run-time flag, not a template parameter as in the float pass: one copy of the code.)
 __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos, int t, int tb, const SjDonutTables<double> *tab,
-                                         const double *mean_tab, ClipState<double> *st, double *scratch, int lane, int c0, uint32_t release)
+                                         const double *mean_tab, ClipState<double> *st, double *scratch, int lane, int c0, int release)
 {
     typedef double T;
     typedef double2 T2;
@@ -1001,7 +982,7 @@ __device__ __forceinline__ void pass_f64(const bool BAND, double *rows, int pos,
         for (int k = 0; k < 8; ++k) w[8 * h + k] = *reinterpret_cast<const T2 *>(rowp + ((lbase + 18 * k) & 255));
         __syncwarp();
     }
-    if (release && lane == 0) mbar_arrive(release, 1); // done with the rows: the filter warp may write the next hop
+    if (release) bar_arrive(release, kPair); // done with the rows (the warp's last pass of the frame): the next hop may be written
     {
         T2(&u0)[8] = *reinterpret_cast<T2(*)[8]>(&w[0]);
         T2(&u1)[8] = *reinterpret_cast<T2(*)[8]>(&w[8]);
@@ -1087,10 +1068,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
         const uint32_t *src = reinterpret_cast<const uint32_t *>(a.tables);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tab);
         for (int i = threadIdx.x; i < int(sizeof(SjDonutTables<T>) / 4); i += kThreads) dst[i] = __ldg(src + i);
-        if (threadIdx.x < kIir) {
-            mbar_init(smem_u32(&gs_all[threadIdx.x].empty_bar), kPasses);
-            gs_all[threadIdx.x].frames_done = gs_all[threadIdx.x].epilogues_done = 0;
-        }
+        if (threadIdx.x < kIir) gs_all[threadIdx.x].frames_done = gs_all[threadIdx.x].epilogues_done = 0;
     }
     __syncthreads();
     if (threadIdx.x < DN_MAX_TB) frame_time[threadIdx.x] = div_rn((T)(threadIdx.x * DN_HOP + DN_WIN / 2), tab->fs);
@@ -1098,7 +1076,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 
     const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 16, fewer for small batches
     const long n_groups = (a.n_clips + cpg - 1) / cpg;
-    constexpr int kPair = 32 + 32 * kFft; // threads of a "full" barrier: one filter warp + the transform warps
+    static_assert(kPasses >= kFft && kIir <= 4, "every transform warp has a pass in every frame; barrier ids");
     // scratch of group slot g, buffer b: [16][tb][129] PSD cells of the band rows
     auto scratch_of = [&](int g, int b) {
         return reinterpret_cast<T *>(a.scratch) + ((size_t(blockIdx.x) * kIir + g) * 2 + b) * kGroup * tb * DN_BINS;
@@ -1117,8 +1095,6 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 #pragma unroll
         for (int j = 0; j < 9; ++j) { ca[j] = tab->a[f][j]; cb[j] = tab->b[f][j]; }
         T *myrow = rows + lane * kRS;
-        const uint32_t empty_bar = smem_u32(&st->empty_bar);
-        uint32_t empty_phase = 0; // parity of the next phase to wait for: one phase per frame, all groups of this warp in a row
         for (long r = 0;; ++r) {
             const long gid = blockIdx.x + (r * kIir + g) * gridDim.x;
             if (gid >= n_groups) break;
@@ -1162,7 +1138,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
             T acc_cur = 0, acc_next = 0;
             int pos = 0, sample = 0;
             for (int t = 0; t < tb; ++t) {
-                if (t > 0) { mbar_wait(empty_bar, empty_phase); empty_phase ^= 1; } // every pass of frame t - 1 has read its rows
+                if (t > 0) bar_sync(kBarEmpty + g, kPair); // every pass of frame t - 1 has read its rows
                 const int nnew = t == 0 ? DN_WIN : DN_HOP;
 #ifdef SJ_DONUT_SKIP_FILTER /* timing experiment only (results are wrong): the filter warps run the barrier protocol alone */
                 if (t == 0) for (int i = 0; i < 256; ++i) myrow[i] = (T)0.001 * (T)((i * 37 + lane * 11) & 63);
@@ -1216,8 +1192,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                 __threadfence_block();
                 bar_arrive(kBarFull + g, kPair);
             }
-            mbar_wait(empty_bar, empty_phase); // every pass of the last frame has read its rows: they are free for the next group
-            empty_phase ^= 1;
+            bar_sync(kBarEmpty + g, kPair); // every pass of the last frame has read its rows: they are free for the next group
         }
     } else if (warp < kFft) {
         // ------------------------------------------------------------------ transform warps
@@ -1248,7 +1223,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                     GroupState<T> *st = gs_all + g;
                     ClipState<T> *cs = &st->cs[r & 1];
                     T *scratch = scratch_of(g, (int)(r & 1));
-                    const uint32_t release = smem_u32(&st->empty_bar);
+                    const int last_p = w + kFft * ((kPasses - 1 - w) / kFft); // this warp's last pass of the frame
                     bar_sync(kBarFull + g, kPair);
                     // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
                     // double: 8 passes, p < 4 the flag rows; pass j of a kind holds the clips 4 j .. 4 j + 3.
@@ -1260,8 +1235,9 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
                         skip = true;
 #endif
+                        const int release = p == last_p ? kBarEmpty + g : 0;
                         if (skip) {
-                            if (lane == 0) mbar_arrive(release, 1);
+                            if (release) bar_arrive(release, kPair);
                             continue;
                         }
                         if constexpr (sizeof(T) == 4) {
