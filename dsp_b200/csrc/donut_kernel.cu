@@ -68,7 +68,6 @@ __device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(
 __device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
 __device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
 
-__device__ __forceinline__ void fft32(float2 (&v)[32]) { sj_fft32(v); }
 __device__ __forceinline__ void fft32(double2 (&v)[32]) { sj_fft32d(v); }
 
 // 4- / 8-byte asynchronous copy global -> shared (LDGSTS): the band-sum epilogue stages a whole box of PSD cells with
@@ -793,9 +792,12 @@ template <typename T> __device__ __noinline__ T level_of(T av, T U, T mn, T rang
 }
 
 // volatile poll of a shared-memory counter (the hand-overs to and from the epilogue warps: rare, never on the frame path)
+#ifndef SJ_DONUT_EPI_NAP_NS
+#define SJ_DONUT_EPI_NAP_NS 1000
+#endif
 __device__ __forceinline__ void wait_count(const int *ctr, int at_least)
 {
-    while (*reinterpret_cast<const volatile int *>(ctr) < at_least) __nanosleep(200);
+    while (*reinterpret_cast<const volatile int *>(ctr) < at_least) __nanosleep(SJ_DONUT_EPI_NAP_NS);
     __threadfence_block();
 }
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
