@@ -207,6 +207,21 @@ def test_small_batch_grouping_equals_large_batch_grouping(variant):
         assert np.array_equal(l, ref_l[:n]) and np.array_equal(d, ref_d[:n], equal_nan=True), "n = %d" % n
 
 
+@pytest.mark.parametrize("variant", [0, 1])
+def test_many_rounds_per_group_slot_equal_single_round_chunks(variant):
+    """A CTA's group slot takes a new group while the epilogue warps still work on the previous one (two copies of the clip
+    state and of the PSD scratch per slot): 30 000 call-flavoured clips are 4-5 groups per slot; the same
+    clips in chunks that fit one round (and so never reuse a slot within a launch) must give the same bits."""
+    sj = _ctx()
+    n, chunk = 30000, 6000
+    d = _synth_calls(sj, 90000, n)
+    l, det = _gpu(sj, d, variant)
+    for a in range(0, n, chunk):
+        lc, dc = _gpu(sj, d[a:a + chunk].contiguous(), variant)
+        assert np.array_equal(lc, l[a:a + chunk]) and np.array_equal(dc, det[a:a + chunk], equal_nan=True), "chunk at %d" % a
+    assert (det[:, 0] > 0).mean() > 0.3  # many clips have midpoints: the epilogue had real work
+
+
 def _synth_calls(sj, first, n, ns=16000):
     import torch
     import dsp_b200
