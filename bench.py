@@ -34,6 +34,7 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 N_SAMPLES = 16000
 BYTES_PER_CLIP = N_SAMPLES * 4 + 4 + 4  # fp32 clip in, int32 label + fp32 score out
+FP32_PIPE_CYCLES_PER_CLIP = 16 * (643 * 2 + 142)  # per scheduler: packed f32x2 instructions hold the pipe 2 cycles, scalar ones 1
 FRAMES_PER_CLIP = 16
 SEED = 0x5C2B
 METRIC = "clips/s (1 s @16 kHz) cepstrum+SVM"
@@ -604,6 +605,9 @@ def run_ours(args, rank, local_rank, world):
         cpu = cpu_baseline(host[:min(E, 65536)].numpy()) if (args.cpu_baseline and world == 1) else None  # N = 1 only (host is kept at N = 1)
         if cpu and single and cpu.get("one_thread_value"):
             single["cpu_port_us"] = 1e6 / cpu["one_thread_value"]
+        clk_sum = clk.summary()
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        fp32_frac = (value / world) * FP32_PIPE_CYCLES_PER_CLIP / (sms * 4 * clk_sum["sm_mhz"] * 1e6) if clk_sum.get("sm_mhz") else None
         line = {
             "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -620,6 +624,10 @@ def run_ours(args, rank, local_rank, world):
                          "traffic": (traffic or {}).get("dram_bytes_per_clip", 0) * C or None,
                          "traffic_source": "ncu dram bytes per clip (%.0f B, profiles/roofline_traffic.json: a 200 k-clip --set full capture) "
                                            "x the %d clips of this launch" % ((traffic or {}).get("dram_bytes_per_clip", 0), C),
+                         "fp32_frac": fp32_frac, "fp32_pipe_cycles_per_clip": FP32_PIPE_CYCLES_PER_CLIP,
+                         "fp32_frac_note": "clips/s x FP32-pipe cycles per clip (16 frames x (643 packed x 2 + 142 scalar) warp-instruction "
+                                           "cycles per scheduler, profiles/r2f_ncu_opcodes_cepstrum.txt; issue rates measured by "
+                                           "tools/micro/fp32_issue.cu) / (SMs x 4 schedulers x the SM clock sampled during the run)",
                          "fp32_note": "binding resources are the FP32 pipe (58 %), instruction issue (56 %) and the shared-memory LSU (72 %), "
                                       "all per profiles/r2f_ncu_full_cepstrum.txt; HBM is at 29 %",
                          "peak_source": peak_src, "kernel": "cepstrum_kernel<12 warps, TMA, fast-16k>",
@@ -635,7 +643,7 @@ def run_ours(args, rank, local_rank, world):
             "gather_check": gather_check,
             "single_clip": single,
             "gpu_launches": launches,
-            "clocks": clk.summary(),
+            "clocks": clk_sum,
         }
         sys.stdout.flush()
         os.dup2(real_stdout, 1)

@@ -511,6 +511,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             }
             __syncwarp();
 
+#ifdef SJ_EXP_SKIP_MEL /* timing experiment only (results are wrong): the FFT half of a frame alone */
+            sum += (double)(tb[lane] * 1e-9f); sq += 1.0;
+            if (false)
+#endif
             // ---- sparse Slaney mel sums over this lane's bin chunk: two running sums (filter f, f+1);
             // where f steps, the finished sum is flushed and the f+1 sum moves down
             {
@@ -559,6 +563,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
                 }
             }
             __syncwarp();
+#ifdef SJ_EXP_SKIP_MEL
+            if (false)
+#endif
             {
                 float e0 = 0.f, e1 = 0.f;
                 if (FAST) {
@@ -592,6 +599,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) cepstrum_kernel(const SjCepstru
             __syncwarp();
             // ---- DCT-II (first 20 rows) and the reference's double accumulators
             if (!STREAM) {
+#ifdef SJ_EXP_SKIP_MEL
+                if (false)
+#endif
                 if ((hr & 1) || hr == nh - 1) {
                     float acc0 = 0.f, acc1 = 0.f;
                     // folded log energies as 128-bit loads (two addresses per warp: even / odd coefficient lanes)
