@@ -222,6 +222,38 @@ def test_many_rounds_per_group_slot_equal_single_round_chunks(variant):
     assert (det[:, 0] > 0).mean() > 0.3  # many clips have midpoints: the epilogue had real work
 
 
+def test_round1_kernels_behind_the_env_switch_agree_with_the_warp_specialised_ones(tmp_path):
+    """SCRUBJAY_DONUT_LEGACY=1 (read once per process) selects the round-1 kernels: same bits in float (the same arithmetic
+    in another schedule); in double the FFT is organised differently (4 lanes x FFT32 against 8 lanes x FFT16 + FFT8), so
+    midpoint counts and labels are equal and the band sums agree to rounding."""
+    import subprocess
+    script = (
+        "import sys, numpy as np, torch\n"
+        "sys.path.insert(0, %r)\n"
+        "import dsp_b200\n"
+        "sj = dsp_b200.ScrubJay(device=0, samplerate=16000)\n"
+        "sj.set_stream(torch.cuda.current_stream().cuda_stream)\n"
+        "n = 3000\n"
+        "d = torch.empty((n, 16000), dtype=torch.float32, device='cuda')\n"
+        "sj.synth_clips_dev(d, 5150, n, 16000, flavour=dsp_b200.SYNTH_CALLS)\n"
+        "out = {}\n"
+        "for v in (0, 1):\n"
+        "    l = torch.empty(n, dtype=torch.int32, device='cuda'); det = torch.empty((n, 4), device='cuda')\n"
+        "    sj.donut_classify_batch_dev(d, n, 16000, v, l, det); torch.cuda.synchronize()\n"
+        "    out['l%%d' %% v] = l.cpu().numpy(); out['d%%d' %% v] = det.cpu().numpy()\n"
+        "np.savez(sys.argv[1], **out)\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    res = {}
+    for tag, env in (("ws", {}), ("r1", {"SCRUBJAY_DONUT_LEGACY": "1"})):
+        f = str(tmp_path / (tag + ".npz"))
+        subprocess.run([sys.executable, "-c", script, f], check=True, env=dict(os.environ, **env), timeout=300)
+        res[tag] = np.load(f)
+    a, b = res["ws"], res["r1"]
+    assert np.array_equal(a["l1"], b["l1"]) and np.array_equal(a["d1"], b["d1"], equal_nan=True)
+    assert np.array_equal(a["l0"], b["l0"]) and np.array_equal(a["d0"][:, 0], b["d0"][:, 0])
+    assert np.allclose(a["d0"][:, 1:], b["d0"][:, 1:], rtol=1e-5, atol=1e-4)
+    assert (a["d1"][:, 0] > 0).mean() > 0.3
+
+
 def _synth_calls(sj, first, n, ns=16000):
     import torch
     import dsp_b200
