@@ -54,6 +54,8 @@ struct scrubjay_ctx {
     int chunk_n_samples = 0;
     // single-item scratch for scrubjay_predict / scrubjay_mfcc_stats
     float *d_small = nullptr;
+    // mapped pinned results of the single-clip zero-copy path (run_host_batch_impl): labels, conf, score, features
+    float *h_zc = nullptr;
     // grow-only device buffer of scrubjay_mfcc_stats (one clip): allocated on first use, never on the steady-state path
     float *d_one = nullptr;
     size_t one_bytes = 0;
@@ -259,6 +261,7 @@ int scrubjay_create_ex(scrubjay_ctx **out, int device, const void *model_blob, s
         if (ce == cudaSuccess) ce = cudaMalloc(&c->d_tables, sizeof(SjTables));
         if (ce == cudaSuccess) ce = cudaMemcpy(c->d_tables, c->h_tables, sizeof(SjTables), cudaMemcpyHostToDevice);
         if (ce == cudaSuccess) ce = cudaMalloc(&c->d_small, 4096);
+        if (ce == cudaSuccess) ce = cudaHostAlloc(&c->h_zc, 4096, cudaHostAllocMapped);
         if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev0);
         if (ce == cudaSuccess) ce = cudaEventCreate(&c->ev1);
         if (ce == cudaSuccess) ce = sj_cepstrum_setup(c->h_tables->mel_maxseg);
@@ -281,6 +284,7 @@ void scrubjay_destroy(scrubjay_ctx *c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     cudaFree(c->d_tables);
     cudaFree(c->d_small);
+    cudaFreeHost(c->h_zc);
     cudaFree(c->d_one);
     cudaFree(c->d_peers);
     cudaFree(c->d_frame_scratch);
@@ -718,6 +722,30 @@ int run_host_batch_impl(scrubjay_ctx *c, const void *clips_v, long n_clips, int 
     const unsigned char *clips = static_cast<const unsigned char *>(clips_v);
     const size_t es = pcm16 ? 2 : 4; // bytes per sample; the staging buffers are sized for float
     SJ_CUDA(c, cudaSetDevice(c->device));
+    // One to three clips in pinned host memory (BASELINE config 1, the latency case): no copy operations at all.  The
+    // kernels read the clips through their device alias (bulk copies over PCIe: 64 KB per clip) and write the results into
+    // mapped pinned memory of the context -- two launches and one synchronisation instead of a copy in, two launches,
+    // three copies out: 32 us against 45 us per call for one clip (tools/zero_copy_probe.py).  From four clips on the
+    // copy engine is as fast or faster.
+    constexpr long kZeroCopyClips = 3;
+    if (n_clips >= 1 && n_clips <= kZeroCopyClips && c->h_zc && c->fail_at_chunk < 0) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, clips_v) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+            float *zc = nullptr; // [0, 8) labels, [8, 16) confidence, [16, 24) score, from 64 on [clip][40] features
+            SJ_CUDA(c, cudaHostGetDevicePointer((void **)&zc, c->h_zc, 0));
+            int rc = launch_cepstrum(c, c->stream, static_cast<const float *>(at.devicePointer), n_clips, n_samples, (int32_t *)zc,
+                                     zc + 8, zc + 16, feats ? zc + 64 : nullptr, do_svm, false, pcm16);
+            if (rc != SJ_OK) return rc;
+            SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (do_svm) {
+                memcpy(labels, c->h_zc, (size_t)n_clips * 4);
+                if (conf) memcpy(conf, c->h_zc + 8, (size_t)n_clips * 4);
+                if (score) memcpy(score, c->h_zc + 16, (size_t)n_clips * 4);
+            }
+            if (feats) memcpy(feats, c->h_zc + 64, (size_t)n_clips * SJ_FEAT * 4);
+            return SJ_OK;
+        } else cudaGetLastError(); // a pageable pointer is not an error here
+    }
     int rc = ensure_stages(c, n_samples);
     if (rc != SJ_OK) return rc;
     long done = 0;

@@ -90,3 +90,32 @@ def test_host_call_and_gather_call(sj):
         assert np.array_equal(l[1:n + 1].cpu().numpy(), l0) and np.array_equal(s[1:n + 1].cpu().numpy(), s0)
         assert int(l[0]) == -7 and int(l[n + 1]) == -7
     sj.gather_bind([], None, 0)
+
+
+def test_zero_copy_path_of_one_to_three_pinned_clips_equals_the_copy_path():
+    """One to three clips in PINNED host memory take the zero-copy path of scrubjay_infer_batch (the kernels read the clips
+    through their device alias and write into mapped host memory); a pageable copy of the same clips takes the copy path.
+    Same bits, for float and int16 clips, with and without features, and for a ragged length; four clips take the copy path
+    either way."""
+    import torch
+    sj = dsp_b200.ScrubJay(0, 16000)
+    for n, ns in ((1, 16000), (1, 12345), (2, 16000), (3, 7777), (4, 16000)):
+        d = torch.empty((n, ns), dtype=torch.float32, device="cuda")
+        sj.set_stream(torch.cuda.current_stream().cuda_stream)
+        sj.synth_clips_dev(d, 4711, n, ns)
+        torch.cuda.synchronize()
+        pinned = d.cpu().pin_memory()
+        pageable = pinned.numpy().copy()
+        a = sj.infer_batch(pinned.data_ptr(), want_feats=True, n_clips=n, n_samples=ns)
+        b = sj.infer_batch(pageable, want_feats=True)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        a2 = sj.infer_batch(pinned.data_ptr(), n_clips=n, n_samples=ns)
+        assert np.array_equal(a2[0], b[0]) and np.array_equal(a2[2], b[2])
+        pcm = (pinned.numpy() * 32767.0).astype(np.int16)
+        pp = torch.from_numpy(pcm).pin_memory()
+        c1 = sj.infer_batch_pcm16(pp.data_ptr(), n_clips=n, n_samples=ns)
+        c2 = sj.infer_batch_pcm16(pcm)
+        for x, y in zip(c1, c2):
+            assert np.array_equal(x, y)
+    sj.close()
