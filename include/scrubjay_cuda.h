@@ -245,7 +245,9 @@ SJ_API int scrubjay_mfcc_stats(scrubjay_ctx *ctx, const float *samples, long n_s
 /* returns the label (0/1) like ort_predict, or a negative error */
 SJ_API int scrubjay_predict(scrubjay_ctx *ctx, const float feat[SJ_FEAT_DIM], float *conf);
 /* host clips [n_clips][n_samples] (pageable or pinned); chunks are pipelined H2D -> kernel -> D2H
- * on internal streams.  conf / score / feats may be NULL. */
+ * on internal streams.  conf / score / feats may be NULL.  One to three clips in PINNED memory (scrubjay_host_alloc,
+ * cudaHostAlloc, cudaHostRegister) are read by the kernels in place and answered through mapped memory: no copy
+ * operation, 33 us per single-clip call instead of 46 us; the call then runs on the context's stream. */
 SJ_API int scrubjay_infer_batch(scrubjay_ctx *ctx, const float *clips, long n_clips, int n_samples,
                          int32_t *labels, float *conf, float *score, float *feats);
 
