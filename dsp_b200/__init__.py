@@ -579,3 +579,15 @@ def shard_range(n_items, rank, world_size):
     lo = (n_items * rank) // world_size
     hi = (n_items * (rank + 1)) // world_size
     return lo, hi
+
+
+def shard_range_weighted(n_items, rank, weights):
+    """Contiguous clip range [lo, hi) of `rank` when the ranks take shares in proportion to `weights` (one per rank, e.g. each
+    rank's measured host-to-device rate: the PCIe links of a box are not all alike).  The ranges
+    partition [0, n_items) exactly; equal weights give shard_range()."""
+    w = [float(x) for x in weights]
+    if not w or min(w) < 0 or sum(w) <= 0:
+        raise ValueError("weights must be non-negative with a positive sum")
+    tot = sum(w)
+    cut = lambda k: int(round(n_items * sum(w[:k]) / tot)) if k < len(w) else n_items
+    return cut(rank), cut(rank + 1)

@@ -74,3 +74,16 @@ def test_shard_range_partitions_exactly():
             assert r[0][0] == 0 and r[-1][1] == n
             assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
             assert max(b - a for a, b in r) - min(b - a for a, b in r) <= 1
+
+
+def test_shard_range_weighted_partitions_exactly_and_follows_the_weights():
+    for n in (0, 1, 7, 65536 * 8, 10_000_019):
+        for w in ([1, 1, 1, 1], [23.2] * 4 + [35.3] * 4, [0, 1, 0, 3], [5]):
+            r = [dsp_b200.shard_range_weighted(n, k, w) for k in range(len(w))]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(r[k][1] == r[k + 1][0] for k in range(len(w) - 1))
+            for k, (lo, hi) in enumerate(r):
+                assert abs((hi - lo) - n * w[k] / sum(w)) <= 1
+    assert [dsp_b200.shard_range_weighted(1000, k, [1, 1, 1]) for k in range(3)] == [(0, 333), (333, 667), (667, 1000)]
+    with pytest.raises(ValueError):
+        dsp_b200.shard_range_weighted(10, 0, [0, 0])
