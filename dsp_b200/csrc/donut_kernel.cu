@@ -806,15 +806,10 @@ template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("s
 // one pass = spectrogram column t of two rows of one kind (BAND: 3000-7500 Hz rows whose cells are kept; otherwise the
 // 1000-3000 Hz rows that only flag frames), the clips c0 and c0 + 8 of the group; PlainFFT replayed as in
 // spectrogram_column_exact_f32
-// (SJ_DONUT_F32_ONE_PASS_BODY: BAND as a run-time flag = one copy of the FFT code for both row kinds, 9 KB less to keep in
-// the instruction cache next to the filter loop and the epilogue)
-#ifdef SJ_DONUT_F32_ONE_PASS_BODY
-template <bool UNUSED>
-__device__ __forceinline__ void pass_exact_f32(const bool BAND, const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
-#else
+// (BAND as a run-time flag -- one copy of the FFT code for both row kinds, 9 KB less in the instruction cache -- was measured:
+// +2 % with the long filter loop, -1.5 % with the short one that is shipped.)
 template <bool BAND>
-__device__ __forceinline__ void pass_exact_f32(const bool, const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
-#endif
+__device__ __forceinline__ void pass_exact_f32(const float *rows, int pos, int t, int tb, const SjDonutTables<float> *tab,
                                                const float *mean_tab, ClipState<float> *st, FftWarpState<float> *fw, float *scratch,
                                                int lane, int c0, const float2 (&tw)[15], const float (&win)[16], int release)
 {
@@ -1250,12 +1245,8 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                             continue;
                         }
                         if constexpr (sizeof(T) == 4) {
-#ifdef SJ_DONUT_F32_ONE_PASS_BODY
-                            pass_exact_f32<false>(p >= 8, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
-#else
-                            if (p < 8) pass_exact_f32<false>(false, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
-                            else pass_exact_f32<true>(true, rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
-#endif
+                            if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
+                            else pass_exact_f32<true>(rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
                         } else {
                             pass_f64(p >= 4, rows, pos, t, tb, tab, st->mean, cs, scratch, lane, c0, release);
                         }
@@ -1414,11 +1405,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                                 __syncwarp();
                                 int sj = cj, si = ci;
                                 for (int c = cc + lane; c < ncell && c < cc + kStage; c += 32) {
-#ifdef SJ_DONUT_EXP_NOSTAGE /* timing experiment only: results are wrong */
-                                    stage[c - cc] = (T)(c & 1023);
-#else
                                     cp_async_elem(stage + (c - cc), scr + (t0 + sj) * DN_BINS + f0 + si);
-#endif
                                     si += r32;
                                     sj += q32;
                                     if (si >= nf) { si -= nf; ++sj; }
@@ -1437,11 +1424,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                             nq += __popc(bal);
                             __syncwarp();
                             if (nq >= 32) {
-#ifdef SJ_DONUT_EXP_NOLEVEL /* timing experiment only: results are wrong */
-                                acc += (double)qu[lane];
-#else
                                 acc += (double)level(qu[lane]);
-#endif
                                 nq -= 32;
                                 __syncwarp();
                                 if (lane < nq) qu[lane] = qu[32 + lane];
