@@ -78,6 +78,43 @@ template <int NR> __global__ void rec(double *out, int iters, long long *cyc, do
     if (threadIdx.x == 0) *cyc = t1 - t0;
 }
 
+// the kernel's whole step: the recurrence plus y = b0 w0 + b2 w2 + b4 w4 + b6 w6 + b8 w8 (b[odd] = 0) and the frame-mean sum.
+// LAG = 1 forms y of step n - 1 during step n (its inputs are all old values: nothing of it sits behind the new w0)
+template <int LAG> __global__ void full(double *out, int iters, long long *cyc, double b, double c)
+{
+    double w[8], acc = 0, wprev = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = threadIdx.x * 1e-3 + j * 0.01;
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+            double w0 = c;
+#pragma unroll
+            for (int j = 1; j < 9; ++j) w0 = __dsub_rn(w0, __dmul_rn(b, w[(s - j + 8) & 7]));
+            if (LAG == 0) {
+                double yy = __dmul_rn(c, w0);
+#pragma unroll
+                for (int j = 2; j < 9; j += 2) yy = __dadd_rn(yy, __dmul_rn(b, w[(s - j + 8) & 7]));
+                acc = __dadd_rn(acc, yy);
+            } else { // y of the previous step: w0(n-1) = wprev, delayed values shifted by one
+                double yy = __dmul_rn(c, wprev);
+#pragma unroll
+                for (int j = 2; j < 9; j += 2) yy = __dadd_rn(yy, __dmul_rn(b, w[(s - 1 - j + 16) & 7]));
+                acc = __dadd_rn(acc, yy);
+                wprev = w0;
+            }
+            w[s] = w0;
+        }
+    }
+    const long long t1 = clock64();
+    double sum = acc;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sum += w[j];
+    out[threadIdx.x] = sum;
+    if (threadIdx.x == 0) *cyc = t1 - t0;
+}
+
 static double *out;
 static long long *cyc;
 static long long get() { long long h; cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost); return h; }
@@ -101,6 +138,8 @@ int main()
     rec<1><<<1, 32>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"recurrence_step_cycles_1_per_lane\": %.1f,\n", (double)get() / (iters * 8.0));
     rec<2><<<1, 32>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"recurrence_step_cycles_2_per_lane\": %.1f,\n", (double)get() / (iters * 8.0));
     rec<4><<<1, 32>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"recurrence_step_cycles_4_per_lane\": %.1f,\n", (double)get() / (iters * 8.0));
+    full<0><<<1, 32>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"full_step_cycles\": %.1f,\n", (double)get() / (iters * 8.0));
+    full<1><<<1, 32>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"full_step_cycles_output_one_step_behind\": %.1f,\n", (double)get() / (iters * 8.0));
     rec<1><<<1, 128>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"recurrence_step_cycles_1_per_lane_4warps\": %.1f,\n", (double)get() / (iters * 8.0));
     rec<1><<<1, 256>>>(out, iters, cyc, 0.1, 1e-3); printf(" \"recurrence_step_cycles_1_per_lane_8warps\": %.1f\n", (double)get() / (iters * 8.0));
     printf("}\n");
