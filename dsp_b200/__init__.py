@@ -388,9 +388,13 @@ class ScrubJay:
         return out
 
     # ---- host-pointer entry points (numpy in, numpy out)
-    def mfcc_stats(self, samples):
-        x = np.ascontiguousarray(samples, dtype=np.float32)
+    def mfcc_stats(self, samples, n_samples=None):
+        """samples: numpy float32 array, or a raw host address with n_samples"""
         out = np.empty(FEAT_DIM, np.float32)
+        if isinstance(samples, int):
+            self._check(self._L.scrubjay_mfcc_stats(self._h, samples, n_samples, out.ctypes.data))
+            return out
+        x = np.ascontiguousarray(samples, dtype=np.float32)
         self._check(self._L.scrubjay_mfcc_stats(self._h, x.ctypes.data, x.size, out.ctypes.data))
         return out
 

@@ -807,6 +807,19 @@ int scrubjay_mfcc_stats(scrubjay_ctx *c, const float *samples, long n_samples, f
     if (!samples || !out) return set_err(c, SJ_EINVAL, "NULL pointer");
     if (n_samples <= 0 || n_samples > 0x7fffffffL) return set_err(c, SJ_EINVAL, "empty clip");
     SJ_CUDA(c, cudaSetDevice(c->device));
+    {   // a clip in pinned host memory is read in place and answered through mapped memory (see run_host_batch_impl)
+        cudaPointerAttributes at;
+        if (c->h_zc && cudaPointerGetAttributes(&at, samples) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+            float *zc = nullptr;
+            SJ_CUDA(c, cudaHostGetDevicePointer((void **)&zc, c->h_zc, 0));
+            int rc = launch_cepstrum(c, c->stream, static_cast<const float *>(at.devicePointer), 1, (int)n_samples, nullptr, nullptr,
+                                     nullptr, zc + 64, 0, false);
+            if (rc != SJ_OK) return rc;
+            SJ_CUDA(c, cudaStreamSynchronize(c->stream));
+            memcpy(out, c->h_zc + 64, SJ_FEAT * 4);
+            return SJ_OK;
+        } else cudaGetLastError();
+    }
     // the clip goes through a grow-only buffer owned by the context (sized for 4 s at 96 kHz at first use): no
     // allocation on the steady-state path
     const size_t need = (size_t)n_samples * 4;

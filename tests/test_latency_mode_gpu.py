@@ -119,3 +119,18 @@ def test_zero_copy_path_of_one_to_three_pinned_clips_equals_the_copy_path():
         for x, y in zip(c1, c2):
             assert np.array_equal(x, y)
     sj.close()
+
+
+def test_mfcc_stats_of_a_pinned_clip_equals_the_copy_path():
+    import torch
+    sj = dsp_b200.ScrubJay(0, 16000)
+    for ns in (16000, 5000, 40001):
+        d = torch.empty((1, ns), dtype=torch.float32, device="cuda")
+        sj.set_stream(torch.cuda.current_stream().cuda_stream)
+        sj.synth_clips_dev(d, 99, 1, ns)
+        torch.cuda.synchronize()
+        pinned = d.cpu().pin_memory()
+        a = sj.mfcc_stats(pinned.data_ptr(), n_samples=ns)
+        b = sj.mfcc_stats(pinned.numpy().copy().reshape(-1))
+        assert np.array_equal(a, b)
+    sj.close()
