@@ -1073,7 +1073,7 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
 
     const int tb = a.tb, n_samples = a.n_samples, cpg = a.clips_per_cta; // clips per group: 16, fewer for small batches
     const long n_groups = (a.n_clips + cpg - 1) / cpg;
-    static_assert(kPasses >= kFft && kIir <= 4, "every transform warp has a pass in every frame; barrier ids");
+    static_assert(kPasses >= kFft && kPasses % kFft == 0 && kIir <= 4, "every transform warp has the same number of passes in every frame; barrier ids");
     // scratch of group slot g, buffer b: [16][tb][129] PSD cells of the band rows
     auto scratch_of = [&](int g, int b) {
         return reinterpret_cast<T *>(a.scratch) + ((size_t(blockIdx.x) * kIir + g) * 2 + b) * kGroup * tb * DN_BINS;
@@ -1227,23 +1227,32 @@ __global__ void __launch_bounds__(kThreads, 1) donut_ws_kernel(const SjDonutArgs
                     GroupState<T> *st = gs_all + g;
                     ClipState<T> *cs = &st->cs[r & 1];
                     T *scratch = scratch_of(g, (int)(r & 1));
-                    const int last_p = w + kFft * ((kPasses - 1 - w) / kFft); // this warp's last pass of the frame
                     bar_sync(kBarFull + g, kPair);
                     // float: 16 passes, p < 8 the flag rows, p >= 8 the band rows; pass j of a kind holds the clips j, j + 8.
                     // double: 8 passes, p < 4 the flag rows; pass j of a kind holds the clips 4 j .. 4 j + 3.
-                    // Warp w takes the passes w, w + kFft, ...  (A shared-memory ticket counter -- atomicAdd, later a
-                    // compare-and-swap that never claims beyond the frame -- cost 6 % of the float kernel's throughput.)
-                    for (int p = w; p < kPasses; p += kFft) {
-                        const int c0 = sizeof(T) == 4 ? (p & 7) : 4 * (p & 3);
-                        bool skip = c0 >= nact;
+                    // Warp w takes one pass per round k of kFft passes: (w + 1 + 4 k) mod kFft of round k.  (A shared-memory
+                    // ticket counter -- atomicAdd, later a compare-and-swap that never claims beyond the frame -- cost 6 % of
+                    // the float kernel's throughput.)  The offsets matter for small batches only, where a group holds few clips:
+                    // + 1 keeps the passes of a group's first clip off the scheduler of the group's filter warp (warp 12 + g),
+                    // + 4 k gives the flag pass and the band pass of a clip to different warps, so that they run side by side
+                    // and each warp reports "rows read" right after its loads (one clip: 645 -> 583 us; round-1 kernel 536 us).
+                    auto pass_of = [&](int k) { return (w + 1 + 4 * k) % kFft + kFft * k; };
+                    auto clip0_of = [&](int p) { return sizeof(T) == 4 ? (p & 7) : 4 * (p & 3); };
+                    // the warp's last pass with clips in it: the filter warp is told "rows read" after that pass's loads (at
+                    // once if the warp has nothing to do in this frame)
+                    int last_k = -1;
+#pragma unroll
+                    for (int k = 0; k < kPasses / kFft; ++k)
+                        if (clip0_of(pass_of(k)) < nact) last_k = k;
 #ifdef SJ_DONUT_SKIP_FFT /* timing experiment only: results are wrong */
-                        skip = true;
+                    last_k = -1;
 #endif
-                        const int release = p == last_p ? kBarEmpty + g : 0;
-                        if (skip) {
-                            if (release) bar_arrive(release, kPair);
-                            continue;
-                        }
+                    if (last_k < 0) bar_arrive(kBarEmpty + g, kPair);
+#pragma unroll
+                    for (int k = 0; k < kPasses / kFft; ++k) {
+                        const int p = pass_of(k), c0 = clip0_of(p);
+                        if (c0 >= nact || last_k < 0) continue;
+                        const int release = k == last_k ? kBarEmpty + g : 0;
                         if constexpr (sizeof(T) == 4) {
                             if (p < 8) pass_exact_f32<false>(rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
                             else pass_exact_f32<true>(rows, pos, t, tb, tab, st->mean, cs, fw, scratch, lane, c0, tw, win, release);
