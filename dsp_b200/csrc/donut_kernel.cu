@@ -1484,20 +1484,30 @@ template <typename T> size_t smem_total()
 
 } // namespace
 
-// A/B switch: SCRUBJAY_DONUT_LEGACY=1 keeps the round-1 kernels (CTA-wide barriers, warp 0 filters alone) for both
-// precisions, =f32 / =f64 for one of them
-static int donut_legacy_mask()
+// Which kernel runs.  The warp-specialised kernels win on throughput, the round-1 kernels (CTA-wide barriers, warp 0 filters
+// alone) on the latency of small batches: up to about one round of groups per CTA (60 clips per SM) a float batch takes the
+// round-1 kernel, whose results are the same bit for bit (tests/test_donut_gpu.py: ..._agree_with_the_warp_specialised_ones).
+// The double kernels organise the FFT differently (equal to rounding only), and a clip's result must not depend on the size
+// of the batch it came in: double always takes the warp-specialised kernel.
+// SCRUBJAY_DONUT_LEGACY=1 forces the round-1 kernels for both precisions, =f32 / =f64 for one of them, =0 never uses them.
+static int donut_legacy_mask() // bit 0 / 1: always round-1 for float / double; bit 2: never
 {
     static const int mask = [] {
         const char *e = getenv("SCRUBJAY_DONUT_LEGACY");
-        if (!e || !e[0] || e[0] == '0') return 0;
+        if (!e || !e[0]) return 0;
+        if (e[0] == '0') return 4;
         if (e[0] == 'f') return e[1] == '6' ? 2 : 1;
         return 3;
     }();
     return mask;
 }
-bool sj_donut_legacy_f32() { return donut_legacy_mask() & 1; }
-bool sj_donut_legacy(bool f64) { return donut_legacy_mask() & (f64 ? 2 : 1); }
+static bool use_round1(bool f64, long n_clips, int num_sms)
+{
+    const int m = donut_legacy_mask();
+    if (m & (f64 ? 2 : 1)) return true;
+    if (m & 4) return false;
+    return !f64 && n_clips <= 60L * num_sms;
+}
 
 cudaError_t sj_donut_setup()
 {
@@ -1516,21 +1526,25 @@ cudaError_t sj_donut_setup()
     return e;
 }
 
-int sj_donut_grid(int num_sms, bool f64)
+static int round1_grid(int num_sms, bool f64)
 {
-    if (!sj_donut_legacy(f64)) return num_sms; // warp-specialised kernels: one persistent CTA per SM
-    int per_sm = 0;
-    if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true, false>, DnWarps<double>::value * 32, smem_total<double>());
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true, false>, DnWarps<float>::value * 32, smem_total<float>());
-    if (per_sm < 1) per_sm = 1;
+    static int per_sm_cache[2] = {0, 0};
+    int &per_sm = per_sm_cache[f64 ? 1 : 0];
+    if (per_sm < 1) {
+        if (f64) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<double, true, false>, DnWarps<double>::value * 32, smem_total<double>());
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, donut_kernel<float, true, false>, DnWarps<float>::value * 32, smem_total<float>());
+        if (per_sm < 1) per_sm = 1;
+    }
     return num_sms * per_sm;
 }
 
-size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64)
+// PSD scratch for the clips in flight, sized for whichever kernel a launch may take
+size_t sj_donut_scratch_bytes(int num_sms, int tb, bool f64)
 {
-    if (!sj_donut_legacy(f64)) // two buffers per group slot: a group's epilogue runs while the slot's next group is transformed
-        return size_t(f64 ? ws::Cfg<double>::kIir : ws::Cfg<float>::kIir) * 2 * ws::kGroup * tb * DN_BINS * (f64 ? 8 : 4);
-    return size_t(DN_CLIPS_PER_WARP) * tb * DN_BINS * (f64 ? 8 : 4);
+    // warp-specialised: two buffers per group slot (a group's epilogue runs while the slot's next group is transformed)
+    const size_t ws_bytes = size_t(num_sms) * (f64 ? ws::Cfg<double>::kIir : ws::Cfg<float>::kIir) * 2 * ws::kGroup * tb * DN_BINS * (f64 ? 8 : 4);
+    const size_t r1_bytes = size_t(round1_grid(num_sms, f64)) * DN_CLIPS_PER_WARP * tb * DN_BINS * (f64 ? 8 : 4);
+    return ws_bytes > r1_bytes ? ws_bytes : r1_bytes;
 }
 
 template <typename T> static cudaError_t launch_ws(SjDonutArgs a, int grid, cudaStream_t stream)
@@ -1550,11 +1564,12 @@ template <typename T> static cudaError_t launch_ws(SjDonutArgs a, int grid, cuda
     return cudaGetLastError();
 }
 
-cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int grid, cudaStream_t stream)
+cudaError_t sj_launch_donut(const SjDonutArgs &a_in, bool f64, int num_sms, cudaStream_t stream)
 {
     if (a_in.n_clips <= 0) return cudaSuccess;
     SjDonutArgs a = a_in;
-    if (!sj_donut_legacy(f64)) return f64 ? launch_ws<double>(a, grid, stream) : launch_ws<float>(a, grid, stream);
+    if (!use_round1(f64, a.n_clips, num_sms)) return f64 ? launch_ws<double>(a, num_sms, stream) : launch_ws<float>(a, num_sms, stream);
+    int grid = round1_grid(num_sms, f64);
     long cpc = (a.n_clips + grid - 1) / grid; // spread small batches over the resident CTAs
     if (cpc > DN_CLIPS_PER_WARP) cpc = DN_CLIPS_PER_WARP;
     if (cpc < 1) cpc = 1;

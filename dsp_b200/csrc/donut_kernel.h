@@ -63,10 +63,8 @@ void sj_donut_build_tables_f32(SjDonutTables<float> *t, const SjDonutParams &p, 
 void sj_donut_build_tables_f64(SjDonutTables<double> *t, const SjDonutParams &p, int fs);
 void sj_donut_default_params(SjDonutParams *p, int variant); // 0: classifier.c (f64 row), 1: sync/lib (f32 row), 2, 3, 4: classifier.ino
 
-// number of CTAs (1 warp each) the kernel wants for `num_sms` SMs, and scratch bytes per CTA
-int sj_donut_grid(int num_sms, bool f64);
-size_t sj_donut_scratch_bytes_per_cta(int tb, bool f64);
+// PSD scratch bytes for a launch on `num_sms` SMs (whichever kernel it takes); the launch picks kernel and grid itself:
+// SCRUBJAY_DONUT_LEGACY = 1 | f32 | f64 forces the round-1 kernels, = 0 the warp-specialised ones (donut_kernel.cu: use_round1)
+size_t sj_donut_scratch_bytes(int num_sms, int tb, bool f64);
 cudaError_t sj_donut_setup();
-bool sj_donut_legacy_f32(); // SCRUBJAY_DONUT_LEGACY=1 (both precisions), =f32, =f64: the round-1 kernels instead of the warp-specialised ones
-bool sj_donut_legacy(bool f64);
-cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int grid, cudaStream_t stream);
+cudaError_t sj_launch_donut(const SjDonutArgs &a, bool f64, int num_sms, cudaStream_t stream);

@@ -79,7 +79,6 @@ struct scrubjay_ctx {
     int peer_access_on[SJ_MAX_PEERS * 2] = {0}; // devices this context has enabled peer access to (index = device id)
     // donut path (allocated on first use): tables per variant, PSD scratch for the clips in flight
     void *d_donut_tables[SJ_DONUT_N_VARIANTS] = {nullptr, nullptr, nullptr, nullptr};
-    int donut_grid[SJ_DONUT_N_VARIANTS] = {0, 0, 0, 0};
     void *d_donut_scratch = nullptr;
     size_t donut_scratch_bytes = 0;
     float *d_donut_clips = nullptr; // host-path staging
@@ -943,9 +942,8 @@ int donut_prepare(scrubjay_ctx *c, int variant, int n_samples, int *tb_out)
             SJ_CUDA(c, cudaMalloc(&c->d_donut_tables[variant], sizeof t));
             SJ_CUDA(c, cudaMemcpy(c->d_donut_tables[variant], &t, sizeof t, cudaMemcpyHostToDevice));
         }
-        c->donut_grid[variant] = sj_donut_grid(c->num_sms, f64);
     }
-    const size_t need = sj_donut_scratch_bytes_per_cta(tb, f64) * (size_t)c->donut_grid[variant];
+    const size_t need = sj_donut_scratch_bytes(c->num_sms, tb, f64);
     if (need > c->donut_scratch_bytes) {
         SJ_CUDA(c, cudaStreamSynchronize(c->stream));
         cudaFree(c->d_donut_scratch);
@@ -967,7 +965,7 @@ int donut_launch(scrubjay_ctx *c, const float *d_clips, long n_clips, int n_samp
     a.tables = c->d_donut_tables[variant]; a.scratch = c->d_donut_scratch; a.labels = d_labels; a.detail = d_detail; a.mids = d_mids;
     a.track = d_track; a.row_stride = row_stride; a.clips_per_row = clips_per_row;
     SJ_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-    SJ_CUDA(c, sj_launch_donut(a, sj_donut_variant_is_f64(variant), c->donut_grid[variant], c->stream));
+    SJ_CUDA(c, sj_launch_donut(a, sj_donut_variant_is_f64(variant), c->num_sms, c->stream));
     SJ_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->have_timing = true;
     if (n_clips > 0) c->launches += 1;

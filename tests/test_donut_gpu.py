@@ -223,8 +223,9 @@ def test_many_rounds_per_group_slot_equal_single_round_chunks(variant):
 
 
 def test_round1_kernels_behind_the_env_switch_agree_with_the_warp_specialised_ones(tmp_path):
-    """SCRUBJAY_DONUT_LEGACY=1 (read once per process) selects the round-1 kernels: same bits in float (the same arithmetic
-    in another schedule); in double the FFT is organised differently (4 lanes x FFT32 against 8 lanes x FFT16 + FFT8), so
+    """SCRUBJAY_DONUT_LEGACY (read once per process) = 1 forces the round-1 kernels, = 0 the warp-specialised ones (by default
+    small float batches take the former, everything else the latter): same bits in float (the same arithmetic in another
+    schedule -- which is what allows the library to switch by batch size); in double the FFT is organised differently (4 lanes x FFT32 against 8 lanes x FFT16 + FFT8), so
     midpoint counts and labels are equal and the band sums agree to rounding."""
     import subprocess
     script = (
@@ -243,7 +244,7 @@ def test_round1_kernels_behind_the_env_switch_agree_with_the_warp_specialised_on
         "    out['l%%d' %% v] = l.cpu().numpy(); out['d%%d' %% v] = det.cpu().numpy()\n"
         "np.savez(sys.argv[1], **out)\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     res = {}
-    for tag, env in (("ws", {}), ("r1", {"SCRUBJAY_DONUT_LEGACY": "1"})):
+    for tag, env in (("ws", {"SCRUBJAY_DONUT_LEGACY": "0"}), ("r1", {"SCRUBJAY_DONUT_LEGACY": "1"})):  # 0 = never, 1 = always round 1
         f = str(tmp_path / (tag + ".npz"))
         subprocess.run([sys.executable, "-c", script, f], check=True, env=dict(os.environ, **env), timeout=300)
         res[tag] = np.load(f)
