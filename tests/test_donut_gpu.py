@@ -129,6 +129,21 @@ def test_ragged_lengths(ns):
         _compare(gl, gd, ol, od, variant, tol)
 
 
+@pytest.mark.parametrize("ns", [479, 3001, 7200])
+def test_ragged_lengths_large_batch_equals_small_batch(ns):
+    """Large batches take the warp-specialised kernels (unaligned instantiation for odd lengths, aligned otherwise), small
+    float batches the round-1 kernel: the first clips of a 9 500-clip batch must equal the same clips classified alone
+    (float: another kernel, same bits; double: the same kernel in another grouping)."""
+    import torch
+    sj = _ctx()
+    n = 9500
+    d = _synth_calls(sj, 321, n, ns)
+    for variant in (0, 1):
+        l, det = _gpu(sj, d, variant)
+        ls, ds = _gpu(sj, d[:300].contiguous(), variant)
+        assert np.array_equal(ls, l[:300]) and np.array_equal(ds, det[:300], equal_nan=True)
+
+
 def test_too_short_and_silent():
     import dsp_b200
     sj = _ctx()
