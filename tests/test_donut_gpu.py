@@ -210,6 +210,28 @@ def test_stream_decision_track_equals_clip_path():
     assert np.array_equal(track2.cpu().numpy().reshape(-1), labels.astype(np.int8) + 1)
 
 
+def test_stream_decision_tracks_of_a_large_stream_array_equal_the_clip_path():
+    """the same for 1 300 channels x 7 s = 9 100 clips: the warp-specialised kernels' stream addressing (odd and aligned row
+    strides), against the clip path on contiguous clips"""
+    import torch
+    import dsp_b200
+    sj = _ctx()
+    ch, secs = 1300, 7
+    clips = _synth_calls(sj, 5000, ch * secs)
+    for stride in (secs * 16000 + 3, secs * 16000 + 16):
+        streams = torch.zeros((ch, stride), dtype=torch.float32, device="cuda")
+        streams[:, :secs * 16000] = clips.view(ch, secs * 16000)
+        for variant in (dsp_b200.DONUT_SYNC_F32, dsp_b200.DONUT_DESKTOP_F64):
+            labels, detail = _gpu(sj, clips, variant)
+            track = torch.zeros((ch, secs), dtype=torch.int8, device="cuda")
+            det2 = torch.empty((ch, secs, 4), dtype=torch.float32, device="cuda")
+            sj.donut_classify_streams_dev(streams, ch, secs * 16000, stride, variant, track, det2)
+            torch.cuda.synchronize()
+            assert np.array_equal(track.cpu().numpy().reshape(-1), labels.astype(np.int8) + 1)
+            assert np.array_equal(det2.cpu().numpy().reshape(-1, 4), detail, equal_nan=True)
+        del streams
+
+
 @pytest.mark.parametrize("variant", [0, 1])
 def test_small_batch_grouping_equals_large_batch_grouping(variant):
     """Small batches are spread over the CTAs (down to one clip per CTA, absent clips' passes skipped), large ones
